@@ -1,0 +1,309 @@
+// fk_math.h -- pose / quaternion / Jacobian primitives shared by the host model code (g++) and the
+// sm_100a kernels (nvcc).  Header only, no CUDA API in here.
+//
+// Every function states the reference expression it evaluates.  In the FP64 "strict" mode the
+// operation ORDER is the reference's (left-to-right as written there) and the translation unit is
+// built without FMA contraction (nvcc -fmad=false / g++ -ffp-contract=off), so results are
+// bit-identical to the reference built with the same libm (oracle/_ref/libtinyfk_ref_strict.so).
+// The only liberty taken: products with a literal 0.0 operand are dropped where the reference
+// multiplies a pure-vector quaternion (w == 0) -- that can flip the sign of an exact zero, never a
+// non-zero bit (documented in DESIGN.md, "signed zeros").
+//
+// Reference files: urdf_parser/include/urdf_model/pose.h (Rotation, Pose), urdf_parser/src/pose.cpp
+// (pose_transform, cross_product), urdf_parser/include/urdf_model/joint.h:227-253 (Joint::transform),
+// src/kinematics.cpp:14-35 (rpy_derivative, q_derivative).
+#ifndef TFK_FK_MATH_H
+#define TFK_FK_MATH_H
+
+#include "fkmath.h"
+
+#if defined(__CUDACC__)
+#define TFK_FN __host__ __device__ __forceinline__
+#else
+#define TFK_FN inline
+#endif
+
+namespace tfk {
+
+template <class T> struct Vec3 {
+  T x, y, z;
+};
+template <class T> struct Quat {
+  T x, y, z, w;
+};
+template <class T> struct PoseT {
+  Vec3<T> p;
+  Quat<T> q;
+};
+
+// ---- math policies --------------------------------------------------------------------------
+// Portable libm: identical bits on host and device (fkmath.h).  FP64 only.
+struct MathPortable {
+  typedef double real;
+  static TFK_FN double sin_(double x) { return tfk_sin(x); }
+  static TFK_FN double cos_(double x) { return tfk_cos(x); }
+  static TFK_FN void sincos_(double x, double *s, double *c) { tfk_sincos(x, s, c); }
+  static TFK_FN double asin_(double x) { return tfk_asin(x); }
+  static TFK_FN double atan2_(double y, double x) { return tfk_atan2(y, x); }
+  static TFK_FN double sqrt_(double x) { return sqrt(x); }
+};
+
+// The platform's own libm (glibc on the host, libdevice on the GPU).
+struct MathNative64 {
+  typedef double real;
+  static TFK_FN double sin_(double x) { return ::sin(x); }
+  static TFK_FN double cos_(double x) { return ::cos(x); }
+  static TFK_FN void sincos_(double x, double *s, double *c) {
+#if defined(__CUDA_ARCH__)
+    ::sincos(x, s, c);
+#else
+    *s = ::sin(x);
+    *c = ::cos(x);
+#endif
+  }
+  static TFK_FN double asin_(double x) { return ::asin(x); }
+  static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
+  static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
+};
+
+struct MathNative32 {
+  typedef float real;
+  static TFK_FN float sin_(float x) { return ::sinf(x); }
+  static TFK_FN float cos_(float x) { return ::cosf(x); }
+  static TFK_FN void sincos_(float x, float *s, float *c) {
+#if defined(__CUDA_ARCH__)
+    ::sincosf(x, s, c);
+#else
+    *s = ::sinf(x);
+    *c = ::cosf(x);
+#endif
+  }
+  static TFK_FN float asin_(float x) { return ::asinf(x); }
+  static TFK_FN float atan2_(float y, float x) { return ::atan2f(y, x); }
+  static TFK_FN float sqrt_(float x) { return ::sqrtf(x); }
+};
+
+template <class M> struct Ops {
+  typedef typename M::real T;
+  typedef Vec3<T> V;
+  typedef Quat<T> Q;
+  typedef PoseT<T> P;
+
+  static TFK_FN Q qidentity() {
+    Q q;
+    q.x = q.y = q.z = T(0);
+    q.w = T(1);
+    return q;
+  }
+
+  // Rotation::operator*(Rotation), pose.h:253-263
+  static TFK_FN Q qmul(const Q &a, const Q &b) {
+    Q c;
+    c.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+    c.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+    c.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+    c.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+    return c;
+  }
+
+  // Rotation::GetInverse, pose.h:284-299 (returns the default-constructed identity if norm <= 0)
+  static TFK_FN Q qget_inverse(const Q &q) {
+    T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
+    Q r = qidentity();
+    if (norm > T(0)) {
+      r.w = q.w / norm;
+      r.x = -q.x / norm;
+      r.y = -q.y / norm;
+      r.z = -q.z / norm;
+    }
+    return r;
+  }
+
+  // Rotation::inverse, pose.h:301-304 (no norm check)
+  static TFK_FN Q qinverse(const Q &q) {
+    T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
+    Q r;
+    r.x = -q.x / norm;
+    r.y = -q.y / norm;
+    r.z = -q.z / norm;
+    r.w = q.w / norm;
+    return r;
+  }
+
+  // Rotation::operator*(Vector3), pose.h:265-282:  q * ((v,0) * GetInverse(q)), xyz part.
+  // (v,0) * inv with the literal-zero products dropped (see file header).
+  static TFK_FN V rotate(const Q &q, const V &v) {
+    Q i = qget_inverse(q);
+    Q t;
+    t.x = v.x * i.w + v.y * i.z - v.z * i.y;
+    t.y = -(v.x * i.z) + v.y * i.w + v.z * i.x;
+    t.z = v.x * i.y - v.y * i.x + v.z * i.w;
+    t.w = -(v.x * i.x) - v.y * i.y - v.z * i.z;
+    V r;
+    r.x = q.w * t.x + q.x * t.w + q.y * t.z - q.z * t.y;
+    r.y = q.w * t.y - q.x * t.z + q.y * t.w + q.z * t.x;
+    r.z = q.w * t.z + q.x * t.y - q.y * t.x + q.z * t.w;
+    return r;
+  }
+
+  // urdf::pose_transform, pose.cpp:139-146
+  static TFK_FN P compose(const P &a, const P &b) {
+    P o;
+    o.q = qmul(a.q, b.q);
+    V r = rotate(a.q, b.p);
+    o.p.x = r.x + a.p.x;
+    o.p.y = r.y + a.p.y;
+    o.p.z = r.z + a.p.z;
+    return o;
+  }
+
+  // Rotation::normalize, pose.h:230-250
+  static TFK_FN void qnormalize(Q &q) {
+    T s = M::sqrt_(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    if (s == T(0)) {
+      q = qidentity();
+    } else {
+      q.x /= s;
+      q.y /= s;
+      q.z /= s;
+      q.w /= s;
+    }
+  }
+
+  // Rotation::setFromRPY, pose.h:202-216
+  static TFK_FN Q from_rpy(T roll, T pitch, T yaw) {
+    T phi = roll / T(2), the = pitch / T(2), psi = yaw / T(2);
+    T sph, cph, sth, cth, sps, cps;
+    M::sincos_(phi, &sph, &cph);
+    M::sincos_(the, &sth, &cth);
+    M::sincos_(psi, &sps, &cps);
+    Q q;
+    q.x = sph * cth * cps - cph * sth * sps;
+    q.y = cph * sth * cps + sph * cth * sps;
+    q.z = cph * cth * sps - sph * sth * cps;
+    q.w = cph * cth * cps + sph * sth * sps;
+    qnormalize(q);
+    return q;
+  }
+
+  // Rotation::getRPY, pose.h:161-192
+  static TFK_FN V to_rpy(const Q &q) {
+    T sqx = q.x * q.x, sqy = q.y * q.y, sqz = q.z * q.z, sqw = q.w * q.w;
+    T sarg = T(-2) * (q.x * q.z - q.w * q.y);
+    const T pi_2 = T(1.57079632679489661923);
+    V r;
+    if (sarg <= T(-0.99999)) {
+      r.y = -pi_2;
+      r.x = T(0);
+      r.z = T(2) * M::atan2_(q.x, -q.y);
+    } else if (sarg >= T(0.99999)) {
+      r.y = pi_2;
+      r.x = T(0);
+      r.z = T(2) * M::atan2_(-q.x, q.y);
+    } else {
+      r.y = M::asin_(sarg);
+      r.x = M::atan2_(T(2) * (q.y * q.z + q.w * q.x), sqw - sqx - sqy + sqz);
+      r.z = M::atan2_(T(2) * (q.x * q.y + q.w * q.z), sqw + sqx - sqy - sqz);
+    }
+    return r;
+  }
+
+  // Joint::transform for REVOLUTE/CONTINUOUS, joint.h:231-240 (axis is NOT normalised)
+  static TFK_FN Q joint_quat(const V &axis, T angle) {
+    T s, c;
+    M::sincos_(angle * T(0.5), &s, &c);
+    Q q;
+    q.x = axis.x * s;
+    q.y = axis.y * s;
+    q.z = axis.z * s;
+    q.w = c;
+    return q;
+  }
+
+  // pose_transform(origin, Joint::transform(angle)) for a revolute joint (src/kinematics.cpp:77-80).
+  // Joint::transform leaves position = 0, so rotate(origin.q, 0) = (+-0,+-0,+-0) and the sum is
+  // origin.p (up to the sign of an exact zero).
+  static TFK_FN P local_revolute(const P &origin, const V &axis, T angle) {
+    P o;
+    o.q = qmul(origin.q, joint_quat(axis, angle));
+    o.p = origin.p;
+    return o;
+  }
+
+  // same for PRISMATIC (joint.h:241-247): rotation identity, position axis*angle.  Evaluated in full.
+  static TFK_FN P local_prismatic(const P &origin, const V &axis, T angle) {
+    P j;
+    j.q = qidentity();
+    j.p.x = axis.x * angle;
+    j.p.y = axis.y * angle;
+    j.p.z = axis.z * angle;
+    return compose(origin, j);
+  }
+
+  // Pose::inverse, pose.h:329-339 (Rotation::inverse_inplace :306-312, Vector3::inverse_inplace :95-99)
+  static TFK_FN P inverse(const P &a) {
+    P o;
+    T norm = a.q.w * a.q.w + a.q.x * a.q.x + a.q.y * a.q.y + a.q.z * a.q.z;
+    o.q.w = a.q.w / norm;
+    o.q.x = -a.q.x / norm;
+    o.q.y = -a.q.y / norm;
+    o.q.z = -a.q.z / norm;
+    V n;
+    n.x = a.p.x * T(-1);
+    n.y = a.p.y * T(-1);
+    n.z = a.p.z * T(-1);
+    o.p = rotate(o.q, n);
+    return o;
+  }
+
+  // urdf::cross_product, pose.cpp:90-94
+  static TFK_FN V cross(const V &a, const V &b) {
+    V o;
+    o.x = a.y * b.z - a.z * b.y;
+    o.y = a.z * b.x - a.x * b.z;
+    o.z = a.x * b.y - a.y * b.x;
+    return o;
+  }
+
+  // Coefficients of rpy_derivative (src/kinematics.cpp:14-23) that depend only on the link's rpy.
+  // The reference recomputes cos/sin per joint; the values are the same, so hoisting is exact.
+  struct RpyCoef {
+    T k_xx, k_xy; //  cos(a3)/cos(a2),  sin(a3)/cos(a2)
+    T s3, c3;     //  sin(a3), cos(a3)
+    T k_zx, k_zy; // -cos(a3)*sin(a2)/cos(a2),  sin(a3)*sin(a2)/cos(a2)
+  };
+  static TFK_FN RpyCoef rpy_coef(const V &rpy) {
+    T a2 = -rpy.y, a3 = -rpy.z;
+    T s2, c2, s3, c3;
+    M::sincos_(a2, &s2, &c2);
+    M::sincos_(a3, &s3, &c3);
+    RpyCoef k;
+    k.k_xx = c3 / c2;
+    k.k_xy = s3 / c2;
+    k.s3 = s3;
+    k.c3 = c3;
+    k.k_zx = -c3 * s2 / c2;
+    k.k_zy = s3 * s2 / c2;
+    return k;
+  }
+  static TFK_FN V rpy_derivative(const RpyCoef &k, const V &axis) {
+    V d;
+    d.x = k.k_xx * axis.x - k.k_xy * axis.y;
+    d.y = k.s3 * axis.x + k.c3 * axis.y;
+    d.z = k.k_zx * axis.x + k.k_zy * axis.y + axis.z;
+    return d;
+  }
+
+  // q_derivative, src/kinematics.cpp:25-35 (literal 0 * q terms dropped); returns (dx,dy,dz,-dw)
+  static TFK_FN Q q_derivative(const Q &q, const V &om) {
+    Q d;
+    d.x = T(0.5) * (om.z * q.y - om.y * q.z + om.x * q.w);
+    d.y = T(0.5) * (-(om.z * q.x) + om.x * q.z + om.y * q.w);
+    d.z = T(0.5) * (om.y * q.x - om.x * q.y + om.z * q.w);
+    d.w = -(T(0.5) * (-(om.x * q.x) - om.y * q.y - om.z * q.z));
+    return d;
+  }
+};
+
+} // namespace tfk
+#endif

@@ -1,0 +1,201 @@
+// plan.cpp -- see plan.hpp / fk_plan.h.
+#include "plan.hpp"
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+namespace tfk {
+
+namespace {
+
+struct Builder {
+  const KinematicModel &m;
+  const PlanKey &key;
+  std::vector<char> needed;       // per link
+  std::vector<int> qcol_of_joint; // per joint id: last column that names it, or -1
+  std::vector<int> slot_of_link;  // per link
+  std::vector<PlanSlot> slots;
+  int frames_live, frames_max;
+
+  Builder(const KinematicModel &model, const PlanKey &k)
+      : m(model), key(k), needed(model.n_links(), 0), qcol_of_joint(model.n_joints(), -1),
+        slot_of_link(model.n_links(), -1), frames_live(0), frames_max(0) {}
+
+  void visit(int u, int frame_ld) {
+    const LinkRec &l = m.links()[u];
+    PlanSlot s;
+    std::memset(&s, 0, sizeof s);
+    s.qcol = -1;
+    s.frame_ld = frame_ld;
+    s.frame_st = -1;
+    s.jrec = -1;
+    s.lrec = -1;
+    const bool selected = l.jid >= 0 && qcol_of_joint[l.jid] >= 0;
+    Pose64 local;
+    if (selected) {
+      s.kind = (l.jtype == JT_PRISMATIC) ? SLOT_PRISMATIC : SLOT_REVOLUTE;
+      s.qcol = qcol_of_joint[l.jid];
+      local = l.origin;
+    } else {
+      // not driven by the input: the joint sits at the model's stored angle (src/tinyfk.cpp:122-128)
+      s.kind = SLOT_FIXED;
+      local = (l.jid >= 0) ? m.local_transform(l, m.joint_angles()[l.jid]) : l.origin;
+    }
+    s.opos[0] = local.p.x;
+    s.opos[1] = local.p.y;
+    s.opos[2] = local.p.z;
+    s.oquat[0] = local.q.x;
+    s.oquat[1] = local.q.y;
+    s.oquat[2] = local.q.z;
+    s.oquat[3] = local.q.w;
+    s.axis[0] = l.axis.x;
+    s.axis[1] = l.axis.y;
+    s.axis[2] = l.axis.z;
+
+    int n_children = 0;
+    for (int c : l.children)
+      if (needed[c]) ++n_children;
+    if (n_children >= 2) {
+      s.frame_st = frames_live++;
+      if (frames_live > frames_max) frames_max = frames_live;
+    }
+    slot_of_link[u] = (int)slots.size();
+    slots.push_back(s);
+    const int my_frame = s.frame_st;
+    bool first = true;
+    for (int c : l.children) {
+      if (!needed[c]) continue;
+      visit(c, first ? (int)FRAME_RUNNING : my_frame);
+      first = false;
+    }
+    if (my_frame >= 0) --frames_live;
+  }
+};
+
+} // namespace
+
+std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey &key) {
+  const int n_out = (int)key.elink_ids.size();
+  const int n_cols = (int)key.joint_ids.size();
+  if (key.rot_type < 0 || key.rot_type > 2) throw std::invalid_argument("rot_type must be 0 (IGNORE), 1 (RPY) or 2 (XYZW)");
+  if (key.base_type < 0 || key.base_type > 2) throw std::invalid_argument("base_type must be 0 (FIXED), 1 (PLANER) or 2 (FLOATING)");
+  for (int id : key.elink_ids)
+    if (id < 0 || (size_t)id >= model.n_links()) throw std::invalid_argument("link id " + std::to_string(id) + " out of range");
+  for (int id : key.joint_ids)
+    if (id < 0 || (size_t)id >= model.n_joints()) throw std::invalid_argument("joint id " + std::to_string(id) + " out of range");
+
+  Builder b(model, key);
+  const std::vector<LinkRec> &links = model.links();
+  const int root = model.root_link_id();
+  for (int id : key.elink_ids)
+    for (int l = id; l >= 0 && l != root; l = links[l].parent) {
+      if (b.needed[l]) break;
+      b.needed[l] = 1;
+    }
+  for (int c = 0; c < n_cols; ++c) b.qcol_of_joint[key.joint_ids[c]] = c; // last one wins
+
+  for (int c : links[root].children)
+    if (b.needed[c]) b.visit(c, FRAME_BASE);
+  if (b.frames_max > TFK_MAX_FRAMES)
+    throw std::invalid_argument("kinematic tree branches too deeply for the kernel's frame file (" +
+                                std::to_string(b.frames_max) + " > " + std::to_string((int)TFK_MAX_FRAMES) + ")");
+
+  const bool jac = key.with_jacobian != 0;
+  // joint records: one per selected joint whose child link is on a requested chain
+  int n_jrec = 0;
+  std::vector<int> jrec_of_joint(model.n_joints(), -1);
+  std::vector<PlanCol> cols(n_cols);
+  if (jac) {
+    for (size_t s = 0; s < b.slots.size(); ++s) {
+      if (b.slots[s].kind == SLOT_FIXED) continue;
+      b.slots[s].jrec = n_jrec++;
+    }
+    for (size_t l = 0; l < links.size(); ++l) {
+      int s = b.slot_of_link[l];
+      if (s >= 0 && b.slots[s].jrec >= 0) jrec_of_joint[links[l].jid] = b.slots[s].jrec;
+    }
+  }
+  for (int c = 0; c < n_cols; ++c) {
+    cols[c].jrec = jac ? jrec_of_joint[key.joint_ids[c]] : -1;
+    cols[c].prismatic = model.joints()[key.joint_ids[c]].type == JT_PRISMATIC ? 1 : 0;
+  }
+
+  // link records: one per distinct requested link
+  int n_lrec = 0, root_lrec = -1;
+  std::vector<int> lrec_of_out(n_out, -1);
+  for (int o = 0; o < n_out; ++o) {
+    const int id = key.elink_ids[o];
+    if (id == root) {
+      if (root_lrec < 0) root_lrec = n_lrec++;
+      lrec_of_out[o] = root_lrec;
+    } else {
+      PlanSlot &s = b.slots[b.slot_of_link[id]];
+      if (s.lrec < 0) s.lrec = n_lrec++;
+      lrec_of_out[o] = s.lrec;
+    }
+  }
+
+  const int mask_words = (n_cols + 31) / 32 > 0 ? (n_cols + 31) / 32 : 1;
+  std::vector<uint32_t> masks((size_t)n_out * mask_words, 0u);
+  if (jac)
+    for (int o = 0; o < n_out; ++o)
+      for (int c = 0; c < n_cols; ++c)
+        if (model.is_relevant(key.elink_ids[o], key.joint_ids[c]))
+          masks[(size_t)o * mask_words + c / 32] |= (1u << (c % 32));
+
+  PlanHeader h;
+  std::memset(&h, 0, sizeof h);
+  h.n_slots = (int)b.slots.size();
+  h.n_out = n_out;
+  h.n_cols = n_cols;
+  h.n_jrec = n_jrec;
+  h.n_lrec = n_lrec;
+  h.rot_type = key.rot_type;
+  h.base_type = key.base_type;
+  h.pose_dim = pose_dim_of(key.rot_type);
+  h.with_jacobian = jac ? 1 : 0;
+  h.n_in = n_cols + base_dof_of(key.base_type);
+  h.n_out_cols = h.n_in;
+  // IGNORE needs positions only -- also for the base columns, whose position rows never read the
+  // link's rotation (src/kinematics.cpp:189-219 with pose.cpp:139-146)
+  h.lrec_size = key.rot_type == ROT_IGNORE ? 3 : 7;
+  h.off_base = 0;
+  const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 0;
+  h.off_jrec = h.off_base + base_rec;
+  h.off_lrec = h.off_jrec + 6 * n_jrec;
+  h.rec_size = h.off_lrec + h.lrec_size * n_lrec;
+  h.root_lrec = root_lrec;
+  h.mask_words = mask_words;
+  h.n_frames = b.frames_max;
+  const Pose64 &bp = model.base_pose();
+  h.base_pose[0] = bp.p.x;
+  h.base_pose[1] = bp.p.y;
+  h.base_pose[2] = bp.p.z;
+  h.base_pose[3] = bp.q.x;
+  h.base_pose[4] = bp.q.y;
+  h.base_pose[5] = bp.q.z;
+  h.base_pose[6] = bp.q.w;
+
+  size_t off = sizeof(PlanHeader);
+  h.off_slots = (int)off;
+  off += sizeof(PlanSlot) * b.slots.size();
+  h.off_outs = (int)off;
+  off += sizeof(int32_t) * n_out;
+  h.off_masks = (int)off;
+  off += sizeof(uint32_t) * masks.size();
+  h.off_cols = (int)off;
+  off += sizeof(PlanCol) * n_cols;
+  off = (off + 15) & ~(size_t)15;
+  h.total_bytes = (int)off;
+
+  std::vector<unsigned char> blob(off, 0);
+  std::memcpy(blob.data(), &h, sizeof h);
+  if (!b.slots.empty()) std::memcpy(blob.data() + h.off_slots, b.slots.data(), sizeof(PlanSlot) * b.slots.size());
+  if (n_out) std::memcpy(blob.data() + h.off_outs, lrec_of_out.data(), sizeof(int32_t) * n_out);
+  if (!masks.empty()) std::memcpy(blob.data() + h.off_masks, masks.data(), sizeof(uint32_t) * masks.size());
+  if (n_cols) std::memcpy(blob.data() + h.off_cols, cols.data(), sizeof(PlanCol) * n_cols);
+  return blob;
+}
+
+} // namespace tfk

@@ -1,0 +1,30 @@
+// plan.hpp -- host flattening: model + call signature -> plan blob (fk_plan.h).
+#ifndef TFK_PLAN_HPP
+#define TFK_PLAN_HPP
+
+#include <cstdint>
+#include <vector>
+
+#include "fk_plan.h"
+#include "model.hpp"
+
+namespace tfk {
+
+struct PlanKey {
+  std::vector<int> elink_ids, joint_ids;
+  int rot_type, base_type, with_jacobian;
+  uint64_t model_version;
+  bool operator==(const PlanKey &o) const {
+    return rot_type == o.rot_type && base_type == o.base_type && with_jacobian == o.with_jacobian &&
+           model_version == o.model_version && elink_ids == o.elink_ids && joint_ids == o.joint_ids;
+  }
+};
+
+// Builds the plan blob.  Throws std::invalid_argument on out-of-range ids or too deep branching.
+std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey &key);
+
+inline int pose_dim_of(int rot_type) { return 3 + (rot_type == ROT_RPY) * 3 + (rot_type == ROT_XYZW) * 4; }
+inline int base_dof_of(int base_type) { return base_type == BASE_PLANER ? 3 : (base_type == BASE_FLOATING ? 6 : 0); }
+
+} // namespace tfk
+#endif
