@@ -1,0 +1,130 @@
+/*
+ * tinyfk_b200.h -- C ABI of the B200-native batched forward-kinematics engine.
+ *
+ * This is the drop-in boundary for tinyfk's FK path: plain pointers and sizes, no C++ types, no
+ * exceptions, no torch types.  Each entry names the reference interface it replaces (paths relative
+ * to the tinyfk source tree, HiroIshida/tinyfk @ f18ea42).  The pybind11 module _tinyfk
+ * (tinyfk_b200/csrc/wrapper.cpp) re-exports it to Python as numpy-in / numpy-out under the reference's
+ * own class and method names (src/wrapper.cpp:246-283).
+ *
+ * Conventions
+ *   - Every function returns 0 on success or a TFK_ERR_* code; tfk_last_error() gives the message
+ *     for the calling thread.  TFK_ERR_INVALID mirrors std::invalid_argument (-> Python ValueError),
+ *     TFK_ERR_RUNTIME mirrors std::runtime_error (-> RuntimeError), TFK_ERR_CUDA is a CUDA failure
+ *     (including "no CUDA device": there is NO CPU fallback).
+ *   - ids are the reference's ids: links in lexicographic name order, then "<link>_com" links, then
+ *     user links; joints = movable joints in lexicographic order (src/tinyfk.cpp:23-64, 89-111).
+ *   - rot_type: 0 IGNORE, 1 RPY, 2 XYZW (include/tinyfk.hpp:53).  base_type: 0 FIXED, 1 PLANER,
+ *     2 FLOATING (python/tinyfk/__init__.py:29-32).  pose_dim = 3 / 6 / 7.
+ *   - Input rows: [q(joint_ids[0]) ... q(joint_ids[n-1]), base...] with base = (x, y, yaw) for PLANER,
+ *     (x, y, z, roll, pitch, yaw) for FLOATING (python/tinyfk/__init__.py:98-103, 133-142).
+ *   - Outputs are COLUMN-MAJOR exactly as the reference hands them to numpy (src/wrapper.cpp:80-82,123):
+ *       P[d * (N*n_link) + i*n_link + j]                         shape (N*n_link, pose_dim)
+ *       J[c * (N*n_link*pose_dim) + (i*n_link + j)*pose_dim + r] shape (N*n_link*pose_dim, n_dof)
+ *     with n_dof = n_joint (+3 PLANER: x, y, yaw columns, python/tinyfk/__init__.py:154-158; +6 FLOATING).
+ *   - precision: TFK_F64_STRICT computes in double in the reference's operation order (matches the
+ *     reference to 1e-12 and the libm-pinned reference bit for bit); TFK_F32 is the opt-in float mode
+ *     (arrays are float, tolerance 1e-5).
+ */
+#ifndef TINYFK_B200_H
+#define TINYFK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TFK_API __attribute__((visibility("default")))
+#else
+#define TFK_API
+#endif
+
+typedef struct tfk_model tfk_model; /* opaque: tinyfk::KinematicModel (include/tinyfk.hpp:55-161) */
+
+enum { TFK_OK = 0, TFK_ERR_INVALID = 1, TFK_ERR_RUNTIME = 2, TFK_ERR_CUDA = 3 };
+enum { TFK_ROT_IGNORE = 0, TFK_ROT_RPY = 1, TFK_ROT_XYZW = 2 };
+enum { TFK_BASE_FIXED = 0, TFK_BASE_PLANER = 1, TFK_BASE_FLOATING = 2 };
+enum { TFK_F64_STRICT = 0, TFK_F32 = 1 };
+enum { TFK_LIBM_PORTABLE = 0, TFK_LIBM_SYSTEM = 1 };
+
+/* message of the last failing call on this thread */
+TFK_API const char *tfk_last_error(void);
+
+/* ---- model life cycle ------------------------------------------------------------------------ */
+/* KinematicModel::KinematicModel(xml_string), src/tinyfk.cpp:16-114 (RobotModel(xml), src/wrapper.cpp:255).
+ * host_libm selects the libm that evaluates host-side constants (TFK_LIBM_PORTABLE: bit-compatible with
+ * the kernels; TFK_LIBM_SYSTEM: the platform libm, as stock tinyfk on this host). */
+TFK_API int tfk_model_create(const char *xml, size_t xml_len, int host_libm, tfk_model **out);
+TFK_API void tfk_model_destroy(tfk_model *m);
+
+/* ---- ids, names, limits ------------------------------------------------------------------------ */
+TFK_API int tfk_num_links(const tfk_model *m);   /* links_.size(), include/tinyfk.hpp:61 */
+TFK_API int tfk_num_joints(const tfk_model *m);  /* joints_.size(), include/tinyfk.hpp:65 */
+TFK_API int tfk_root_link_id(const tfk_model *m); /* root_link_id_, include/tinyfk.hpp:60 */
+TFK_API double tfk_total_mass(const tfk_model *m); /* total_mass_, src/wrapper.cpp:256 */
+/* get_link_names / get_joint_names, include/tinyfk.hpp:114-130; NULL if id is out of range */
+TFK_API const char *tfk_link_name(const tfk_model *m, int link_id);
+TFK_API const char *tfk_joint_name(const tfk_model *m, int joint_id);
+/* get_link_ids / get_joint_ids, src/tinyfk.cpp:203-215 / 150-162; unknown name -> TFK_ERR_INVALID */
+TFK_API int tfk_get_link_ids(const tfk_model *m, const char *const *names, int n, int *ids_out);
+TFK_API int tfk_get_joint_ids(const tfk_model *m, const char *const *names, int n, int *ids_out);
+/* get_joint_position_limits, src/tinyfk.cpp:164-179 (continuous joints: -inf / +inf) */
+TFK_API int tfk_get_joint_limits(const tfk_model *m, const int *joint_ids, int n, double *lower, double *upper);
+/* get_joint_velocity_limits / get_joint_effort_limits, src/tinyfk.cpp:181-201 */
+TFK_API int tfk_get_joint_velocity_limits(const tfk_model *m, const int *joint_ids, int n, double *out);
+TFK_API int tfk_get_joint_effort_limits(const tfk_model *m, const int *joint_ids, int n, double *out);
+/* rptable_.isRelevant(link, joint), include/tinyfk.hpp:43; writes 0/1 */
+TFK_API int tfk_is_relevant(const tfk_model *m, int link_id, int joint_id, int *out);
+
+/* ---- stored state ---------------------------------------------------------------------------- */
+/* set_joint_angles / get_joint_angles, src/tinyfk.cpp:116-148 */
+TFK_API int tfk_set_joint_angles(tfk_model *m, const int *joint_ids, int n, const double *angles);
+TFK_API int tfk_get_joint_angles(const tfk_model *m, const int *joint_ids, int n, double *angles);
+/* set_base_pose(xyzrpy) / get_base_pose(), src/wrapper.cpp:37-55 */
+TFK_API int tfk_set_base_pose(tfk_model *m, const double xyzrpy[6]);
+TFK_API int tfk_get_base_pose(const tfk_model *m, double xyzrpy[6]);
+/* add_new_link(name, parent_id, position, rpy), src/tinyfk.cpp:217-258; duplicate name -> TFK_ERR_INVALID */
+TFK_API int tfk_add_new_link(tfk_model *m, const char *name, int parent_id, const double pos[3],
+                             const double rpy[3], int *new_id_out);
+
+/* ---- the hot path ---------------------------------------------------------------------------- */
+/* Batched solve_fk on HOST buffers: KinematicsModelPyWrapper::solve_forward_kinematics
+ * (src/wrapper.cpp:60-124) + the facade glue of KinematicModel.solve_fk (python/tinyfk/__init__.py:105-159).
+ * q: n x n_in row-major (double, or float for TFK_F32).  P, J: column-major outputs as described above
+ * (J may be NULL when with_jacobian == 0).  devices/n_devices: CUDA ordinals to shard the batch over
+ * (contiguous slices, no collective); NULL/0 = the current device.  Copies are chunked and overlapped
+ * with the kernel; pass pinned memory (tfk_host_alloc) for full PCIe speed.  Like the reference, the
+ * model's stored joint angles / base pose afterwards are those of the LAST configuration. */
+TFK_API int tfk_solve_fk_host(tfk_model *m, const void *q, int64_t n, const int *elink_ids, int n_link,
+                              const int *joint_ids, int n_joint, int rot_type, int base_type,
+                              int with_jacobian, int precision, const int *devices, int n_devices, void *P,
+                              void *J);
+
+/* Same computation on DEVICE-resident buffers of `device`, enqueued on `stream` (a cudaStream_t; NULL =
+ * the legacy default stream) and not synchronised.  The destination arrays are dimensioned for ld_cfg
+ * configurations and this call fills configurations [row0, row0 + n).  Does not touch the model's stored
+ * state.  This is the entry the throughput metric is timed on. */
+TFK_API int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                const int *elink_ids, int n_link, const int *joint_ids, int n_joint,
+                                int rot_type, int base_type, int with_jacobian, int precision, void *d_P,
+                                void *d_J, int64_t ld_cfg, int64_t row0);
+
+/* ---- helpers ---------------------------------------------------------------------------------- */
+TFK_API int tfk_device_count(int *count);
+/* pinned host memory for the host path (pooled; tfk_host_free returns the block to the pool) */
+TFK_API int tfk_host_alloc(size_t bytes, void **ptr);
+TFK_API int tfk_host_free(void *ptr);
+/* kernels launched by this library since load (bench.py's gpu_launches) */
+TFK_API int64_t tfk_kernel_launch_count(void);
+/* name of the kernel last launched for (m, precision) and its launch shape, for logs */
+TFK_API int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int *smem_bytes, int *blocks_per_sm,
+                                 int *rec_reals);
+TFK_API const char *tfk_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TINYFK_B200_H */

@@ -1,0 +1,105 @@
+// emu_driver.cpp -- TEST INFRASTRUCTURE, not a product path and never loaded by tinyfk_b200.
+//
+// Runs the SAME per-thread code the CUDA kernels run (tinyfk_b200/csrc/fk_core.h, phase A / phase B)
+// serially on the CPU, driven by the product's own host model + plan flattening.  Purpose: this
+// container has no GPU, so the kernel logic is debugged here against oracle/_ref before GPU time is
+// spent; `-m "not gpu"` tests also use it to pin the host logic (plan pruning, masks, layouts).
+// Built by tests/emu/build.sh with g++ -ffp-contract=off (the CPU equivalent of nvcc -fmad=false).
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../tinyfk_b200/csrc/fk_core.h"
+#include "../../tinyfk_b200/csrc/model.hpp"
+#include "../../tinyfk_b200/csrc/plan.hpp"
+
+using namespace tfk;
+
+static thread_local std::string g_err;
+
+template <class Core, class T>
+static void run(const std::vector<unsigned char> &blob, const double *qs, long n, double *Pd, double *Jd) {
+  PlanView pv = plan_view(blob.data());
+  const PlanHeader &h = *pv.h;
+  const long long ldP = (long long)n * h.n_out, ldJ = ldP * h.pose_dim;
+  std::vector<T> rec((size_t)(h.rec_size > 0 ? h.rec_size : 1));
+  std::vector<T> qrow((size_t)(h.n_in > 0 ? h.n_in : 1));
+  std::vector<T> P((size_t)ldP * h.pose_dim), J(h.with_jacobian ? (size_t)ldJ * h.n_out_cols : 0);
+  for (long i = 0; i < n; ++i) {
+    for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
+    Core::phase_a(pv, qrow.data(), rec.data(), 1);
+    for (int o = 0; o < h.n_out; ++o) Core::phase_b(pv, rec.data(), 1, i, o, P.data(), J.data(), ldP, ldJ);
+  }
+  for (size_t k = 0; k < P.size(); ++k) Pd[k] = (double)P[k];
+  if (Jd)
+    for (size_t k = 0; k < J.size(); ++k) Jd[k] = (double)J[k];
+}
+
+extern "C" {
+const char *emu_last_error() { return g_err.c_str(); }
+
+void *emu_create(const char *xml, int system_libm) {
+  try {
+    return new KinematicModel(std::string(xml), system_libm ? LIBM_SYSTEM : LIBM_PORTABLE);
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return nullptr;
+  }
+}
+void emu_destroy(void *m) { delete static_cast<KinematicModel *>(m); }
+int emu_add_link(void *m, const char *name, int parent, const double *pos, const double *rpy) {
+  try {
+    return static_cast<KinematicModel *>(m)->add_new_link(name, (size_t)parent, pos, rpy);
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+void emu_set_joint_angles(void *m, const int *ids, int n, const double *a) {
+  std::vector<size_t> v(ids, ids + n);
+  std::vector<double> x(a, a + n);
+  static_cast<KinematicModel *>(m)->set_joint_angles(v, x);
+}
+void emu_set_base_pose(void *m, const double *b) { static_cast<KinematicModel *>(m)->set_base_pose_xyzrpy(b); }
+int emu_num_links(void *m) { return (int)static_cast<KinematicModel *>(m)->n_links(); }
+int emu_num_joints(void *m) { return (int)static_cast<KinematicModel *>(m)->n_joints(); }
+int emu_root(void *m) { return static_cast<KinematicModel *>(m)->root_link_id(); }
+const char *emu_link_name(void *m, int i) { return static_cast<KinematicModel *>(m)->links()[i].name.c_str(); }
+const char *emu_joint_name(void *m, int i) { return static_cast<KinematicModel *>(m)->joints()[i].name.c_str(); }
+void emu_link_info(void *m, int id, int *parent, int *jtype, int *jid, double *axis, double *origin7) {
+  const LinkRec &l = static_cast<KinematicModel *>(m)->links()[id];
+  *parent = l.parent;
+  *jtype = l.jtype;
+  *jid = l.jid;
+  axis[0] = l.axis.x, axis[1] = l.axis.y, axis[2] = l.axis.z;
+  origin7[0] = l.origin.p.x, origin7[1] = l.origin.p.y, origin7[2] = l.origin.p.z;
+  origin7[3] = l.origin.q.x, origin7[4] = l.origin.q.y, origin7[5] = l.origin.q.z, origin7[6] = l.origin.q.w;
+}
+int emu_is_relevant(void *m, int l, int j) { return static_cast<KinematicModel *>(m)->is_relevant(l, j) ? 1 : 0; }
+
+// mode 0: FP64 strict (portable libm, FD base columns); 1: FP32 (native libm, analytic base columns);
+// 2: FP64 with the platform libm (FD base columns)
+int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, const int *joints, int n_joint,
+              int rot_type, int base_type, int with_jacobian, int mode, double *P, double *J) {
+  try {
+    PlanKey key;
+    key.elink_ids.assign(elinks, elinks + n_link);
+    key.joint_ids.assign(joints, joints + n_joint);
+    key.rot_type = rot_type;
+    key.base_type = base_type;
+    key.with_jacobian = with_jacobian;
+    key.model_version = static_cast<KinematicModel *>(m)->version();
+    std::vector<unsigned char> blob = build_plan(*static_cast<KinematicModel *>(m), key);
+    if (mode == 0)
+      run<FkCore<MathPortable, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr);
+    else if (mode == 1)
+      run<FkCore<MathNative32, true>, float>(blob, qs, n, P, with_jacobian ? J : nullptr);
+    else
+      run<FkCore<MathNative64, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr);
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
+}

@@ -1,0 +1,380 @@
+// engine.cpp -- see engine.hpp.
+#include "engine.hpp"
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+
+namespace tfk {
+
+namespace {
+
+std::atomic<int64_t> g_launches(0);
+
+inline void ck(cudaError_t e, const char *what) {
+  if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+struct DeviceGuard { // restore the caller's current device
+  int prev;
+  bool ok;
+  explicit DeviceGuard(int dev) : prev(0), ok(false) {
+    ck(cudaGetDevice(&prev), "cudaGetDevice (is a CUDA device present? there is no CPU fallback)");
+    ok = true;
+    if (dev != prev) ck(cudaSetDevice(dev), "cudaSetDevice");
+  }
+  ~DeviceGuard() {
+    if (ok) cudaSetDevice(prev);
+  }
+};
+
+inline size_t real_size(int precision) { return precision == PREC_F32 ? sizeof(float) : sizeof(double); }
+
+// ---- pinned pool --------------------------------------------------------------------------------
+std::mutex g_pin_mu;
+std::map<void *, size_t> g_pin_live;            // handed out
+std::multimap<size_t, void *> g_pin_free;       // available, by size
+
+} // namespace
+
+int64_t kernel_launch_count() { return g_launches.load(); }
+
+void *pinned_alloc(size_t bytes) {
+  if (bytes == 0) bytes = 1;
+  std::lock_guard<std::mutex> lk(g_pin_mu);
+  auto it = g_pin_free.lower_bound(bytes);
+  if (it != g_pin_free.end() && it->first <= bytes + bytes / 4 + 4096) {
+    void *p = it->second;
+    g_pin_live[p] = it->first;
+    g_pin_free.erase(it);
+    return p;
+  }
+  void *p = nullptr;
+  ck(cudaHostAlloc(&p, bytes, cudaHostAllocPortable), "cudaHostAlloc");
+  g_pin_live[p] = bytes;
+  return p;
+}
+
+void pinned_free(void *p) {
+  if (!p) return;
+  std::lock_guard<std::mutex> lk(g_pin_mu);
+  auto it = g_pin_live.find(p);
+  if (it == g_pin_live.end()) throw std::invalid_argument("tfk_host_free: pointer was not returned by tfk_host_alloc");
+  g_pin_free.emplace(it->second, p);
+  g_pin_live.erase(it);
+  // keep the pool bounded: drop the largest free blocks beyond 8 GiB
+  size_t total = 0;
+  for (auto &kv : g_pin_free) total += kv.first;
+  while (total > (size_t(8) << 30) && !g_pin_free.empty()) {
+    auto last = std::prev(g_pin_free.end());
+    total -= last->first;
+    cudaFreeHost(last->second);
+    g_pin_free.erase(last);
+  }
+}
+
+// ---- engine -------------------------------------------------------------------------------------
+Engine::Engine(const std::string &xml, HostLibm libm) : model(xml, libm) { std::memset(&last_launch, 0, sizeof last_launch); }
+
+Engine::~Engine() { release_device_memory(); }
+
+void Engine::release_device_memory() {
+  int prev = 0;
+  if (cudaGetDevice(&prev) != cudaSuccess) return;
+  for (auto &e : plans_)
+    for (auto &kv : e->on_device) {
+      cudaSetDevice(kv.first);
+      cudaFree(kv.second);
+    }
+  plans_.clear();
+  for (auto &kv : workspaces_) {
+    cudaSetDevice(kv.first.first);
+    cudaFree(kv.second.scratch);
+  }
+  workspaces_.clear();
+  for (auto &kv : pipes_) {
+    cudaSetDevice(kv.first);
+    for (int s = 0; s < 2; ++s) {
+      cudaStreamSynchronize(kv.second.stream[s]);
+      cudaFree(kv.second.dq[s]);
+      cudaFree(kv.second.dP[s]);
+      cudaFree(kv.second.dJ[s]);
+      cudaStreamDestroy(kv.second.stream[s]);
+    }
+  }
+  pipes_.clear();
+  cudaSetDevice(prev);
+}
+
+int Engine::sm_count(int device) {
+  auto it = sm_counts_.find(device);
+  if (it != sm_counts_.end()) return it->second;
+  int n = 0;
+  ck(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
+  sm_counts_[device] = n;
+  return n;
+}
+
+Engine::PlanEntry &Engine::plan_for(const SolveSpec &spec) {
+  if (spec.n_link < 0 || spec.n_joint < 0) throw std::invalid_argument("negative id count");
+  PlanKey key;
+  key.elink_ids.assign(spec.elink_ids, spec.elink_ids + spec.n_link);
+  key.joint_ids.assign(spec.joint_ids, spec.joint_ids + spec.n_joint);
+  key.rot_type = spec.rot_type;
+  key.base_type = spec.base_type;
+  key.with_jacobian = spec.with_jacobian ? 1 : 0;
+  key.model_version = model.version();
+  for (auto &e : plans_)
+    if (e->key == key) return *e;
+  std::vector<unsigned char> blob = build_plan(model, key);
+  // same signature, older model version, identical bytes (the stored state that changed is not used by
+  // this plan): keep the uploaded copies
+  for (auto &e : plans_) {
+    PlanKey k2 = e->key;
+    k2.model_version = key.model_version;
+    if (k2 == key && e->blob == blob) {
+      e->key.model_version = key.model_version;
+      return *e;
+    }
+  }
+  if (plans_.size() >= 64) { // bounded cache: drop everything (rare), after the devices went idle
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (auto &e : plans_)
+      for (auto &kv : e->on_device) {
+        cudaSetDevice(kv.first);
+        cudaDeviceSynchronize();
+        cudaFree(kv.second);
+      }
+    cudaSetDevice(prev);
+    plans_.clear();
+  }
+  std::unique_ptr<PlanEntry> e(new PlanEntry);
+  e->key = key;
+  e->blob.swap(blob);
+  plans_.push_back(std::move(e));
+  return *plans_.back();
+}
+
+const unsigned char *Engine::plan_on_device(PlanEntry &e, int device, cudaStream_t stream) {
+  auto it = e.on_device.find(device);
+  if (it != e.on_device.end()) return it->second;
+  unsigned char *d = nullptr;
+  ck(cudaMalloc(&d, e.blob.size()), "cudaMalloc(plan)");
+  // pageable source: the runtime stages it before returning, and the copy is ordered before the kernel
+  cudaError_t err = cudaMemcpyAsync(d, e.blob.data(), e.blob.size(), cudaMemcpyHostToDevice, stream);
+  if (err != cudaSuccess) {
+    cudaFree(d);
+    ck(err, "cudaMemcpyAsync(plan)");
+  }
+  // other streams may use this copy right away: make it visible device-wide first
+  ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(plan upload)");
+  e.on_device[device] = d;
+  return d;
+}
+
+Engine::Workspace &Engine::workspace(int device, cudaStream_t stream, size_t bytes) {
+  Workspace &w = workspaces_[std::make_pair(device, stream)];
+  if (w.scratch_bytes < bytes) {
+    if (w.scratch) {
+      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(workspace)");
+      cudaFree(w.scratch);
+      w.scratch = nullptr;
+      w.scratch_bytes = 0;
+    }
+    ck(cudaMalloc(&w.scratch, bytes), "cudaMalloc(records)");
+    w.scratch_bytes = bytes;
+  }
+  return w;
+}
+
+void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n,
+                    void *d_P, void *d_J, int64_t ld_cfg, int64_t row0) {
+  const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
+  if (n <= 0 || h->n_out == 0) return;
+  if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
+  const int smem = (int)e.blob.size();
+  if (smem > 200 * 1024) throw std::invalid_argument("plan too large for shared memory");
+  auto okey = std::make_pair(precision, smem);
+  auto oit = occupancy_.find(okey);
+  int bps = 0;
+  if (oit == occupancy_.end()) {
+    ck(precision == PREC_F32 ? occupancy_fk_f32(smem, &bps) : occupancy_fk_f64_strict(smem, &bps), "occupancy query");
+    if (bps < 1) throw CudaError("kernel does not fit on an SM");
+    occupancy_[okey] = bps;
+  } else {
+    bps = oit->second;
+  }
+  const int64_t n_tiles = (n + TFK_TILE - 1) / TFK_TILE;
+  const int64_t resident = (int64_t)sm_count(device) * bps;
+  const int grid = (int)std::min<int64_t>(n_tiles, resident);
+  const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(h->rec_size, 1) * real_size(precision);
+  Workspace &w = workspace(device, stream, rec_bytes);
+  KernelArgs a;
+  a.plan = plan_on_device(e, device, stream);
+  a.plan_bytes = smem;
+  a.q = d_q;
+  a.n = n;
+  a.row0 = row0;
+  a.ld_cfg = ld_cfg;
+  a.P = d_P;
+  a.J = d_J;
+  a.scratch = w.scratch;
+  ck(precision == PREC_F32 ? launch_fk_f32(a, grid, stream) : launch_fk_f64_strict(a, grid, stream), "kernel launch");
+  g_launches.fetch_add(1);
+  last_launch.grid = grid;
+  last_launch.block = TFK_TILE;
+  last_launch.smem_bytes = smem;
+  last_launch.blocks_per_sm = bps;
+  last_launch.rec_reals = h->rec_size;
+}
+
+void Engine::solve_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec,
+                          void *d_P, void *d_J, int64_t ld_cfg, int64_t row0) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (row0 < 0 || row0 + n > ld_cfg) throw std::invalid_argument("rows [row0, row0+n) exceed ld_cfg");
+  PlanEntry &e = plan_for(spec);
+  if (n == 0) return;
+  if (!d_q && reinterpret_cast<const PlanHeader *>(e.blob.data())->n_in > 0) throw std::invalid_argument("q is null");
+  if (!d_P) throw std::invalid_argument("P is null");
+  if (spec.with_jacobian && !d_J) throw std::invalid_argument("J is null but with_jacobian is set");
+  DeviceGuard g(device);
+  launch(device, stream, e, spec.precision, d_q, n, d_P, d_J, ld_cfg, row0);
+}
+
+Engine::HostPipe &Engine::pipe(int device) {
+  HostPipe &p = pipes_[device];
+  if (!p.ready) {
+    for (int s = 0; s < 2; ++s) ck(cudaStreamCreateWithFlags(&p.stream[s], cudaStreamNonBlocking), "cudaStreamCreate");
+    p.ready = true;
+  }
+  return p;
+}
+
+static void grow(void **buf, size_t *cap, size_t need, cudaStream_t st) {
+  if (*cap >= need) return;
+  if (*buf) {
+    cudaStreamSynchronize(st); // the slot's buffers are only ever used on the slot's stream
+    cudaFree(*buf);
+    *buf = nullptr;
+    *cap = 0;
+  }
+  ck(cudaMalloc(buf, need), "cudaMalloc(staging)");
+  *cap = need;
+}
+
+// Host buffers in, host buffers out.  The batch is cut into contiguous per-device slices (no
+// collective: configurations are independent) and each slice into chunks that ping-pong between two
+// stream slots, so chunk k's device->host copies overlap chunk k+1's host->device copy and kernel.
+void Engine::solve_host(const void *q, int64_t n, const SolveSpec &spec, const int *devices, int n_devices, void *P,
+                        void *J) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  PlanEntry &e = plan_for(spec);
+  const PlanHeader h = *reinterpret_cast<const PlanHeader *>(e.blob.data());
+  if (n == 0 || h.n_out == 0) return;
+  if (!q && h.n_in > 0) throw std::invalid_argument("q is null");
+  if (!P) throw std::invalid_argument("P is null");
+  const bool jac = h.with_jacobian != 0;
+  if (jac && !J) throw std::invalid_argument("J is null but with_jacobian is set");
+
+  int cur = 0;
+  ck(cudaGetDevice(&cur), "cudaGetDevice (is a CUDA device present? there is no CPU fallback)");
+  std::vector<int> devs;
+  if (devices && n_devices > 0)
+    devs.assign(devices, devices + n_devices);
+  else
+    devs.push_back(cur);
+  int count = 0;
+  ck(cudaGetDeviceCount(&count), "cudaGetDeviceCount");
+  for (int d : devs)
+    if (d < 0 || d >= count) throw std::invalid_argument("device ordinal " + std::to_string(d) + " out of range");
+  const int G = (int)devs.size();
+
+  const size_t sz = real_size(spec.precision);
+  const size_t in_row = (size_t)h.n_in * sz;
+  const size_t p_cfg = (size_t)h.n_out * sz;                  // bytes per configuration in one P column
+  const size_t j_cfg = (size_t)h.n_out * h.pose_dim * sz;     // bytes per configuration in one J column
+  const size_t out_cfg = p_cfg * h.pose_dim + (jac ? j_cfg * h.n_out_cols : 0);
+  // chunk: ~48 MB of output per slot, a whole number of tiles, at least one full wave of tiles
+  int64_t chunk = (int64_t)((size_t(48) << 20) / std::max<size_t>(out_cfg, 1));
+  chunk = std::max<int64_t>(chunk, 8192);
+  chunk = (chunk + TFK_TILE - 1) / TFK_TILE * TFK_TILE;
+
+  const int64_t per_dev = (n + G - 1) / G;
+  struct Slice {
+    int64_t begin, end, next;
+  };
+  std::vector<Slice> sl(G);
+  for (int g = 0; g < G; ++g) {
+    sl[g].begin = std::min<int64_t>(n, (int64_t)g * per_dev);
+    sl[g].end = std::min<int64_t>(n, (int64_t)(g + 1) * per_dev);
+    sl[g].next = sl[g].begin;
+  }
+  const char *qb = static_cast<const char *>(q);
+  char *Pb = static_cast<char *>(P);
+  char *Jb = static_cast<char *>(J);
+
+  try {
+    bool work = true;
+    for (int64_t k = 0; work; ++k) {
+      work = false;
+      for (int g = 0; g < G; ++g) {
+        if (sl[g].next >= sl[g].end) continue;
+        work = true;
+        const int64_t r0 = sl[g].next;
+        const int64_t nc = std::min<int64_t>(chunk, sl[g].end - r0);
+        sl[g].next += nc;
+        const int dev = devs[g];
+        ck(cudaSetDevice(dev), "cudaSetDevice");
+        HostPipe &pp = pipe(dev);
+        const int s = (int)(k & 1);
+        cudaStream_t st = pp.stream[s];
+        const int64_t capn = std::min<int64_t>(chunk, per_dev); // size once for a full chunk
+        grow(&pp.dq[s], &pp.cap_q[s], std::max<size_t>((size_t)capn * in_row, 16), st);
+        grow(&pp.dP[s], &pp.cap_P[s], (size_t)capn * p_cfg * h.pose_dim, st);
+        if (jac) grow(&pp.dJ[s], &pp.cap_J[s], (size_t)capn * j_cfg * h.n_out_cols, st);
+
+        if (in_row)
+          ck(cudaMemcpyAsync(pp.dq[s], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st),
+             "cudaMemcpyAsync(q)");
+        launch(dev, st, e, spec.precision, pp.dq[s], nc, pp.dP[s], jac ? pp.dJ[s] : nullptr, nc, 0);
+        // one contiguous run per output column (column-major destination dimensioned for all n)
+        for (int d = 0; d < h.pose_dim; ++d)
+          ck(cudaMemcpyAsync(Pb + ((size_t)d * n + r0) * p_cfg, static_cast<char *>(pp.dP[s]) + (size_t)d * nc * p_cfg,
+                             (size_t)nc * p_cfg, cudaMemcpyDeviceToHost, st),
+             "cudaMemcpyAsync(P)");
+        if (jac)
+          for (int c = 0; c < h.n_out_cols; ++c)
+            ck(cudaMemcpyAsync(Jb + ((size_t)c * n + r0) * j_cfg, static_cast<char *>(pp.dJ[s]) + (size_t)c * nc * j_cfg,
+                               (size_t)nc * j_cfg, cudaMemcpyDeviceToHost, st),
+               "cudaMemcpyAsync(J)");
+      }
+    }
+    for (int g = 0; g < G; ++g) {
+      ck(cudaSetDevice(devs[g]), "cudaSetDevice");
+      HostPipe &pp = pipe(devs[g]);
+      ck(cudaStreamSynchronize(pp.stream[0]), "cudaStreamSynchronize");
+      ck(cudaStreamSynchronize(pp.stream[1]), "cudaStreamSynchronize");
+    }
+  } catch (...) {
+    cudaSetDevice(cur);
+    throw;
+  }
+  cudaSetDevice(cur);
+
+  // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:85-89)
+  std::vector<size_t> ids(spec.joint_ids, spec.joint_ids + spec.n_joint);
+  std::vector<double> last((size_t)h.n_in);
+  for (int c = 0; c < h.n_in; ++c)
+    last[c] = spec.precision == PREC_F32 ? (double)reinterpret_cast<const float *>(qb)[(size_t)(n - 1) * h.n_in + c]
+                                         : reinterpret_cast<const double *>(qb)[(size_t)(n - 1) * h.n_in + c];
+  if (spec.n_joint > 0) model.set_joint_angles(ids, std::vector<double>(last.begin(), last.begin() + spec.n_joint));
+  if (h.base_type == BASE_PLANER) {
+    const double b[6] = {last[spec.n_joint], last[spec.n_joint + 1], 0.0, 0.0, 0.0, last[spec.n_joint + 2]};
+    model.set_base_pose_xyzrpy(b);
+  } else if (h.base_type == BASE_FLOATING) {
+    model.set_base_pose_xyzrpy(&last[spec.n_joint]);
+  }
+}
+
+} // namespace tfk

@@ -1,0 +1,94 @@
+// engine.hpp -- host runtime around the batch kernel: plan cache, per-device workspaces, the chunked
+// host<->device pipeline and the contiguous multi-GPU split.  Replaces the sequential, stateful batch
+// loop of the reference (src/wrapper.cpp:84-122).  No CPU compute path exists here: without a CUDA
+// device every solve fails with TFK_ERR_CUDA.
+#ifndef TFK_ENGINE_HPP
+#define TFK_ENGINE_HPP
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "fk_launch.h"
+#include "model.hpp"
+#include "plan.hpp"
+
+namespace tfk {
+
+struct CudaError : std::runtime_error {
+  explicit CudaError(const std::string &w) : std::runtime_error(w) {}
+};
+
+struct SolveSpec {
+  const int *elink_ids;
+  int n_link;
+  const int *joint_ids;
+  int n_joint;
+  int rot_type, base_type, with_jacobian, precision;
+};
+
+struct LaunchInfo {
+  int grid, block, smem_bytes, blocks_per_sm, rec_reals;
+};
+
+class Engine {
+public:
+  Engine(const std::string &xml, HostLibm libm);
+  ~Engine();
+
+  KinematicModel model;
+  std::mutex mu; // the C ABI serialises calls per model handle
+
+  void solve_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec, void *d_P,
+                    void *d_J, int64_t ld_cfg, int64_t row0);
+  void solve_host(const void *q, int64_t n, const SolveSpec &spec, const int *devices, int n_devices, void *P, void *J);
+  LaunchInfo last_launch;
+
+private:
+  struct PlanEntry {
+    PlanKey key;
+    std::vector<unsigned char> blob;
+    std::map<int, unsigned char *> on_device; // device ordinal -> uploaded copy
+  };
+  struct Workspace { // one per (device, stream): concurrent launches never share records
+    void *scratch;
+    size_t scratch_bytes;
+  };
+  struct HostPipe { // per device: two slots of staging buffers, one stream each
+    cudaStream_t stream[2];
+    void *dq[2], *dP[2], *dJ[2];
+    size_t cap_q[2], cap_P[2], cap_J[2];
+    bool ready;
+  };
+
+  PlanEntry &plan_for(const SolveSpec &spec);
+  const unsigned char *plan_on_device(PlanEntry &e, int device, cudaStream_t stream);
+  Workspace &workspace(int device, cudaStream_t stream, size_t bytes);
+  HostPipe &pipe(int device);
+  int sm_count(int device);
+  void launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n, void *d_P,
+              void *d_J, int64_t ld_cfg, int64_t row0);
+  void release_device_memory();
+
+  std::vector<std::unique_ptr<PlanEntry>> plans_;
+  std::map<std::pair<int, cudaStream_t>, Workspace> workspaces_;
+  std::map<int, HostPipe> pipes_;
+  std::map<int, int> sm_counts_;
+  std::map<std::pair<int, int>, int> occupancy_; // (precision, smem bytes rounded) -> blocks per SM
+};
+
+int64_t kernel_launch_count();
+
+// pooled pinned host memory
+void *pinned_alloc(size_t bytes);
+void pinned_free(void *p);
+
+} // namespace tfk
+#endif

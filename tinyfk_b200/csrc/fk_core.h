@@ -230,3 +230,180 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       }
     }
   }
+
+  // ---------------------------------------------------------------------------------------------
+  // One (configuration, requested link) pair.  row = global configuration index (row0 + i) used for
+  // addressing; o = index into elink_ids.  Outputs are column-major exactly as the reference hands
+  // them to numpy (src/wrapper.cpp:80-82,123):  P[d * ldP + row*n_out + o],
+  // J[c * ldJ + (row*n_out + o)*pose_dim + r]  with ldP = N*n_out, ldJ = ldP*pose_dim.
+  static TFK_FN void phase_b(const PlanView &pv, const T *rec, int stride, long long row, int o, T *Pout,
+                             T *Jout, long long ldP, long long ldJ) {
+    const PlanHeader &h = *pv.h;
+    const int lat = h.off_lrec + pv.lrec_of_out[o] * h.lrec_size;
+    P e;
+    e.p = get_vec(rec, stride, lat);
+    e.q = O::qidentity();
+    if (h.lrec_size == 7) {
+      e.q.x = rec[(lat + 3) * stride];
+      e.q.y = rec[(lat + 4) * stride];
+      e.q.z = rec[(lat + 5) * stride];
+      e.q.w = rec[(lat + 6) * stride];
+    }
+    const long long head = row * h.n_out + o;
+    Pout[0 * ldP + head] = e.p.x; // src/wrapper.cpp:98-100
+    Pout[1 * ldP + head] = e.p.y;
+    Pout[2 * ldP + head] = e.p.z;
+    V erpy;
+    erpy.x = erpy.y = erpy.z = T(0);
+    if (h.rot_type == 1) { // src/wrapper.cpp:101-106
+      erpy = O::to_rpy(e.q);
+      Pout[3 * ldP + head] = erpy.x;
+      Pout[4 * ldP + head] = erpy.y;
+      Pout[5 * ldP + head] = erpy.z;
+    } else if (h.rot_type == 2) { // src/wrapper.cpp:107-112
+      Pout[3 * ldP + head] = e.q.x;
+      Pout[4 * ldP + head] = e.q.y;
+      Pout[5 * ldP + head] = e.q.z;
+      Pout[6 * ldP + head] = e.q.w;
+    }
+    if (!h.with_jacobian) return;
+
+    const int D = h.pose_dim;
+    T *Jrow = Jout + head * D;
+    typename O::RpyCoef coef;
+    Q einv = O::qidentity();
+    if (h.rot_type == 1) coef = O::rpy_coef(erpy);   // src/kinematics.cpp:121-123 + :14-21
+    if (h.rot_type == 2) einv = O::qinverse(e.q);    // src/kinematics.cpp:124-126
+
+    // joint columns, src/kinematics.cpp:131-180
+    const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
+    for (int c = 0; c < h.n_cols; ++c) {
+      T *Jc = Jrow + (long long)c * ldJ;
+      const bool relevant = (mask[c >> 5] >> (c & 31)) & 1u;
+      if (!relevant) {
+        for (int r = 0; r < D; ++r) Jc[r] = T(0);
+        continue;
+      }
+      const int jat = h.off_jrec + 6 * pv.cols[c].jrec;
+      const V aw = get_vec(rec, stride, jat);
+      if (pv.cols[c].prismatic) {
+        Jc[0] = aw.x;
+        Jc[1] = aw.y;
+        Jc[2] = aw.z;
+        for (int r = 3; r < D; ++r) Jc[r] = T(0);
+        continue;
+      }
+      const V cp = get_vec(rec, stride, jat + 3);
+      V d;
+      d.x = e.p.x - cp.x;
+      d.y = e.p.y - cp.y;
+      d.z = e.p.z - cp.z;
+      const V dpos = O::cross(aw, d);
+      Jc[0] = dpos.x;
+      Jc[1] = dpos.y;
+      Jc[2] = dpos.z;
+      if (h.rot_type == 1) {
+        const V dr = O::rpy_derivative(coef, aw);
+        Jc[3] = dr.x;
+        Jc[4] = dr.y;
+        Jc[5] = dr.z;
+      } else if (h.rot_type == 2) {
+        const Q dq = O::q_derivative(einv, aw);
+        Jc[3] = dq.x;
+        Jc[4] = dq.y;
+        Jc[5] = dq.z;
+        Jc[6] = dq.w;
+      }
+    }
+
+    if (h.base_type == 0) return;
+    // base translation columns, src/kinematics.cpp:194-196
+    const int n_trans = (h.base_type == 1) ? 2 : 3;
+    for (int k = 0; k < n_trans; ++k) {
+      T *Jc = Jrow + (long long)(h.n_cols + k) * ldJ;
+      for (int r = 0; r < D; ++r) Jc[r] = (r == k) ? T(1) : T(0);
+    }
+    // base rotation columns: FLOATING keeps roll, pitch, yaw; PLANER keeps yaw only
+    const P base = get_pose(rec, stride, h.off_base);
+    const int k0 = (h.base_type == 1) ? 2 : 0;
+    if (ANALYTIC_BASE) {
+      V d;
+      d.x = e.p.x - base.p.x;
+      d.y = e.p.y - base.p.y;
+      d.z = e.p.z - base.p.z;
+      for (int k = k0; k < 3; ++k) {
+        T *Jc = Jrow + (long long)(h.n_cols + n_trans + (k - k0)) * ldJ;
+        const V w = get_vec(rec, stride, h.off_base + 7 + 3 * k);
+        const V dpos = O::cross(w, d);
+        Jc[0] = dpos.x;
+        Jc[1] = dpos.y;
+        Jc[2] = dpos.z;
+        if (h.rot_type == 1) {
+          const V dr = O::rpy_derivative(coef, w);
+          Jc[3] = dr.x;
+          Jc[4] = dr.y;
+          Jc[5] = dr.z;
+        } else if (h.rot_type == 2) {
+          const Q dq = O::q_derivative(einv, w);
+          Jc[3] = dq.x;
+          Jc[4] = dq.y;
+          Jc[5] = dq.z;
+          Jc[6] = dq.w;
+        }
+      }
+      return;
+    }
+    // forward finite difference replica, src/kinematics.cpp:182-232
+    const T eps = T(1e-7);
+    const P binv = get_pose(rec, stride, h.off_base + 7);
+    P be; // tf_blink_to_elink = pose_transform(tf_blink_to_rlink, tf_rlink_to_elink)
+    if (h.lrec_size == 7) {
+      be = O::compose(binv, e);
+    } else { // IGNORE: only the position rows exist and they never read the link rotation
+      const V r = O::rotate(binv.q, e.p);
+      be.p.x = r.x + binv.p.x;
+      be.p.y = r.y + binv.p.y;
+      be.p.z = r.z + binv.p.z;
+      be.q = O::qidentity();
+    }
+    for (int k = k0; k < 3; ++k) {
+      T *Jc = Jrow + (long long)(h.n_cols + n_trans + (k - k0)) * ldJ;
+      const int at = h.off_base + 14 + 4 * k;
+      P bk;
+      bk.p = base.p;
+      bk.q.x = rec[(at + 0) * stride];
+      bk.q.y = rec[(at + 1) * stride];
+      bk.q.z = rec[(at + 2) * stride];
+      bk.q.w = rec[(at + 3) * stride];
+      V pk;
+      Q qk = O::qidentity();
+      if (h.lrec_size == 7) {
+        const P t = O::compose(bk, be);
+        pk = t.p;
+        qk = t.q;
+      } else {
+        const V r = O::rotate(bk.q, be.p);
+        pk.x = r.x + bk.p.x;
+        pk.y = r.y + bk.p.y;
+        pk.z = r.z + bk.p.z;
+      }
+      Jc[0] = (pk.x - e.p.x) / eps;
+      Jc[1] = (pk.y - e.p.y) / eps;
+      Jc[2] = (pk.z - e.p.z) / eps;
+      if (h.rot_type == 1) {
+        const V rk = O::to_rpy(qk);
+        Jc[3] = (rk.x - erpy.x) / eps;
+        Jc[4] = (rk.y - erpy.y) / eps;
+        Jc[5] = (rk.z - erpy.z) / eps;
+      } else if (h.rot_type == 2) {
+        Jc[3] = (qk.x - e.q.x) / eps;
+        Jc[4] = (qk.y - e.q.y) / eps;
+        Jc[5] = (qk.z - e.q.z) / eps;
+        Jc[6] = (qk.w - e.q.w) / eps;
+      }
+    }
+  }
+};
+
+} // namespace tfk
+#endif

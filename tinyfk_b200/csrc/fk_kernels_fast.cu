@@ -1,0 +1,15 @@
+// fk_kernels_fast.cu -- opt-in FP32 mode (FMA contraction on, libdevice libm, analytic base-rotation
+// columns: the reference's eps = 1e-7 forward difference is below one FP32 ulp).  Tolerance vs the
+// reference: 1e-5 (BASELINE.json north_star).
+#include "fk_kernels.cuh"
+
+namespace tfk {
+typedef FkCore<MathNative32, true> CoreF32;
+
+cudaError_t launch_fk_f32(const KernelArgs &a, int grid, cudaStream_t stream) {
+  return launch_fk<CoreF32>(a, grid, stream);
+}
+cudaError_t occupancy_fk_f32(int plan_bytes, int *blocks_per_sm) {
+  return occupancy_fk<CoreF32>(plan_bytes, blocks_per_sm);
+}
+} // namespace tfk

@@ -1,0 +1,15 @@
+// fk_kernels_strict.cu -- FP64 "strict" instantiation.  MUST be compiled with -fmad=false: every
+// multiply and add rounds separately, as in the reference's x86-64 build (CMakeLists.txt:3-14 has no
+// -march/-ffast-math, so no FMA contraction).  libm = fkmath.h, shared bit for bit with the host.
+#include "fk_kernels.cuh"
+
+namespace tfk {
+typedef FkCore<MathPortable, false> CoreStrict64;
+
+cudaError_t launch_fk_f64_strict(const KernelArgs &a, int grid, cudaStream_t stream) {
+  return launch_fk<CoreStrict64>(a, grid, stream);
+}
+cudaError_t occupancy_fk_f64_strict(int plan_bytes, int *blocks_per_sm) {
+  return occupancy_fk<CoreStrict64>(plan_bytes, blocks_per_sm);
+}
+} // namespace tfk

@@ -1,0 +1,235 @@
+// wrapper.cpp -- pybind11 module `_tinyfk`: the reference's Python-visible class RobotModel
+// (reference src/wrapper.cpp:246-283), re-exported on top of the C ABI (include/tinyfk_b200.h).
+// numpy in / numpy out, no PyTorch.  Method names, argument order and error types follow the
+// reference; everything numerical happens behind tfk_solve_fk_host (CUDA, no CPU fallback).
+//
+// Out of scope here ("next"): solve_com_forward_kinematics,
+// compute_total_inertia_matrix, compute_inter_link_squared_dists -- they raise NotImplementedError.
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <array>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/tinyfk_b200.h"
+
+namespace py = pybind11;
+
+namespace {
+
+enum class RotationType { IGNORE = 0, RPY = 1, XYZW = 2 };
+
+[[noreturn]] void raise_for(int rc) {
+  const std::string msg = tfk_last_error();
+  if (rc == TFK_ERR_INVALID) throw std::invalid_argument(msg); // -> ValueError, as the reference
+  throw std::runtime_error(msg);                               // -> RuntimeError
+}
+inline void check(int rc) {
+  if (rc != TFK_OK) raise_for(rc);
+}
+
+std::vector<int> to_int(const std::vector<size_t> &v) { return std::vector<int>(v.begin(), v.end()); }
+
+// numpy array backed by pooled pinned memory (device->host copies land in it at full PCIe speed)
+template <class T> py::array_t<T, py::array::f_style> pinned_array(size_t rows, size_t cols, bool pinned) {
+  const size_t bytes = rows * cols * sizeof(T);
+  if (!pinned || bytes == 0) return py::array_t<T, py::array::f_style>({rows, cols});
+  void *p = nullptr;
+  check(tfk_host_alloc(bytes, &p));
+  py::capsule owner(p, [](void *q) { tfk_host_free(q); });
+  return py::array_t<T, py::array::f_style>({rows, cols}, {sizeof(T), sizeof(T) * rows}, static_cast<T *>(p), owner);
+}
+
+class RobotModel {
+public:
+  explicit RobotModel(const std::string &xml, int host_libm = TFK_LIBM_PORTABLE) : m_(nullptr) {
+    check(tfk_model_create(xml.data(), xml.size(), host_libm, &m_));
+  }
+  ~RobotModel() { tfk_model_destroy(m_); }
+  RobotModel(const RobotModel &) = delete;
+  RobotModel &operator=(const RobotModel &) = delete;
+
+  double total_mass() const { return tfk_total_mass(m_); }
+  std::string get_root_link_name() const { return tfk_link_name(m_, tfk_root_link_id(m_)); }
+
+  std::vector<std::string> get_joint_names() const {
+    std::vector<std::string> v;
+    for (int i = 0; i < tfk_num_joints(m_); ++i) v.push_back(tfk_joint_name(m_, i));
+    return v;
+  }
+  std::vector<std::string> get_link_names() const {
+    std::vector<std::string> v;
+    for (int i = 0; i < tfk_num_links(m_); ++i) v.push_back(tfk_link_name(m_, i));
+    return v;
+  }
+  std::vector<size_t> get_joint_ids(const std::vector<std::string> &names) const {
+    std::vector<const char *> c;
+    for (auto &s : names) c.push_back(s.c_str());
+    std::vector<int> ids(names.size());
+    check(tfk_get_joint_ids(m_, c.data(), (int)c.size(), ids.data()));
+    return std::vector<size_t>(ids.begin(), ids.end());
+  }
+  std::vector<size_t> get_link_ids(const std::vector<std::string> &names) const {
+    std::vector<const char *> c;
+    for (auto &s : names) c.push_back(s.c_str());
+    std::vector<int> ids(names.size());
+    check(tfk_get_link_ids(m_, c.data(), (int)c.size(), ids.data()));
+    return std::vector<size_t>(ids.begin(), ids.end());
+  }
+  std::vector<std::pair<double, double>> get_joint_limits(const std::vector<size_t> &ids) const {
+    std::vector<int> i = to_int(ids);
+    std::vector<double> lo(i.size()), hi(i.size());
+    check(tfk_get_joint_limits(m_, i.data(), (int)i.size(), lo.data(), hi.data()));
+    std::vector<std::pair<double, double>> out;
+    for (size_t k = 0; k < i.size(); ++k) out.emplace_back(lo[k], hi[k]);
+    return out;
+  }
+  std::vector<double> get_joint_angles(const std::vector<size_t> &ids) const {
+    std::vector<int> i = to_int(ids);
+    std::vector<double> a(i.size());
+    check(tfk_get_joint_angles(m_, i.data(), (int)i.size(), a.data()));
+    return a;
+  }
+  void set_joint_angles(const std::vector<size_t> &ids, const std::vector<double> &angles) {
+    if (ids.size() != angles.size()) throw std::invalid_argument("joint id / angle count mismatch");
+    std::vector<int> i = to_int(ids);
+    check(tfk_set_joint_angles(m_, i.data(), (int)i.size(), angles.data()));
+  }
+  std::vector<double> get_base_pose() const {
+    std::vector<double> b(6);
+    check(tfk_get_base_pose(m_, b.data()));
+    return b;
+  }
+  void set_base_pose(const std::vector<double> &xyzrpy) {
+    if (xyzrpy.size() != 6) throw std::invalid_argument("argument must have size 6"); // src/wrapper.cpp:38-40
+    check(tfk_set_base_pose(m_, xyzrpy.data()));
+  }
+  void add_new_link(const std::string &name, size_t parent_id, std::array<double, 3> pos, std::array<double, 3> rpy) {
+    check(tfk_add_new_link(m_, name.c_str(), (int)parent_id, pos.data(), rpy.data(), nullptr));
+  }
+  bool is_relevant(size_t link_id, size_t joint_id) const {
+    int r = 0;
+    check(tfk_is_relevant(m_, (int)link_id, (int)joint_id, &r));
+    return r != 0;
+  }
+  void clear_cache() {} // there is no transform cache to clear: every batch is computed from its inputs
+
+  // The new batched overload: qs is an (N, n_dof) ndarray; base_type 0/1/2; returns (P, J) F-ordered
+  // exactly like the reference.  J is all zeros (lazily allocated) when with_jacobian is false, as
+  // src/wrapper.cpp:81-82 returns it.
+  py::tuple solve_batch(py::array qs_in, const std::vector<size_t> &elink_ids, const std::vector<size_t> &joint_ids,
+                        int rot_type, int base_type, bool with_jacobian, int precision, const std::vector<int> &devices,
+                        bool pinned_output) {
+    if (rot_type < 0 || rot_type > 2) throw std::invalid_argument("bad rot_type");
+    if (base_type < 0 || base_type > 2) throw std::invalid_argument("bad base_type");
+    const int pose_dim = 3 + (rot_type == 1) * 3 + (rot_type == 2) * 4;
+    const size_t n_in = joint_ids.size() + (base_type == 1 ? 3 : (base_type == 2 ? 6 : 0));
+    std::vector<int> l = to_int(elink_ids), j = to_int(joint_ids);
+    if (precision == TFK_F32)
+      return run<float>(py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(qs_in), l, j, rot_type,
+                        base_type, with_jacobian, precision, devices, pinned_output, pose_dim, n_in);
+    return run<double>(py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(qs_in), l, j, rot_type,
+                       base_type, with_jacobian, precision, devices, pinned_output, pose_dim, n_in);
+  }
+
+  // The reference's 7-argument entry (src/wrapper.cpp:60-124): with_base means the 6-D floating base.
+  py::tuple solve_forward_kinematics(py::array qs, const std::vector<size_t> &elink_ids,
+                                     const std::vector<size_t> &joint_ids, RotationType rot_type, bool with_base,
+                                     bool with_jacobian, bool /*use_cache: no cache exists*/) {
+    py::array_t<double, py::array::c_style | py::array::forcecast> a =
+        py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(qs);
+    if (!a) throw std::invalid_argument("joint_angles_sequence must be a sequence of float sequences");
+    if (with_base && a.ndim() == 2 && (size_t)a.shape(1) != joint_ids.size() + 6)
+      throw std::invalid_argument("dof mismatch!! Probably you forget base's (x, y, theta)"); // src/wrapper.cpp:74-78
+    return solve_batch(a, elink_ids, joint_ids, (int)rot_type, with_base ? TFK_BASE_FLOATING : TFK_BASE_FIXED,
+                       with_jacobian, TFK_F64_STRICT, {}, true);
+  }
+
+  int64_t kernel_launches() const { return tfk_kernel_launch_count(); }
+
+private:
+  template <class T>
+  py::tuple run(py::array_t<T, py::array::c_style | py::array::forcecast> qs, const std::vector<int> &l,
+                const std::vector<int> &j, int rot_type, int base_type, bool with_jacobian, int precision,
+                const std::vector<int> &devices, bool pinned_output, int pose_dim, size_t n_in) {
+    if (!qs) throw std::invalid_argument("qs must be convertible to a 2-D float array");
+    if (qs.ndim() != 2) throw std::invalid_argument("qs must be 2-D (n_configs, n_dof)");
+    if ((size_t)qs.shape(1) != n_in)
+      throw std::invalid_argument("dof mismatch: expected " + std::to_string(n_in) + " columns, got " +
+                                  std::to_string(qs.shape(1)));
+    const size_t n = (size_t)qs.shape(0);
+    const size_t rowsP = n * l.size();
+    auto P = pinned_array<T>(rowsP, (size_t)pose_dim, pinned_output);
+    py::array_t<T, py::array::f_style> J;
+    void *Jp = nullptr;
+    if (with_jacobian) {
+      J = pinned_array<T>(rowsP * pose_dim, n_in, pinned_output);
+      Jp = J.mutable_data();
+    }
+    int rc;
+    {
+      py::gil_scoped_release nogil;
+      rc = tfk_solve_fk_host(m_, qs.data(), (int64_t)n, l.data(), (int)l.size(), j.data(), (int)j.size(), rot_type,
+                             base_type, with_jacobian ? 1 : 0, precision, devices.empty() ? nullptr : devices.data(),
+                             (int)devices.size(), P.mutable_data(), Jp);
+    }
+    check(rc);
+    if (!with_jacobian) {
+      // zeros of the full shape (calloc-backed: no pages are touched until someone reads them)
+      py::object zeros = py::module_::import("numpy").attr("zeros")(
+          py::make_tuple(rowsP * pose_dim, n_in), py::arg("dtype") = py::dtype::of<T>(), py::arg("order") = "F");
+      return py::make_tuple(P, zeros);
+    }
+    return py::make_tuple(P, J);
+  }
+
+  tfk_model *m_;
+};
+
+[[noreturn]] void not_on_path(const char *what) {
+  PyErr_SetString(PyExc_NotImplementedError,
+                  (std::string(what) + " is outside the accelerated FK path (see DESIGN.md, 'out of scope')").c_str());
+  throw py::error_already_set();
+}
+
+} // namespace
+
+PYBIND11_MODULE(_tinyfk, m) {
+  m.doc() = "B200-native batched forward kinematics behind tinyfk's RobotModel interface";
+
+  py::enum_<RotationType>(m, "RotationType")
+      .value("IGNORE", RotationType::IGNORE)
+      .value("RPY", RotationType::RPY)
+      .value("XYZW", RotationType::XYZW);
+
+  py::class_<RobotModel>(m, "RobotModel")
+      .def(py::init<const std::string &, int>(), py::arg("xml"), py::arg("host_libm") = (int)TFK_LIBM_PORTABLE)
+      .def_property_readonly("total_mass_", &RobotModel::total_mass)
+      .def("get_root_link_name", &RobotModel::get_root_link_name)
+      .def("solve_forward_kinematics", &RobotModel::solve_forward_kinematics)
+      .def("solve_forward_kinematics_batch", &RobotModel::solve_batch, py::arg("qs"), py::arg("elink_ids"),
+           py::arg("joint_ids"), py::arg("rot_type"), py::arg("base_type"), py::arg("with_jacobian"),
+           py::arg("precision") = (int)TFK_F64_STRICT, py::arg("devices") = std::vector<int>(),
+           py::arg("pinned_output") = true)
+      .def("get_joint_angles", &RobotModel::get_joint_angles)
+      .def("set_joint_angles", &RobotModel::set_joint_angles)
+      .def("solve_com_forward_kinematics", [](RobotModel &, py::args, py::kwargs) { not_on_path("solve_com_forward_kinematics"); })
+      .def("compute_total_inertia_matrix", [](RobotModel &, py::args, py::kwargs) { not_on_path("compute_total_inertia_matrix"); })
+      .def("get_joint_names", &RobotModel::get_joint_names)
+      .def("get_joint_ids", &RobotModel::get_joint_ids)
+      .def("get_joint_limits", &RobotModel::get_joint_limits)
+      .def("get_base_pose", &RobotModel::get_base_pose)
+      .def("set_base_pose", &RobotModel::set_base_pose)
+      .def("get_link_ids", &RobotModel::get_link_ids)
+      .def("get_link_names", &RobotModel::get_link_names)
+      .def("add_new_link", &RobotModel::add_new_link)
+      .def("compute_inter_link_squared_dists", [](RobotModel &, py::args, py::kwargs) { not_on_path("compute_inter_link_squared_dists"); })
+      .def("is_relevant", &RobotModel::is_relevant)
+      .def("kernel_launches", &RobotModel::kernel_launches)
+      .def("clear_cache", &RobotModel::clear_cache);
+}
