@@ -76,6 +76,11 @@ TFK_API int tfk_get_joint_limits(const tfk_model *m, const int *joint_ids, int n
 /* get_joint_velocity_limits / get_joint_effort_limits, src/tinyfk.cpp:181-201 */
 TFK_API int tfk_get_joint_velocity_limits(const tfk_model *m, const int *joint_ids, int n, double *out);
 TFK_API int tfk_get_joint_effort_limits(const tfk_model *m, const int *joint_ids, int n, double *out);
+/* Parsed tree as the reference holds it per link (urdf::Link / urdf::Joint, link.h:195-220, joint.h:174-199):
+ * parent link id (-1 root), type code of the parent joint (urdf::Joint enum: 1 REVOLUTE 2 CONTINUOUS
+ * 3 PRISMATIC 6 FIXED, 0 for the root), movable-joint id (-1 if fixed), axis[3], origin x y z qx qy qz qw. */
+TFK_API int tfk_link_info(const tfk_model *m, int link_id, int *parent, int *jtype, int *jid, double axis[3],
+                          double origin[7]);
 /* rptable_.isRelevant(link, joint), include/tinyfk.hpp:43; writes 0/1 */
 TFK_API int tfk_is_relevant(const tfk_model *m, int link_id, int joint_id, int *out);
 

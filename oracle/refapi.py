@@ -238,3 +238,69 @@ class RefModel:
             axis[i], origin[i] = a, o
         return dict(parent=parent, jtype=jtype, jid=jid, axis=axis, origin=origin, n_joints=self.n_joints,
                     root=self.root_link_id)
+
+
+_port_libs = {}
+
+
+def _load_port(strict):
+    if strict in _port_libs:
+        return _port_libs[strict]
+    if not os.path.exists(port_lib_path(strict)):
+        build_port()
+    lib = ctypes.CDLL(port_lib_path(strict))
+    lib.fko_create.restype = ctypes.c_void_p
+    lib.fko_create.argtypes = [ctypes.c_int, ctypes.c_int, _ip, _ip, _ip, _dp, _dp, ctypes.c_int]
+    lib.fko_destroy.argtypes = [ctypes.c_void_p]
+    lib.fko_set_joint_angles.argtypes = [ctypes.c_void_p, _ip, ctypes.c_int, _dp]
+    lib.fko_set_base_pose.argtypes = [ctypes.c_void_p, _dp]
+    lib.fko_solve_fk.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, ctypes.c_int,
+                                 ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp]
+    _port_libs[strict] = lib
+    return lib
+
+
+class PortModel:
+    """oracle/fk_oracle.c (plain-C restatement) driven by a link table:
+    dict(parent, jtype, jid, axis[n,3], origin[n,7], n_joints, root) -- see RefModel.export_table()."""
+
+    def __init__(self, table, strict=False):
+        self._lib = _load_port(strict)
+        self.strict = strict
+        parent = _as_int_array(table["parent"])
+        jtype = _as_int_array(table["jtype"])
+        jid = _as_int_array(table["jid"])
+        axis = np.ascontiguousarray(table["axis"], dtype=np.float64)
+        origin = np.ascontiguousarray(table["origin"], dtype=np.float64)
+        self._h = self._lib.fko_create(parent.size, int(table["n_joints"]), parent.ctypes.data_as(_ip),
+                                       jtype.ctypes.data_as(_ip), jid.ctypes.data_as(_ip), axis.ctypes.data_as(_dp),
+                                       origin.ctypes.data_as(_dp), int(table["root"]))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.fko_destroy(self._h)
+            self._h = None
+
+    def set_joint_angles(self, joint_ids, angles):
+        ids = _as_int_array(joint_ids)
+        a = np.ascontiguousarray(angles, dtype=np.float64)
+        self._lib.fko_set_joint_angles(self._h, ids.ctypes.data_as(_ip), ids.size, a.ctypes.data_as(_dp))
+
+    def set_base_pose(self, xyzrpy):
+        a = np.ascontiguousarray(xyzrpy, dtype=np.float64)
+        self._lib.fko_set_base_pose(self._h, a.ctypes.data_as(_dp))
+
+    def solve_fk(self, qs, elink_ids, joint_ids, rot_type=0, base_type=0, with_jacobian=False, use_cache=False):
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        lids = _as_int_array(elink_ids)
+        jids = _as_int_array(joint_ids)
+        n_wp, n_in = qs.shape
+        assert n_in == jids.size + base_dof(base_type)
+        pd = pose_dim(rot_type)
+        P = np.zeros((n_wp * lids.size, pd), order="F")
+        J = np.zeros((n_wp * lids.size * pd, n_in), order="F")
+        self._lib.fko_solve_fk(self._h, qs.ctypes.data_as(_dp), n_wp, lids.ctypes.data_as(_ip), lids.size,
+                               jids.ctypes.data_as(_ip), jids.size, int(rot_type), int(base_type),
+                               int(bool(with_jacobian)), P.ctypes.data_as(_dp),
+                               J.ctypes.data_as(_dp) if with_jacobian else None)
+        return P, J

@@ -19,7 +19,7 @@ SYMBOLS = [
     "tfk_last_error", "tfk_model_create", "tfk_model_destroy", "tfk_num_links", "tfk_num_joints",
     "tfk_root_link_id", "tfk_total_mass", "tfk_link_name", "tfk_joint_name", "tfk_get_link_ids",
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
-    "tfk_get_joint_effort_limits", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
+    "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
     "tfk_solve_fk_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_version",
@@ -52,6 +52,7 @@ def lib():
     L.tfk_get_joint_limits.argtypes = [_vp, _ip, ctypes.c_int, _dp, _dp]
     L.tfk_get_joint_velocity_limits.argtypes = [_vp, _ip, ctypes.c_int, _dp]
     L.tfk_get_joint_effort_limits.argtypes = [_vp, _ip, ctypes.c_int, _dp]
+    L.tfk_link_info.argtypes = [_vp, ctypes.c_int, _ip, _ip, _ip, _dp, _dp]
     L.tfk_is_relevant.argtypes = [_vp, ctypes.c_int, ctypes.c_int, _ip]
     L.tfk_set_joint_angles.argtypes = [_vp, _ip, ctypes.c_int, _dp]
     L.tfk_get_joint_angles.argtypes = [_vp, _ip, ctypes.c_int, _dp]
@@ -162,6 +163,22 @@ class Model:
         _check(self._L.tfk_get_joint_limits(self._h, ids.ctypes.data_as(_ip), ids.size, lo.ctypes.data_as(_dp),
                                             hi.ctypes.data_as(_dp)))
         return list(zip(lo.tolist(), hi.tolist()))
+
+    def link_info(self, link_id):
+        p, t, j = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        axis, origin = np.zeros(3), np.zeros(7)
+        _check(self._L.tfk_link_info(self._h, int(link_id), ctypes.byref(p), ctypes.byref(t), ctypes.byref(j),
+                                     axis.ctypes.data_as(_dp), origin.ctypes.data_as(_dp)))
+        return p.value, t.value, j.value, axis, origin
+
+    def export_table(self):
+        """Link table in the layout oracle/fk_oracle.h takes (test use)."""
+        n = self.n_links
+        info = [self.link_info(i) for i in range(n)]
+        return dict(parent=np.array([x[0] for x in info], dtype=np.int32),
+                    jtype=np.array([x[1] for x in info], dtype=np.int32),
+                    jid=np.array([x[2] for x in info], dtype=np.int32), axis=np.array([x[3] for x in info]),
+                    origin=np.array([x[4] for x in info]), n_joints=self.n_joints, root=self.root_link_id)
 
     def is_relevant(self, link_id, joint_id):
         r = ctypes.c_int()

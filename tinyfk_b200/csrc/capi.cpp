@@ -127,6 +127,21 @@ int tfk_get_joint_effort_limits(const tfk_model *m, const int *joint_ids, int n,
     for (int i = 0; i < n; ++i) out[i] = v[i];
   });
 }
+int tfk_link_info(const tfk_model *m, int link_id, int *parent, int *jtype, int *jid, double axis[3], double origin[7]) {
+  return guarded([&] {
+    need(m, "model");
+    if (link_id < 0 || (size_t)link_id >= m->engine.model.n_links()) throw std::invalid_argument("link id out of range");
+    const LinkRec &l = m->engine.model.links()[link_id];
+    if (parent) *parent = l.parent;
+    if (jtype) *jtype = l.jtype;
+    if (jid) *jid = l.jid;
+    if (axis) axis[0] = l.axis.x, axis[1] = l.axis.y, axis[2] = l.axis.z;
+    if (origin) {
+      origin[0] = l.origin.p.x, origin[1] = l.origin.p.y, origin[2] = l.origin.p.z;
+      origin[3] = l.origin.q.x, origin[4] = l.origin.q.y, origin[5] = l.origin.q.z, origin[6] = l.origin.q.w;
+    }
+  });
+}
 int tfk_is_relevant(const tfk_model *m, int link_id, int joint_id, int *out) {
   return guarded([&] {
     need(m, "model");
