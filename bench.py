@@ -285,8 +285,8 @@ def run_ours(args):
         pin_q = capi.PinnedArray((ne, n_in), dtype=np_dt, order="C")
         pin_q.array[...] = host_q[0][:ne]
         k_e2e = max(3, min(args.steps, 10))
-        for _ in range(2):
-            robot.solve_forward_kinematics_batch(pin_q.array, lids, jids, rot, base, True, prec, [local_rank], True)
+        for _ in range(3):  # results are held across calls, as in the timed loop, so the pinned pool is warm
+            P, J = robot.solve_forward_kinematics_batch(pin_q.array, lids, jids, rot, base, True, prec, [local_rank], True)
         barrier()
         t0 = time.perf_counter()
         for _ in range(k_e2e):
