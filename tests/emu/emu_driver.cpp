@@ -18,17 +18,32 @@ using namespace tfk;
 static thread_local std::string g_err;
 
 template <class Core, class T>
-static void run(const std::vector<unsigned char> &blob, const double *qs, long n, double *Pd, double *Jd) {
+static void run(const std::vector<unsigned char> &blob, const double *qs, long n, double *Pd, double *Jd, bool two_phase) {
   PlanView pv = plan_view(blob.data());
   const PlanHeader &h = *pv.h;
   const long long ldP = (long long)n * h.n_out, ldJ = ldP * h.pose_dim;
-  std::vector<T> rec((size_t)(h.rec_size > 0 ? h.rec_size : 1));
+  const bool fused = h.n_out == 1 && !two_phase; // the kernels' rule (engine.cpp)
+  std::vector<T> rec((size_t)((fused ? h.fz_size : h.rec_size) > 0 ? (fused ? h.fz_size : h.rec_size) : 1));
   std::vector<T> qrow((size_t)(h.n_in > 0 ? h.n_in : 1));
   std::vector<T> P((size_t)ldP * h.pose_dim), J(h.with_jacobian ? (size_t)ldJ * h.n_out_cols : 0);
+  DirectSink<T> out;
+  out.P = P.data();
+  out.J = J.data();
+  out.ldP = ldP;
+  out.ldJ = ldJ;
+  out.D = h.pose_dim;
   for (long i = 0; i < n; ++i) {
     for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
-    Core::phase_a(pv, qrow.data(), rec.data(), 1);
-    for (int o = 0; o < h.n_out; ++o) Core::phase_b(pv, rec.data(), 1, i, o, P.data(), J.data(), ldP, ldJ);
+    if (fused) {
+      out.head = i;
+      Core::run_fused(pv, qrow.data(), rec.data(), 1, out);
+    } else {
+      Core::phase_a(pv, qrow.data(), rec.data(), 1);
+      for (int o = 0; o < h.n_out; ++o) {
+        out.head = (long long)i * h.n_out + o;
+        Core::phase_b(pv, rec.data(), 1, o, out);
+      }
+    }
   }
   for (size_t k = 0; k < P.size(); ++k) Pd[k] = (double)P[k];
   if (Jd)
@@ -78,7 +93,7 @@ void emu_link_info(void *m, int id, int *parent, int *jtype, int *jid, double *a
 int emu_is_relevant(void *m, int l, int j) { return static_cast<KinematicModel *>(m)->is_relevant(l, j) ? 1 : 0; }
 
 // mode 0: FP64 strict (portable libm, FD base columns); 1: FP32 (native libm, analytic base columns);
-// 2: FP64 with the platform libm (FD base columns)
+// 2: FP64 with the platform libm (FD base columns); +16: force the two-phase driver for a single link
 int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, const int *joints, int n_joint,
               int rot_type, int base_type, int with_jacobian, int mode, double *P, double *J) {
   try {
@@ -90,12 +105,14 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     key.with_jacobian = with_jacobian;
     key.model_version = static_cast<KinematicModel *>(m)->version();
     std::vector<unsigned char> blob = build_plan(*static_cast<KinematicModel *>(m), key);
+    const bool two_phase = (mode & 16) != 0;
+    mode &= 15;
     if (mode == 0)
-      run<FkCore<MathPortable, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr);
+      run<FkCore<MathPortable, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
     else if (mode == 1)
-      run<FkCore<MathNative32, true>, float>(blob, qs, n, P, with_jacobian ? J : nullptr);
+      run<FkCore<MathNative32, true>, float>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
     else
-      run<FkCore<MathNative64, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr);
+      run<FkCore<MathNative64, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
     return 0;
   } catch (const std::exception &e) {
     g_err = e.what();

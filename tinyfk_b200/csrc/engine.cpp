@@ -193,13 +193,34 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (n <= 0 || h->n_out == 0) return;
   if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
-  const int smem = (int)e.blob.size();
+  const int plan_bytes = (int)e.blob.size();
+  const int rb = (int)real_size(precision);
+  // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
+  // in shared memory; several links -> two-phase through block-private scratch
+  int variant, rec_reals;
+  SmemLayout L;
+  if (h->n_out == 1) {
+    rec_reals = h->fz_size;
+    L = smem_layout(plan_bytes, h->n_in, rec_reals, rb);
+    variant = KV_FUSED_SMEM;
+    if (L.total > 100 * 1024) { // keep at least two blocks per SM; beyond that records go to L2
+      L = smem_layout(plan_bytes, h->n_in, 0, rb);
+      variant = KV_FUSED_GMEM;
+    }
+  } else {
+    rec_reals = h->rec_size;
+    L = smem_layout(plan_bytes, h->n_in, 0, rb);
+    variant = KV_TWOPHASE;
+  }
+  const int smem = L.total;
   if (smem > 200 * 1024) throw std::invalid_argument("plan too large for shared memory");
-  auto okey = std::make_pair(precision, smem);
+  auto okey = std::make_tuple(device, precision, variant, smem);
   auto oit = occupancy_.find(okey);
   int bps = 0;
   if (oit == occupancy_.end()) {
-    ck(precision == PREC_F32 ? occupancy_fk_f32(smem, &bps) : occupancy_fk_f64_strict(smem, &bps), "occupancy query");
+    // also raises the kernel's dynamic shared memory limit on this device when smem > 48 KB
+    ck(precision == PREC_F32 ? occupancy_fk_f32(variant, smem, &bps) : occupancy_fk_f64_strict(variant, smem, &bps),
+       "occupancy query");
     if (bps < 1) throw CudaError("kernel does not fit on an SM");
     occupancy_[okey] = bps;
   } else {
@@ -208,25 +229,30 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const int64_t n_tiles = (n + TFK_TILE - 1) / TFK_TILE;
   const int64_t resident = (int64_t)sm_count(device) * bps;
   const int grid = (int)std::min<int64_t>(n_tiles, resident);
-  const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(h->rec_size, 1) * real_size(precision);
-  Workspace &w = workspace(device, stream, rec_bytes);
   KernelArgs a;
+  a.scratch = nullptr;
+  if (variant != KV_FUSED_SMEM) {
+    const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(rec_reals, 1) * real_size(precision);
+    a.scratch = workspace(device, stream, rec_bytes).scratch;
+  }
   a.plan = plan_on_device(e, device, stream);
-  a.plan_bytes = smem;
+  a.plan_bytes = plan_bytes;
   a.q = d_q;
   a.n = n;
   a.row0 = row0;
   a.ld_cfg = ld_cfg;
   a.P = d_P;
   a.J = d_J;
-  a.scratch = w.scratch;
-  ck(precision == PREC_F32 ? launch_fk_f32(a, grid, stream) : launch_fk_f64_strict(a, grid, stream), "kernel launch");
+  ck(precision == PREC_F32 ? launch_fk_f32(a, variant, grid, smem, stream)
+                           : launch_fk_f64_strict(a, variant, grid, smem, stream),
+     "kernel launch");
   g_launches.fetch_add(1);
   last_launch.grid = grid;
   last_launch.block = TFK_TILE;
   last_launch.smem_bytes = smem;
   last_launch.blocks_per_sm = bps;
-  last_launch.rec_reals = h->rec_size;
+  last_launch.rec_reals = rec_reals;
+  last_launch.variant = variant;
 }
 
 void Engine::solve_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec,

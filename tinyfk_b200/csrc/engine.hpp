@@ -13,6 +13,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <tuple>
 #include <utility>
 #include <vector>
 
@@ -35,7 +36,7 @@ struct SolveSpec {
 };
 
 struct LaunchInfo {
-  int grid, block, smem_bytes, blocks_per_sm, rec_reals;
+  int grid, block, smem_bytes, blocks_per_sm, rec_reals, variant;
 };
 
 class Engine {
@@ -81,7 +82,7 @@ private:
   std::map<std::pair<int, cudaStream_t>, Workspace> workspaces_;
   std::map<int, HostPipe> pipes_;
   std::map<int, int> sm_counts_;
-  std::map<std::pair<int, int>, int> occupancy_; // (precision, smem bytes rounded) -> blocks per SM
+  std::map<std::tuple<int, int, int, int>, int> occupancy_; // (device, precision, variant, smem bytes) -> blocks per SM
 };
 
 int64_t kernel_launch_count();

@@ -1,17 +1,23 @@
-// fk_core.h -- the per-config work of the batched FK + Jacobian path, as two phases.
+// fk_core.h -- the per-configuration work of the batched FK + Jacobian path.
 //
-//   phase A (one thread per configuration): base pose from the row tail, then ONE pass down the
-//     pruned, topologically sorted link tree composing (quaternion, translation) frames in registers.
-//     Replaces the reference's set_base_pose + clear_cache + get_link_pose/get_link_pose_inner walk
-//     (src/wrapper.cpp:84-97, src/kinematics.cpp:37-103).  Emits small records: the base record,
-//     one (world axis, position) record per driven joint, one (position[, quaternion]) record per
-//     requested link.
-//   phase B (one thread per (configuration, requested link)): pose row of P and all Jacobian
-//     columns for that link from the records.  Replaces src/wrapper.cpp:98-121 + get_jacobian
-//     (src/kinematics.cpp:105-235) and fuses the PLANER column pick of python/tinyfk/__init__.py:154-158.
+//   walk():      base pose -> ONE pass down the pruned, topologically sorted link tree, composing
+//                (quaternion, translation) frames in registers.  Replaces the reference's
+//                set_base_pose + clear_cache + get_link_pose/get_link_pose_inner walk
+//                (src/wrapper.cpp:84-97, src/kinematics.cpp:37-103).  Emits small records (world axis
+//                per driven joint, position per distinct joint position, branch-point frames) and
+//                hands every requested link's pose to a sink.
+//   emit_link(): pose row of P and all Jacobian columns of one (configuration, link) pair from the
+//                records.  Replaces src/wrapper.cpp:98-121 + get_jacobian (src/kinematics.cpp:105-235)
+//                and fuses the PLANER column pick of python/tinyfk/__init__.py:154-158.
 //
-// Header only, TFK_FN = __host__ __device__: the kernels (fk_kernels.cuh) call these per thread; the
-// CPU test harness tests/emu (test infrastructure, not a product path) can run the very same code.
+// Two drivers use them (fk_kernels.cuh):
+//   fused     (one requested link): run_fused() = walk + emit_link in the same thread, records are
+//             thread-private (shared memory), nothing but q, P and J touches HBM;
+//   two-phase (several links): phase_a() = walk per configuration storing link records, phase_b() =
+//             emit_link per (configuration, link) so that consecutive threads write consecutive rows.
+//
+// Header only, TFK_FN = __host__ __device__: the kernels call these per thread; the CPU test harness
+// tests/emu (test infrastructure, not a product path) runs the very same code.
 #ifndef TFK_FK_CORE_H
 #define TFK_FK_CORE_H
 
@@ -39,6 +45,21 @@ TFK_FN PlanView plan_view(const unsigned char *blob) {
   return v;
 }
 
+// Output sink used on the CPU (tests/emu) and wherever no staging is wanted: plain stores into the
+// column-major arrays of the reference (src/wrapper.cpp:80-82,123):
+//   P[d*ldP + head],  J[c*ldJ + head*D + r],  head = row*n_out + o.
+template <class T> struct DirectSink {
+  T *P, *J;
+  long long ldP, ldJ, head;
+  int D;
+  TFK_FN void begin() const {}
+  TFK_FN void put_P(int d, T v) const { P[d * ldP + head] = v; }
+  TFK_FN void put_J(int c, const T (&v)[7]) const {
+    T *Jc = J + c * ldJ + head * D;
+    for (int r = 0; r < D; ++r) Jc[r] = v[r];
+  }
+};
+
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
 // instead of the reference's forward difference (FP32 mode: eps = 1e-7 is below one FP32 ulp).
 template <class M, bool ANALYTIC_BASE> struct FkCore {
@@ -47,6 +68,14 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
   typedef Vec3<T> V;
   typedef Quat<T> Q;
   typedef PoseT<T> P;
+
+  // what the base columns of the Jacobian need, derived once per configuration from the base pose
+  struct BaseCtx {
+    P base;
+    P binv;  // strict: Pose::inverse of the base pose (src/kinematics.cpp:186)
+    Q bk[3]; // strict: setFromRPY(rpy_b + eps*e_k) (src/kinematics.cpp:205-210)
+    V w[3];  // analytic: world angular-velocity axes of roll, pitch, yaw
+  };
 
   static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
     rec[(at + 0) * stride] = a.p.x;
@@ -80,14 +109,28 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     rec[(at + 1) * stride] = a.y;
     rec[(at + 2) * stride] = a.z;
   }
+  static TFK_FN Q get_quat(const T *rec, int stride, int at) {
+    Q a;
+    a.x = rec[(at + 0) * stride];
+    a.y = rec[(at + 1) * stride];
+    a.z = rec[(at + 2) * stride];
+    a.w = rec[(at + 3) * stride];
+    return a;
+  }
+  static TFK_FN void put_quat(T *rec, int stride, int at, const Q &a) {
+    rec[(at + 0) * stride] = a.x;
+    rec[(at + 1) * stride] = a.y;
+    rec[(at + 2) * stride] = a.z;
+    rec[(at + 3) * stride] = a.w;
+  }
 
   // ---------------------------------------------------------------------------------------------
-  // qrow: this configuration's input row (n_in reals).  rec: this configuration's record, element k
-  // at rec[k * stride].
-  static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) {
-    const PlanHeader &h = *pv.h;
+  // Base pose of this configuration.  FIXED: the model's stored pose (include/tinyfk.hpp:72,
+  // kinematics.cpp:51); otherwise src/wrapper.cpp:25-35 on the row tail (PLANER rows are (x, y, yaw),
+  // padded to (x, y, 0, 0, 0, yaw) by python/tinyfk/__init__.py:98-103).
+  static TFK_FN P base_pose_of(const PlanHeader &h, const T *qrow) {
     P base;
-    if (h.base_type == 0) { // FIXED: the model's stored base pose (include/tinyfk.hpp:72, kinematics.cpp:51)
+    if (h.base_type == 0) {
       base.p.x = T(h.base_pose[0]);
       base.p.y = T(h.base_pose[1]);
       base.p.z = T(h.base_pose[2]);
@@ -95,236 +138,253 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       base.q.y = T(h.base_pose[4]);
       base.q.z = T(h.base_pose[5]);
       base.q.w = T(h.base_pose[6]);
+      return base;
+    }
+    const T *b = qrow + h.n_cols;
+    base.p.x = b[0];
+    base.p.y = b[1];
+    if (h.base_type == 1) {
+      // setFromRPY(0, 0, yaw), pose.h:202-216: sin(0) = 0, cos(0) = 1 exactly, so the products with
+      // them are exact and x = y = 0, z = sin(yaw/2), w = cos(yaw/2) before normalize
+      base.p.z = T(0);
+      T s, c;
+      M::sincos_(b[2] / T(2), &s, &c);
+      base.q.x = T(0);
+      base.q.y = T(0);
+      base.q.z = s;
+      base.q.w = c;
+      const T n = M::sqrt_(s * s + c * c); // x*x + y*y + z*z + w*w with x = y = 0 (pose.h:232)
+      if (n == T(0)) {
+        base.q = O::qidentity();
+      } else {
+        base.q.z = s / n;
+        base.q.w = c / n;
+      }
     } else {
-      // src/wrapper.cpp:25-35 on the last 6 entries; PLANER rows are (x, y, yaw) padded to
-      // (x, y, 0, 0, 0, yaw) by python/tinyfk/__init__.py:98-103
-      const T *b = qrow + h.n_cols;
-      T roll = T(0), pitch = T(0), yaw;
-      base.p.x = b[0];
-      base.p.y = b[1];
-      if (h.base_type == 1) {
-        base.p.z = T(0);
-        yaw = b[2];
-      } else {
-        base.p.z = b[2];
-        roll = b[3];
-        pitch = b[4];
-        yaw = b[5];
-      }
-      base.q = O::from_rpy(roll, pitch, yaw);
+      base.p.z = b[2];
+      base.q = O::from_rpy(b[3], b[4], b[5]);
     }
+    return base;
+  }
 
-    if (h.off_jrec > h.off_base) { // base record wanted (Jacobian with a moving base)
-      put_pose(rec, stride, h.off_base, base);
-      const V rpy_b = O::to_rpy(base.q); // src/kinematics.cpp:187
-      if (ANALYTIC_BASE) {
-        // world angular-velocity axes of roll, pitch, yaw for R = Rz(yaw) Ry(pitch) Rx(roll)
-        T sp, cp, sy, cy;
-        M::sincos_(rpy_b.y, &sp, &cp);
-        M::sincos_(rpy_b.z, &sy, &cy);
-        V wr, wp, wy;
-        wr.x = cy * cp;
-        wr.y = sy * cp;
-        wr.z = -sp;
-        wp.x = -sy;
-        wp.y = cy;
-        wp.z = T(0);
-        wy.x = T(0);
-        wy.y = T(0);
-        wy.z = T(1);
-        put_vec(rec, stride, h.off_base + 7, wr);
-        put_vec(rec, stride, h.off_base + 10, wp);
-        put_vec(rec, stride, h.off_base + 13, wy);
-      } else {
-        put_pose(rec, stride, h.off_base + 7, O::inverse(base)); // src/kinematics.cpp:186
-        const T eps = T(1e-7);                                   // src/kinematics.cpp:201
-        for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) {
-          V t = rpy_b;
-          if (k == 0) t.x += eps;
-          if (k == 1) t.y += eps;
-          if (k == 2) t.z += eps;
-          const Q qk = O::from_rpy(t.x, t.y, t.z); // src/kinematics.cpp:205-210
-          const int at = h.off_base + 14 + 4 * k;
-          rec[(at + 0) * stride] = qk.x;
-          rec[(at + 1) * stride] = qk.y;
-          rec[(at + 2) * stride] = qk.z;
-          rec[(at + 3) * stride] = qk.w;
-        }
-      }
+  // src/kinematics.cpp:186-187,201-210 hoisted out of the per-link loop (same operands per link)
+  static TFK_FN void make_base_ctx(const PlanHeader &h, const P &base, BaseCtx &c) {
+    c.base = base;
+    const V rpy_b = O::to_rpy(base.q); // src/kinematics.cpp:187
+    if (ANALYTIC_BASE) {
+      // world angular-velocity axes of roll, pitch, yaw for R = Rz(yaw) Ry(pitch) Rx(roll)
+      T sp, cp, sy, cy;
+      M::sincos_(rpy_b.y, &sp, &cp);
+      M::sincos_(rpy_b.z, &sy, &cy);
+      c.w[0].x = cy * cp;
+      c.w[0].y = sy * cp;
+      c.w[0].z = -sp;
+      c.w[1].x = -sy;
+      c.w[1].y = cy;
+      c.w[1].z = T(0);
+      c.w[2].x = T(0);
+      c.w[2].y = T(0);
+      c.w[2].z = T(1);
+      return;
     }
-    if (h.root_lrec >= 0) { // the root link's pose is the base pose (src/kinematics.cpp:51-58,102)
-      const int at = h.off_lrec + h.root_lrec * h.lrec_size;
-      put_vec(rec, stride, at, base.p);
-      if (h.lrec_size == 7) {
-        rec[(at + 3) * stride] = base.q.x;
-        rec[(at + 4) * stride] = base.q.y;
-        rec[(at + 5) * stride] = base.q.z;
-        rec[(at + 6) * stride] = base.q.w;
-      }
+    c.binv = O::inverse(base); // src/kinematics.cpp:186
+    const T eps = T(1e-7);     // src/kinematics.cpp:201
+    for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) {
+      V t = rpy_b;
+      if (k == 0) t.x += eps;
+      if (k == 1) t.y += eps;
+      if (k == 2) t.z += eps;
+      c.bk[k] = O::from_rpy(t.x, t.y, t.z); // src/kinematics.cpp:205-210
     }
+  }
 
-    T frames[TFK_MAX_FRAMES][7]; // branch-point frames; touched only by trees, never by chains
-    P cur = base;
-    for (int s = 0; s < h.n_slots; ++s) {
-      const PlanSlot &sl = pv.slots[s];
-      P parent;
-      if (sl.frame_ld == FRAME_RUNNING) {
-        parent = cur;
-      } else if (sl.frame_ld == FRAME_BASE) {
-        parent = base;
-      } else {
-        const T *f = frames[sl.frame_ld];
-        parent.p.x = f[0];
-        parent.p.y = f[1];
-        parent.p.z = f[2];
-        parent.q.x = f[3];
-        parent.q.y = f[4];
-        parent.q.z = f[5];
-        parent.q.w = f[6];
-      }
-      P origin;
-      origin.p.x = T(sl.opos[0]);
-      origin.p.y = T(sl.opos[1]);
-      origin.p.z = T(sl.opos[2]);
-      origin.q.x = T(sl.oquat[0]);
-      origin.q.y = T(sl.oquat[1]);
-      origin.q.z = T(sl.oquat[2]);
-      origin.q.w = T(sl.oquat[3]);
-      V axis;
-      axis.x = T(sl.axis[0]);
-      axis.y = T(sl.axis[1]);
-      axis.z = T(sl.axis[2]);
-      P local;
-      if (sl.kind == SLOT_FIXED) {
-        local = origin; // src/kinematics.cpp:74-75
-      } else if (sl.kind == SLOT_REVOLUTE) {
-        local = O::local_revolute(origin, axis, qrow[sl.qcol]); // src/kinematics.cpp:77-80
-      } else {
-        local = O::local_prismatic(origin, axis, qrow[sl.qcol]);
-      }
-      cur = O::compose(parent, local); // src/kinematics.cpp:96-97
-      if (sl.frame_st >= 0) {
-        T *f = frames[sl.frame_st];
-        f[0] = cur.p.x;
-        f[1] = cur.p.y;
-        f[2] = cur.p.z;
-        f[3] = cur.q.x;
-        f[4] = cur.q.y;
-        f[5] = cur.q.z;
-        f[6] = cur.q.w;
-      }
-      if (sl.jrec >= 0) { // src/kinematics.cpp:143-147: axis of the joint in the root frame
-        const int at = h.off_jrec + 6 * sl.jrec;
-        put_vec(rec, stride, at, O::rotate(cur.q, axis));
-        put_vec(rec, stride, at + 3, cur.p);
-      }
-      if (sl.lrec >= 0) {
-        const int at = h.off_lrec + sl.lrec * h.lrec_size;
-        put_vec(rec, stride, at, cur.p);
-        if (h.lrec_size == 7) {
-          rec[(at + 3) * stride] = cur.q.x;
-          rec[(at + 4) * stride] = cur.q.y;
-          rec[(at + 5) * stride] = cur.q.z;
-          rec[(at + 6) * stride] = cur.q.w;
-        }
-      }
+  static TFK_FN void store_base_ctx(const PlanHeader &h, const BaseCtx &c, T *rec, int stride) {
+    put_pose(rec, stride, h.off_base, c.base);
+    if (ANALYTIC_BASE) {
+      for (int k = 0; k < 3; ++k) put_vec(rec, stride, h.off_base + 7 + 3 * k, c.w[k]);
+    } else {
+      put_pose(rec, stride, h.off_base + 7, c.binv);
+      for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) put_quat(rec, stride, h.off_base + 14 + 4 * k, c.bk[k]);
+    }
+  }
+  static TFK_FN void load_base_ctx(const PlanHeader &h, const T *rec, int stride, BaseCtx &c) {
+    c.base = get_pose(rec, stride, h.off_base);
+    if (ANALYTIC_BASE) {
+      for (int k = 0; k < 3; ++k) c.w[k] = get_vec(rec, stride, h.off_base + 7 + 3 * k);
+    } else {
+      c.binv = get_pose(rec, stride, h.off_base + 7);
+      for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) c.bk[k] = get_quat(rec, stride, h.off_base + 14 + 4 * k);
     }
   }
 
   // ---------------------------------------------------------------------------------------------
-  // One (configuration, requested link) pair.  row = global configuration index (row0 + i) used for
-  // addressing; o = index into elink_ids.  Outputs are column-major exactly as the reference hands
-  // them to numpy (src/wrapper.cpp:80-82,123):  P[d * ldP + row*n_out + o],
-  // J[c * ldJ + (row*n_out + o)*pose_dim + r]  with ldP = N*n_out, ldJ = ldP*pose_dim.
-  static TFK_FN void phase_b(const PlanView &pv, const T *rec, int stride, long long row, int o, T *Pout,
-                             T *Jout, long long ldP, long long ldJ) {
+  // One pass down the tree.  qrow: this configuration's input row.  rec: this configuration's records
+  // (element k at rec[k*stride]); o_arec / o_prec / o_frame: where the axis, position and frame records
+  // start.  sink.link(lrec, pose) is called for every requested link, in tree order.
+  template <class LinkSink>
+  static TFK_FN void walk(const PlanView &pv, const T *qrow, T *rec, int stride, int o_arec, int o_prec, int o_frame,
+                          const P &base, LinkSink &sink) {
     const PlanHeader &h = *pv.h;
-    const int lat = h.off_lrec + pv.lrec_of_out[o] * h.lrec_size;
-    P e;
-    e.p = get_vec(rec, stride, lat);
-    e.q = O::qidentity();
-    if (h.lrec_size == 7) {
-      e.q.x = rec[(lat + 3) * stride];
-      e.q.y = rec[(lat + 4) * stride];
-      e.q.z = rec[(lat + 5) * stride];
-      e.q.w = rec[(lat + 6) * stride];
+    P cur = base;
+    Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
+    for (int s = 0; s < h.n_slots; ++s) {
+      const PlanSlot &sl = pv.slots[s];
+      if (sl.frame_ld == FRAME_BASE) {
+        cur = base;
+      } else if (sl.frame_ld != FRAME_RUNNING) {
+        cur = get_pose(rec, stride, o_frame + 7 * sl.frame_ld);
+      }
+      // pose_transform(parent, local), pose.cpp:139-146: position first (it uses the parent's rotation)
+      T ang = T(0);
+      if (sl.kind != SLOT_FIXED) ang = qrow[sl.qcol];
+      if (sl.trn != V_NONE) {
+        if (sl.flags & SF_INV_BEFORE) inv = O::qget_inverse(cur.q);
+        V lp; // local translation
+        lp.x = T(sl.opos[0]);
+        lp.y = T(sl.opos[1]);
+        lp.z = T(sl.opos[2]);
+        if (sl.kind == SLOT_PRISMATIC) {
+          // Joint::transform (joint.h:241-247): position axis*d, rotation identity; then
+          // pose_transform(origin, .) (src/kinematics.cpp:77-80)
+          V d;
+          d.x = T(sl.axis[0]) * ang;
+          d.y = T(sl.axis[1]) * ang;
+          d.z = T(sl.axis[2]) * ang;
+          if (sl.flags & SF_PRISM_OQ) {
+            Q oq, oi;
+            oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
+            oi.x = T(sl.oinv[0]), oi.y = T(sl.oinv[1]), oi.z = T(sl.oinv[2]), oi.w = T(sl.oinv[3]);
+            d = O::qt_xyz(oq, O::vq_full(d, oi));
+          }
+          // components whose axis and origin entries are both exact zeros stay exact zeros
+          lp.x = d.x + lp.x;
+          lp.y = d.y + lp.y;
+          lp.z = d.z + lp.z;
+        }
+        const V r = O::qt_xyz(cur.q, O::vq(sl.trn, lp, inv));
+        cur.p.x = r.x + cur.p.x;
+        cur.p.y = r.y + cur.p.y;
+        cur.p.z = r.z + cur.p.z;
+      }
+      if (sl.rot != ROT_NONE) {
+        if (sl.rot == ROT_CONST) {
+          Q oq;
+          oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
+          cur.q = O::qmul(cur.q, oq);
+        } else {
+          // Joint::transform for REVOLUTE/CONTINUOUS, joint.h:231-240 (axis is NOT normalised)
+          T sn, cs;
+          M::sincos_(ang * T(0.5), &sn, &cs);
+          V ax;
+          ax.x = T(sl.axis[0]), ax.y = T(sl.axis[1]), ax.z = T(sl.axis[2]);
+          if (sl.rot == ROT_REV) {
+            cur.q = O::qmul_axis(cur.q, sl.axc, ax, sn, cs);
+          } else {
+            Q oq;
+            oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
+            cur.q = O::qmul(cur.q, O::qmul_axis(oq, sl.axc, ax, sn, cs));
+          }
+        }
+      }
+      if (sl.frame_st >= 0) put_pose(rec, stride, o_frame + 7 * sl.frame_st, cur);
+      if (sl.arec >= 0) { // src/kinematics.cpp:143-147: axis of the joint in the root frame
+        if (sl.flags & SF_INV_AFTER) inv = O::qget_inverse(cur.q);
+        V ax;
+        ax.x = T(sl.axis[0]), ax.y = T(sl.axis[1]), ax.z = T(sl.axis[2]);
+        put_vec(rec, stride, o_arec + 3 * sl.arec, O::qt_xyz(cur.q, O::vq(sl.axc, ax, inv)));
+        if (sl.prec >= 0) put_vec(rec, stride, o_prec + 3 * sl.prec, cur.p);
+      }
+      if (sl.lrec >= 0) sink.link(sl.lrec, cur);
     }
-    const long long head = row * h.n_out + o;
-    Pout[0 * ldP + head] = e.p.x; // src/wrapper.cpp:98-100
-    Pout[1 * ldP + head] = e.p.y;
-    Pout[2 * ldP + head] = e.p.z;
+  }
+
+  // ---------------------------------------------------------------------------------------------
+  // One (configuration, requested link) pair: pose row (src/wrapper.cpp:98-112) and Jacobian
+  // (src/kinematics.cpp:105-235).  e: the link's pose; o: index into elink_ids; rec/o_arec/o_prec: the
+  // configuration's joint records; ctx: base context (only read with a moving base and a Jacobian).
+  // `out` gets put_P(d, value) and put_J(column, values[pose_dim]) -- every entry of J is written.
+  template <class OutSink>
+  static TFK_FN void emit_link(const PlanView &pv, const P &e, int o, const T *rec, int stride, int o_arec, int o_prec,
+                               const BaseCtx &ctx, OutSink &out) {
+    const PlanHeader &h = *pv.h;
+    out.begin();
+    out.put_P(0, e.p.x);
+    out.put_P(1, e.p.y);
+    out.put_P(2, e.p.z);
     V erpy;
     erpy.x = erpy.y = erpy.z = T(0);
     if (h.rot_type == 1) { // src/wrapper.cpp:101-106
       erpy = O::to_rpy(e.q);
-      Pout[3 * ldP + head] = erpy.x;
-      Pout[4 * ldP + head] = erpy.y;
-      Pout[5 * ldP + head] = erpy.z;
+      out.put_P(3, erpy.x);
+      out.put_P(4, erpy.y);
+      out.put_P(5, erpy.z);
     } else if (h.rot_type == 2) { // src/wrapper.cpp:107-112
-      Pout[3 * ldP + head] = e.q.x;
-      Pout[4 * ldP + head] = e.q.y;
-      Pout[5 * ldP + head] = e.q.z;
-      Pout[6 * ldP + head] = e.q.w;
+      out.put_P(3, e.q.x);
+      out.put_P(4, e.q.y);
+      out.put_P(5, e.q.z);
+      out.put_P(6, e.q.w);
     }
     if (!h.with_jacobian) return;
 
-    const int D = h.pose_dim;
-    T *Jrow = Jout + head * D;
     typename O::RpyCoef coef;
+    coef.k_xx = coef.k_xy = coef.s3 = coef.c3 = coef.k_zx = coef.k_zy = T(0);
     Q einv = O::qidentity();
-    if (h.rot_type == 1) coef = O::rpy_coef(erpy);   // src/kinematics.cpp:121-123 + :14-21
-    if (h.rot_type == 2) einv = O::qinverse(e.q);    // src/kinematics.cpp:124-126
+    if (h.rot_type == 1) coef = O::rpy_coef(erpy);  // src/kinematics.cpp:121-123 + :14-21
+    if (h.rot_type == 2) einv = O::qinverse(e.q);   // src/kinematics.cpp:124-126
 
     // joint columns, src/kinematics.cpp:131-180
     const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
     for (int c = 0; c < h.n_cols; ++c) {
-      T *Jc = Jrow + (long long)c * ldJ;
+      T v[7];
+      v[0] = v[1] = v[2] = v[3] = v[4] = v[5] = v[6] = T(0);
       const bool relevant = (mask[c >> 5] >> (c & 31)) & 1u;
-      if (!relevant) {
-        for (int r = 0; r < D; ++r) Jc[r] = T(0);
-        continue;
+      if (relevant) {
+        const PlanCol &pc = pv.cols[c];
+        const V aw = get_vec(rec, stride, o_arec + 3 * pc.arec);
+        if (pc.prismatic) {
+          v[0] = aw.x;
+          v[1] = aw.y;
+          v[2] = aw.z;
+        } else {
+          const V cp = get_vec(rec, stride, o_prec + 3 * pc.prec);
+          V d;
+          d.x = e.p.x - cp.x;
+          d.y = e.p.y - cp.y;
+          d.z = e.p.z - cp.z;
+          const V dpos = O::cross(aw, d);
+          v[0] = dpos.x;
+          v[1] = dpos.y;
+          v[2] = dpos.z;
+          if (h.rot_type == 1) {
+            const V dr = O::rpy_derivative(coef, aw);
+            v[3] = dr.x;
+            v[4] = dr.y;
+            v[5] = dr.z;
+          } else if (h.rot_type == 2) {
+            const Q dq = O::q_derivative(einv, aw);
+            v[3] = dq.x;
+            v[4] = dq.y;
+            v[5] = dq.z;
+            v[6] = dq.w;
+          }
+        }
       }
-      const int jat = h.off_jrec + 6 * pv.cols[c].jrec;
-      const V aw = get_vec(rec, stride, jat);
-      if (pv.cols[c].prismatic) {
-        Jc[0] = aw.x;
-        Jc[1] = aw.y;
-        Jc[2] = aw.z;
-        for (int r = 3; r < D; ++r) Jc[r] = T(0);
-        continue;
-      }
-      const V cp = get_vec(rec, stride, jat + 3);
-      V d;
-      d.x = e.p.x - cp.x;
-      d.y = e.p.y - cp.y;
-      d.z = e.p.z - cp.z;
-      const V dpos = O::cross(aw, d);
-      Jc[0] = dpos.x;
-      Jc[1] = dpos.y;
-      Jc[2] = dpos.z;
-      if (h.rot_type == 1) {
-        const V dr = O::rpy_derivative(coef, aw);
-        Jc[3] = dr.x;
-        Jc[4] = dr.y;
-        Jc[5] = dr.z;
-      } else if (h.rot_type == 2) {
-        const Q dq = O::q_derivative(einv, aw);
-        Jc[3] = dq.x;
-        Jc[4] = dq.y;
-        Jc[5] = dq.z;
-        Jc[6] = dq.w;
-      }
+      out.put_J(c, v);
     }
 
     if (h.base_type == 0) return;
     // base translation columns, src/kinematics.cpp:194-196
     const int n_trans = (h.base_type == 1) ? 2 : 3;
     for (int k = 0; k < n_trans; ++k) {
-      T *Jc = Jrow + (long long)(h.n_cols + k) * ldJ;
-      for (int r = 0; r < D; ++r) Jc[r] = (r == k) ? T(1) : T(0);
+      T v[7];
+      v[0] = (k == 0) ? T(1) : T(0);
+      v[1] = (k == 1) ? T(1) : T(0);
+      v[2] = (k == 2) ? T(1) : T(0);
+      v[3] = v[4] = v[5] = v[6] = T(0);
+      out.put_J(h.n_cols + k, v);
     }
     // base rotation columns: FLOATING keeps roll, pitch, yaw; PLANER keeps yaw only
-    const P base = get_pose(rec, stride, h.off_base);
+    const P &base = ctx.base;
     const int k0 = (h.base_type == 1) ? 2 : 0;
     if (ANALYTIC_BASE) {
       V d;
@@ -332,30 +392,33 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       d.y = e.p.y - base.p.y;
       d.z = e.p.z - base.p.z;
       for (int k = k0; k < 3; ++k) {
-        T *Jc = Jrow + (long long)(h.n_cols + n_trans + (k - k0)) * ldJ;
-        const V w = get_vec(rec, stride, h.off_base + 7 + 3 * k);
+        T v[7];
+        v[6] = T(0);
+        const V w = ctx.w[k];
         const V dpos = O::cross(w, d);
-        Jc[0] = dpos.x;
-        Jc[1] = dpos.y;
-        Jc[2] = dpos.z;
+        v[0] = dpos.x;
+        v[1] = dpos.y;
+        v[2] = dpos.z;
+        v[3] = v[4] = v[5] = T(0);
         if (h.rot_type == 1) {
           const V dr = O::rpy_derivative(coef, w);
-          Jc[3] = dr.x;
-          Jc[4] = dr.y;
-          Jc[5] = dr.z;
+          v[3] = dr.x;
+          v[4] = dr.y;
+          v[5] = dr.z;
         } else if (h.rot_type == 2) {
           const Q dq = O::q_derivative(einv, w);
-          Jc[3] = dq.x;
-          Jc[4] = dq.y;
-          Jc[5] = dq.z;
-          Jc[6] = dq.w;
+          v[3] = dq.x;
+          v[4] = dq.y;
+          v[5] = dq.z;
+          v[6] = dq.w;
         }
+        out.put_J(h.n_cols + n_trans + (k - k0), v);
       }
       return;
     }
     // forward finite difference replica, src/kinematics.cpp:182-232
     const T eps = T(1e-7);
-    const P binv = get_pose(rec, stride, h.off_base + 7);
+    const P &binv = ctx.binv;
     P be; // tf_blink_to_elink = pose_transform(tf_blink_to_rlink, tf_rlink_to_elink)
     if (h.lrec_size == 7) {
       be = O::compose(binv, e);
@@ -367,14 +430,9 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       be.q = O::qidentity();
     }
     for (int k = k0; k < 3; ++k) {
-      T *Jc = Jrow + (long long)(h.n_cols + n_trans + (k - k0)) * ldJ;
-      const int at = h.off_base + 14 + 4 * k;
       P bk;
       bk.p = base.p;
-      bk.q.x = rec[(at + 0) * stride];
-      bk.q.y = rec[(at + 1) * stride];
-      bk.q.z = rec[(at + 2) * stride];
-      bk.q.w = rec[(at + 3) * stride];
+      bk.q = ctx.bk[k];
       V pk;
       Q qk = O::qidentity();
       if (h.lrec_size == 7) {
@@ -387,21 +445,94 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
         pk.y = r.y + bk.p.y;
         pk.z = r.z + bk.p.z;
       }
-      Jc[0] = (pk.x - e.p.x) / eps;
-      Jc[1] = (pk.y - e.p.y) / eps;
-      Jc[2] = (pk.z - e.p.z) / eps;
+      T v[7];
+      v[3] = v[4] = v[5] = v[6] = T(0);
+      v[0] = (pk.x - e.p.x) / eps;
+      v[1] = (pk.y - e.p.y) / eps;
+      v[2] = (pk.z - e.p.z) / eps;
       if (h.rot_type == 1) {
         const V rk = O::to_rpy(qk);
-        Jc[3] = (rk.x - erpy.x) / eps;
-        Jc[4] = (rk.y - erpy.y) / eps;
-        Jc[5] = (rk.z - erpy.z) / eps;
+        v[3] = (rk.x - erpy.x) / eps;
+        v[4] = (rk.y - erpy.y) / eps;
+        v[5] = (rk.z - erpy.z) / eps;
       } else if (h.rot_type == 2) {
-        Jc[3] = (qk.x - e.q.x) / eps;
-        Jc[4] = (qk.y - e.q.y) / eps;
-        Jc[5] = (qk.z - e.q.z) / eps;
-        Jc[6] = (qk.w - e.q.w) / eps;
+        v[3] = (qk.x - e.q.x) / eps;
+        v[4] = (qk.y - e.q.y) / eps;
+        v[5] = (qk.z - e.q.z) / eps;
+        v[6] = (qk.w - e.q.w) / eps;
       }
+      out.put_J(h.n_cols + n_trans + (k - k0), v);
     }
+  }
+
+  // ---------------------------------------------------------------------------------------------
+  // two-phase driver, phase A: one thread per configuration
+  struct StoreLinks {
+    const PlanHeader *h;
+    T *rec;
+    int stride;
+    TFK_FN void link(int lrec, const P &cur) const {
+      const int at = h->off_lrec + lrec * h->lrec_size;
+      put_vec(rec, stride, at, cur.p);
+      if (h->lrec_size == 7) put_quat(rec, stride, at + 3, cur.q);
+    }
+  };
+  static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) {
+    const PlanHeader &h = *pv.h;
+    const P base = base_pose_of(h, qrow);
+    if (h.off_arec > h.off_base) { // base record wanted (Jacobian with a moving base)
+      BaseCtx ctx;
+      make_base_ctx(h, base, ctx);
+      store_base_ctx(h, ctx, rec, stride);
+    }
+    StoreLinks sink;
+    sink.h = &h;
+    sink.rec = rec;
+    sink.stride = stride;
+    if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
+    walk(pv, qrow, rec, stride, h.off_arec, h.off_prec, h.off_frame, base, sink);
+  }
+
+  // two-phase driver, phase B: one thread per (configuration, requested link)
+  template <class OutSink> static TFK_FN void phase_b(const PlanView &pv, const T *rec, int stride, int o, OutSink &out) {
+    const PlanHeader &h = *pv.h;
+    const int lat = h.off_lrec + pv.lrec_of_out[o] * h.lrec_size;
+    P e;
+    e.p = get_vec(rec, stride, lat);
+    e.q = O::qidentity();
+    if (h.lrec_size == 7) e.q = get_quat(rec, stride, lat + 3);
+    BaseCtx ctx;
+    if (h.with_jacobian && h.base_type != 0) load_base_ctx(h, rec, stride, ctx);
+    emit_link(pv, e, o, rec, stride, h.off_arec, h.off_prec, ctx, out);
+  }
+
+  // ---------------------------------------------------------------------------------------------
+  // fused driver (n_out == 1): walk and emit in the same thread; records use the fz_* layout
+  template <class OutSink> struct EmitAtLink {
+    const PlanView *pv;
+    const T *qrow;
+    T *rec;
+    int stride;
+    OutSink *out;
+    TFK_FN void link(int, const P &cur) const {
+      const PlanHeader &h = *pv->h;
+      BaseCtx ctx;
+      if (h.with_jacobian && h.base_type != 0) make_base_ctx(h, get_pose(rec, stride, 0), ctx);
+      emit_link(*pv, cur, 0, rec, stride, h.fz_arec, h.fz_prec, ctx, *out);
+    }
+  };
+  template <class OutSink> static TFK_FN void run_fused(const PlanView &pv, const T *qrow, T *rec, int stride, OutSink &out) {
+    const PlanHeader &h = *pv.h;
+    const P base = base_pose_of(h, qrow);
+    if (h.fz_arec > 0) put_pose(rec, stride, 0, base); // re-read when the link is reached (base columns)
+    EmitAtLink<OutSink> sink;
+    sink.pv = &pv;
+    sink.qrow = qrow;
+    sink.rec = rec;
+    sink.stride = stride;
+    sink.out = &out;
+    if (h.root_lrec >= 0) sink.link(h.root_lrec, base);
+    walk(pv, qrow, rec, stride, h.fz_arec, h.fz_prec, h.fz_frame, base, sink);
   }
 };
 

@@ -1,15 +1,27 @@
-// fk_kernels.cuh -- the sm_100a batch kernel: persistent blocks, one tile of TFK_TILE configurations
-// per iteration, phase A (thread per configuration) -> block-private records -> phase B (thread per
-// (configuration, link)), see fk_core.h.  Included by fk_kernels_strict.cu (built with -fmad=false:
+// fk_kernels.cuh -- the sm_100a batch kernels.  Persistent blocks of TFK_TILE threads, one tile of
+// TFK_TILE configurations per iteration.  Included by fk_kernels_strict.cu (built with -fmad=false:
 // bit-faithful FP64) and fk_kernels_fast.cu (FMA contraction on: FP32 mode).
 //
-// Memory plan (DESIGN.md "HBM layout"):
-//   q        [N][n_in]           row-major input, read once
-//   P        [pose_dim][N*n_out] column-major, written once      (reference layout, wrapper.cpp:80,123)
-//   J        [n_out_cols][N*n_out*pose_dim] column-major, written once, every entry (zeros included)
-//   records  [grid][rec_size][TFK_TILE] block-private scratch, written in phase A and re-read in phase B
-//            of the same tile; grid*TILE*rec_size*8 B total (L2-resident: 45 MB for the PR2-arm case)
-//   plan     a few KB, copied to shared memory once per block, read with warp-uniform loads
+//   fk_fused_kernel     one requested link (the usual end-effector query): one thread per configuration
+//                       walks the chain and writes the pose row and every Jacobian column itself.  The
+//                       joint records are thread-private and live in shared memory, so HBM sees only
+//                       q (read once), P and J (written once).
+//   fk_twophase_kernel  several links: phase A (thread per configuration) -> records -> phase B (thread
+//                       per (configuration, link)), so that consecutive threads own consecutive rows.
+//
+// Memory plan (DESIGN.md "Data layout in HBM"):
+//   q        [N][n_in] row-major input.  A tile's rows are one contiguous run: staged into shared memory
+//            with coalesced loads (odd row pitch -> conflict-free per-thread reads).
+//   P        [pose_dim][N*n_out] column-major (reference layout, wrapper.cpp:80,123): consecutive
+//            threads write consecutive addresses.
+//   J        [n_out_cols][N*n_out*pose_dim] column-major, every entry written (zeros included).  A
+//            warp's share of one column is ONE contiguous run of 32*pose_dim reals: it is transposed
+//            through a warp-private shared-memory strip and written with full-sector, fully coalesced
+//            streaming stores (st.global.cs).
+//   records  fused: [fz_size][TILE] in shared memory (global scratch only if they do not fit);
+//            two-phase: [grid][rec_size][TILE] block-private scratch, written in phase A and re-read in
+//            phase B of the same tile (L2-resident; the output stores are streaming so they do not evict it).
+//   plan     a few KB, copied to shared memory once per block, read with warp-uniform loads.
 #ifndef TFK_FK_KERNELS_CUH
 #define TFK_FK_KERNELS_CUH
 
@@ -20,50 +32,171 @@
 
 namespace tfk {
 
-template <class Core>
-__global__ void __launch_bounds__(TFK_TILE) fk_batch_kernel(const KernelArgs a) {
+enum { TFK_STG = 32 * 7 }; // reals in a warp's staging strip: 32 rows x pose_dim <= 7
+
+// Output sink of the kernels.  put_J must be called by all 32 lanes of the warp together.
+template <class T> struct StagedSink {
+  T *P, *J;
+  long long ldP, ldJ;
+  long long head;  // this lane's row of P (= row*n_out + o)
+  long long head0; // lane 0's row
+  int D, lane, nvalid;
+  bool valid;
+  T *stg; // warp-private strip of TFK_STG reals
+
+  __device__ __forceinline__ void begin() const { __syncwarp(); }
+  __device__ __forceinline__ void put_P(int d, T v) const {
+    if (valid) __stcs(P + d * ldP + head, v);
+  }
+  __device__ __forceinline__ void put_J(int c, const T (&v)[7]) const {
+    T *w = stg + lane * D;
+#pragma unroll
+    for (int r = 0; r < 7; ++r)
+      if (r < D) w[r] = v[r];
+    __syncwarp();
+    T *dst = J + c * ldJ + head0 * D;
+    const int cnt = nvalid * D;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const int e = lane + 32 * k;
+      if (e < cnt) __stcs(dst + e, stg[e]);
+    }
+    __syncwarp();
+  }
+};
+
+template <class T>
+__device__ __forceinline__ void stage_q_tile(T *qs, int q_pitch, const T *q, long long i0, int nv, int n_in) {
+  // the tile's rows are contiguous in HBM: coalesced loads, scattered (row, col) stores
+  if (n_in == 0) return;
+  const T *src = q + i0 * n_in;
+  const int total = nv * n_in;
+  int r = (int)threadIdx.x / n_in, c = (int)threadIdx.x - r * n_in;
+  const int dr = TFK_TILE / n_in, dc = TFK_TILE - dr * n_in;
+  for (int k = threadIdx.x; k < total; k += TFK_TILE) {
+    qs[r * q_pitch + c] = __ldcs(src + k);
+    r += dr;
+    c += dc;
+    if (c >= n_in) {
+      c -= n_in;
+      ++r;
+    }
+  }
+}
+
+template <class Core, bool SMEM_REC>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs a) {
   typedef typename Core::T T;
-  extern __shared__ __align__(16) unsigned char plan_smem[];
+  extern __shared__ __align__(16) unsigned char smem[];
   for (int i = threadIdx.x * 16; i < a.plan_bytes; i += TFK_TILE * 16)
-    *reinterpret_cast<int4 *>(plan_smem + i) = *reinterpret_cast<const int4 *>(a.plan + i);
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.plan + i);
   __syncthreads();
-  const PlanView pv = plan_view(plan_smem);
+  const PlanView pv = plan_view(smem);
   const PlanHeader &h = *pv.h;
-
-  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  const SmemLayout L = smem_layout(a.plan_bytes, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
+                    : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.fz_size;
+  rec += threadIdx.x;
   const T *q = static_cast<const T *>(a.q);
-  T *Pout = static_cast<T *>(a.P);
-  T *Jout = static_cast<T *>(a.J);
-  const long long ldP = a.ld_cfg * h.n_out;
-  const long long ldJ = ldP * h.pose_dim;
-  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+  StagedSink<T> out;
+  out.P = static_cast<T *>(a.P);
+  out.J = static_cast<T *>(a.J);
+  out.ldP = a.ld_cfg; // n_out == 1
+  out.ldJ = out.ldP * h.pose_dim;
+  out.D = h.pose_dim;
+  out.lane = lane;
+  out.stg = qs + warp * 32 * L.q_pitch; // the warp's own q rows, dead once the walk has read them
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long i0 = tile * TFK_TILE;
     const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
-    if ((int)threadIdx.x < nv) Core::phase_a(pv, q + (i0 + threadIdx.x) * h.n_in, rec + threadIdx.x, TFK_TILE);
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     __syncthreads();
-    const int items = nv * h.n_out;
-    for (int it = threadIdx.x; it < items; it += TFK_TILE) {
-      const int il = it / h.n_out;
-      const int o = it - il * h.n_out;
-      Core::phase_b(pv, rec + il, TFK_TILE, a.row0 + i0 + il, o, Pout, Jout, ldP, ldJ);
+    int nvalid = nv - warp * 32;
+    nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
+    if (nvalid > 0) {
+      const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1; // tail lanes redo the last row, store nothing
+      out.valid = (int)threadIdx.x < nv;
+      out.nvalid = nvalid;
+      out.head = a.row0 + i0 + threadIdx.x;
+      out.head0 = a.row0 + i0 + warp * 32;
+      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, out);
     }
     __syncthreads();
   }
 }
 
-template <class Core> cudaError_t launch_fk(const KernelArgs &a, int grid, cudaStream_t stream) {
-  fk_batch_kernel<Core><<<grid, TFK_TILE, a.plan_bytes, stream>>>(a);
+template <class Core>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a) {
+  typedef typename Core::T T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  for (int i = threadIdx.x * 16; i < a.plan_bytes; i += TFK_TILE * 16)
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.plan + i);
+  __syncthreads();
+  const PlanView pv = plan_view(smem);
+  const PlanHeader &h = *pv.h;
+  const SmemLayout L = smem_layout(a.plan_bytes, h.n_in, 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  const T *q = static_cast<const T *>(a.q);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  StagedSink<T> out;
+  out.P = static_cast<T *>(a.P);
+  out.J = static_cast<T *>(a.J);
+  out.ldP = a.ld_cfg * h.n_out;
+  out.ldJ = out.ldP * h.pose_dim;
+  out.D = h.pose_dim;
+  out.lane = lane;
+  out.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    __syncthreads();
+    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+    __syncthreads();
+    const int items = nv * h.n_out;
+    const long long hbase = (a.row0 + i0) * h.n_out;
+    for (int it0 = warp * 32; it0 < items; it0 += TFK_TILE) {
+      const int it = it0 + lane;
+      const int itc = it < items ? it : items - 1;
+      const int il = itc / h.n_out;
+      const int o = itc - il * h.n_out;
+      out.valid = it < items;
+      out.nvalid = items - it0 < 32 ? items - it0 : 32;
+      out.head = hbase + it;
+      out.head0 = hbase + it0;
+      Core::phase_b(pv, rec + il, TFK_TILE, o, out);
+    }
+    __syncthreads();
+  }
+}
+
+template <class Core> cudaError_t launch_fk(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream) {
+  if (variant == KV_FUSED_SMEM)
+    fk_fused_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
+  else if (variant == KV_FUSED_GMEM)
+    fk_fused_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
+  else
+    fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
   return cudaGetLastError();
 }
 
-template <class Core> cudaError_t occupancy_fk(int plan_bytes, int *blocks_per_sm) {
+template <class Core> cudaError_t occupancy_fk(int variant, int smem_bytes, int *blocks_per_sm) {
+  const void *fn = variant == KV_FUSED_SMEM   ? (const void *)fk_fused_kernel<Core, true>
+                   : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false>
+                                              : (const void *)fk_twophase_kernel<Core>;
   cudaError_t e = cudaSuccess;
-  if (plan_bytes > 48 * 1024)
-    e = cudaFuncSetAttribute(fk_batch_kernel<Core>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan_bytes);
+  if (smem_bytes > 48 * 1024) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_batch_kernel<Core>, TFK_TILE, plan_bytes);
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fn, TFK_TILE, smem_bytes);
 }
 
 } // namespace tfk

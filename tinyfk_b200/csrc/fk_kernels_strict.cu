@@ -6,10 +6,10 @@
 namespace tfk {
 typedef FkCore<MathPortable, false> CoreStrict64;
 
-cudaError_t launch_fk_f64_strict(const KernelArgs &a, int grid, cudaStream_t stream) {
-  return launch_fk<CoreStrict64>(a, grid, stream);
+cudaError_t launch_fk_f64_strict(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream) {
+  return launch_fk<CoreStrict64>(a, variant, grid, smem_bytes, stream);
 }
-cudaError_t occupancy_fk_f64_strict(int plan_bytes, int *blocks_per_sm) {
-  return occupancy_fk<CoreStrict64>(plan_bytes, blocks_per_sm);
+cudaError_t occupancy_fk_f64_strict(int variant, int smem_bytes, int *blocks_per_sm) {
+  return occupancy_fk<CoreStrict64>(variant, smem_bytes, blocks_per_sm);
 }
 } // namespace tfk

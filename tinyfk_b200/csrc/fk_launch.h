@@ -6,11 +6,19 @@
 
 #include <cuda_runtime.h>
 
+#include "fk_plan.h"
+
 namespace tfk {
 
 enum Precision {
   PREC_F64_STRICT = 0, // reference operation order, portable libm, FD base columns, no FMA contraction
   PREC_F32 = 1,        // float arithmetic, libdevice libm, analytic base-rotation columns
+};
+
+enum KernelVariant {
+  KV_FUSED_SMEM = 0, // one requested link, joint records in shared memory
+  KV_FUSED_GMEM = 1, // one requested link, records too large for shared memory: block-private global scratch
+  KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
 };
 
 struct KernelArgs {
@@ -21,13 +29,35 @@ struct KernelArgs {
   long long row0;    // global row of configuration 0 inside P / J
   long long ld_cfg;  // configurations the destination arrays are dimensioned for (ldP = ld_cfg*n_out)
   void *P, *J;       // column-major outputs (J may be null when the plan has no Jacobian)
-  void *scratch;     // grid * TFK_TILE * rec_size reals
+  void *scratch;     // grid * TFK_TILE * (rec_size | fz_size) reals (unused by KV_FUSED_SMEM)
 };
 
-cudaError_t launch_fk_f64_strict(const KernelArgs &a, int grid, cudaStream_t stream);
-cudaError_t occupancy_fk_f64_strict(int plan_bytes, int *blocks_per_sm);
-cudaError_t launch_fk_f32(const KernelArgs &a, int grid, cudaStream_t stream);
-cudaError_t occupancy_fk_f32(int plan_bytes, int *blocks_per_sm);
+// Dynamic shared memory of a block: [plan | q tile (doubles as the warps' staging strips) | records]
+struct SmemLayout {
+  int plan_bytes, q_pitch, q_off, rec_off, total;
+};
+#if defined(__CUDACC__)
+#define TFK_HDI __host__ __device__ inline
+#else
+#define TFK_HDI inline
+#endif
+// q tile pitch: odd (conflict-free 64-bit reads at one row per thread) and >= 7 so that a warp's own 32
+// rows can double as its staging strip (32 x pose_dim reals) once the angles have been consumed
+TFK_HDI int q_pitch_of(int n_in) { return (n_in < 7 ? 7 : n_in) | 1; }
+TFK_HDI SmemLayout smem_layout(int plan_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
+  SmemLayout L;
+  L.plan_bytes = (plan_bytes + 15) & ~15;
+  L.q_pitch = q_pitch_of(n_in);
+  L.q_off = L.plan_bytes;
+  L.rec_off = L.q_off + ((TFK_TILE * L.q_pitch * real_bytes + 15) & ~15);
+  L.total = L.rec_off + rec_reals_in_smem * TFK_TILE * real_bytes;
+  return L;
+}
+
+cudaError_t launch_fk_f64_strict(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream);
+cudaError_t occupancy_fk_f64_strict(int variant, int smem_bytes, int *blocks_per_sm);
+cudaError_t launch_fk_f32(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream);
+cudaError_t occupancy_fk_f32(int variant, int smem_bytes, int *blocks_per_sm);
 
 } // namespace tfk
 #endif

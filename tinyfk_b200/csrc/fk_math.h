@@ -146,6 +146,99 @@ template <class M> struct Ops {
     return r;
   }
 
+  // ---- sparsity-aware pieces of Rotation::operator*(Vector3) (pose.h:265-282) -------------------
+  // rotate(q, v) = xyz( q * ((v,0) * inv) ) with inv = GetInverse(q).  The two Hamilton products are
+  // split so that (a) `inv` can be kept while q does not change (the reference recomputes it per
+  // call: same operands, same bits) and (b) products whose constant factor is an exact zero are not
+  // evaluated (fk_plan.h "sparsity classes"; only the sign of an exact zero can differ).
+
+  // (v,0) * i for v = (vx,0,0) / (0,vy,0) / (0,0,vz) / dense
+  static TFK_FN Q vq_x(T vx, const Q &i) {
+    Q t;
+    t.x = vx * i.w;
+    t.y = -(vx * i.z);
+    t.z = vx * i.y;
+    t.w = -(vx * i.x);
+    return t;
+  }
+  static TFK_FN Q vq_y(T vy, const Q &i) {
+    Q t;
+    t.x = vy * i.z;
+    t.y = vy * i.w;
+    t.z = -(vy * i.x);
+    t.w = -(vy * i.y);
+    return t;
+  }
+  static TFK_FN Q vq_z(T vz, const Q &i) {
+    Q t;
+    t.x = -(vz * i.y);
+    t.y = vz * i.x;
+    t.z = vz * i.w;
+    t.w = -(vz * i.z);
+    return t;
+  }
+  static TFK_FN Q vq_full(const V &v, const Q &i) {
+    Q t;
+    t.x = v.x * i.w + v.y * i.z - v.z * i.y;
+    t.y = -(v.x * i.z) + v.y * i.w + v.z * i.x;
+    t.z = v.x * i.y - v.y * i.x + v.z * i.w;
+    t.w = -(v.x * i.x) - v.y * i.y - v.z * i.z;
+    return t;
+  }
+  // cls: V_X = 1, V_Y = 2, V_Z = 3, anything else dense (fk_plan.h)
+  static TFK_FN Q vq(int cls, const V &v, const Q &i) {
+    if (cls == 1) return vq_x(v.x, i);
+    if (cls == 2) return vq_y(v.y, i);
+    if (cls == 3) return vq_z(v.z, i);
+    return vq_full(v, i);
+  }
+  // xyz part of q * t
+  static TFK_FN V qt_xyz(const Q &q, const Q &t) {
+    V r;
+    r.x = q.w * t.x + q.x * t.w + q.y * t.z - q.z * t.y;
+    r.y = q.w * t.y - q.x * t.z + q.y * t.w + q.z * t.x;
+    r.z = q.w * t.z + q.x * t.y - q.y * t.x + q.z * t.w;
+    return r;
+  }
+
+  // Rotation::operator*(Rotation) (pose.h:253-263) with b = (bx,0,0,bw) / (0,by,0,bw) / (0,0,bz,bw)
+  static TFK_FN Q qmul_bx(const Q &a, T bx, T bw) {
+    Q c;
+    c.x = a.w * bx + a.x * bw;
+    c.y = a.y * bw + a.z * bx;
+    c.z = -(a.y * bx) + a.z * bw;
+    c.w = a.w * bw - a.x * bx;
+    return c;
+  }
+  static TFK_FN Q qmul_by(const Q &a, T by, T bw) {
+    Q c;
+    c.x = a.x * bw - a.z * by;
+    c.y = a.w * by + a.y * bw;
+    c.z = a.x * by + a.z * bw;
+    c.w = a.w * bw - a.y * by;
+    return c;
+  }
+  static TFK_FN Q qmul_bz(const Q &a, T bz, T bw) {
+    Q c;
+    c.x = a.x * bw + a.y * bz;
+    c.y = -(a.x * bz) + a.y * bw;
+    c.z = a.w * bz + a.z * bw;
+    c.w = a.w * bw - a.z * bz;
+    return c;
+  }
+  // a * (axis*s, c) where axis has class cls
+  static TFK_FN Q qmul_axis(const Q &a, int cls, const V &axis, T s, T c) {
+    if (cls == 1) return qmul_bx(a, axis.x * s, c);
+    if (cls == 2) return qmul_by(a, axis.y * s, c);
+    if (cls == 3) return qmul_bz(a, axis.z * s, c);
+    Q b;
+    b.x = axis.x * s;
+    b.y = axis.y * s;
+    b.z = axis.z * s;
+    b.w = c;
+    return qmul(a, b);
+  }
+
   // urdf::pose_transform, pose.cpp:139-146
   static TFK_FN P compose(const P &a, const P &b) {
     P o;

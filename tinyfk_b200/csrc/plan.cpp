@@ -16,11 +16,50 @@ struct Builder {
   std::vector<int> qcol_of_joint; // per joint id: last column that names it, or -1
   std::vector<int> slot_of_link;  // per link
   std::vector<PlanSlot> slots;
+  std::vector<int> parent_slot;   // per slot: slot of the parent link, -1 when the parent is the root
   int frames_live, frames_max;
 
   Builder(const KinematicModel &model, const PlanKey &k)
       : m(model), key(k), needed(model.n_links(), 0), qcol_of_joint(model.n_joints(), -1),
         slot_of_link(model.n_links(), -1), frames_live(0), frames_max(0) {}
+
+  static int vclass(double x, double y, double z) {
+    const int nz = (x != 0.0) + (y != 0.0) + (z != 0.0);
+    if (nz == 0) return V_NONE;
+    if (nz > 1) return V_FULL;
+    return x != 0.0 ? V_X : (y != 0.0 ? V_Y : V_Z);
+  }
+
+  // sparsity classes of the slot's constants (fk_plan.h); every test is an exact comparison
+  static void classify(PlanSlot &s) {
+    const bool oq_ident = s.oquat[0] == 0.0 && s.oquat[1] == 0.0 && s.oquat[2] == 0.0 && s.oquat[3] == 1.0;
+    s.axc = vclass(s.axis[0], s.axis[1], s.axis[2]);
+    s.flags = 0;
+    {
+      // GetInverse(oquat), pose.h:284-299, with the host's own IEEE arithmetic (same bits as the device)
+      Quat<double> oq;
+      oq.x = s.oquat[0], oq.y = s.oquat[1], oq.z = s.oquat[2], oq.w = s.oquat[3];
+      const Quat<double> oi = Ops<MathPortable>::qget_inverse(oq);
+      s.oinv[0] = oi.x, s.oinv[1] = oi.y, s.oinv[2] = oi.z, s.oinv[3] = oi.w;
+    }
+    if (s.kind == SLOT_FIXED) {
+      s.rot = oq_ident ? ROT_NONE : ROT_CONST;
+      s.trn = vclass(s.opos[0], s.opos[1], s.opos[2]);
+    } else if (s.kind == SLOT_REVOLUTE) {
+      s.rot = oq_ident ? ROT_REV : ROT_REV_OQ;
+      s.trn = vclass(s.opos[0], s.opos[1], s.opos[2]);
+    } else { // prismatic: local = pose_transform(origin, (identity, axis*d))
+      s.rot = oq_ident ? ROT_NONE : ROT_CONST;
+      if (oq_ident) {
+        // rotate(identity, v) == v exactly, so local.p[k] = axis[k]*d + opos[k]
+        s.trn = vclass((s.opos[0] != 0.0) || (s.axis[0] != 0.0), (s.opos[1] != 0.0) || (s.axis[1] != 0.0),
+                       (s.opos[2] != 0.0) || (s.axis[2] != 0.0));
+      } else {
+        s.trn = V_FULL;
+        s.flags |= SF_PRISM_OQ;
+      }
+    }
+  }
 
   void visit(int u, int frame_ld) {
     const LinkRec &l = m.links()[u];
@@ -29,7 +68,8 @@ struct Builder {
     s.qcol = -1;
     s.frame_ld = frame_ld;
     s.frame_st = -1;
-    s.jrec = -1;
+    s.arec = -1;
+    s.prec = -1;
     s.lrec = -1;
     const bool selected = l.jid >= 0 && qcol_of_joint[l.jid] >= 0;
     Pose64 local;
@@ -52,6 +92,7 @@ struct Builder {
     s.axis[0] = l.axis.x;
     s.axis[1] = l.axis.y;
     s.axis[2] = l.axis.z;
+    classify(s);
 
     int n_children = 0;
     for (int c : l.children)
@@ -62,6 +103,7 @@ struct Builder {
     }
     slot_of_link[u] = (int)slots.size();
     slots.push_back(s);
+    parent_slot.push_back(l.parent >= 0 ? slot_of_link[l.parent] : -1);
     const int my_frame = s.frame_st;
     bool first = true;
     for (int c : l.children) {
@@ -102,23 +144,59 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
                                 std::to_string(b.frames_max) + " > " + std::to_string((int)TFK_MAX_FRAMES) + ")");
 
   const bool jac = key.with_jacobian != 0;
-  // joint records: one per selected joint whose child link is on a requested chain
-  int n_jrec = 0;
-  std::vector<int> jrec_of_joint(model.n_joints(), -1);
+  // joint records: a world-axis record per selected joint whose child link is on a requested chain and
+  // a position record per distinct joint position (a joint whose local translation is exactly zero sits
+  // where its parent link sits: o.p = 0 + a.p, so co-located joints share one record)
+  int n_arec = 0, n_prec = 0;
+  std::vector<int> arec_of_joint(model.n_joints(), -1), prec_of_joint(model.n_joints(), -1);
   std::vector<PlanCol> cols(n_cols);
   if (jac) {
-    for (size_t s = 0; s < b.slots.size(); ++s) {
-      if (b.slots[s].kind == SLOT_FIXED) continue;
-      b.slots[s].jrec = n_jrec++;
+    const int ns = (int)b.slots.size();
+    std::vector<int> cls(ns), prec_of_cls(ns, -1);
+    for (int s = 0; s < ns; ++s)
+      cls[s] = (b.slots[s].trn == V_NONE && b.parent_slot[s] >= 0) ? cls[b.parent_slot[s]] : s;
+    for (int s = 0; s < ns; ++s) {
+      PlanSlot &sl = b.slots[s];
+      if (sl.kind == SLOT_FIXED) continue;
+      sl.arec = n_arec++;
+      if (sl.kind == SLOT_REVOLUTE) {
+        if (prec_of_cls[cls[s]] < 0) {
+          prec_of_cls[cls[s]] = n_prec++;
+          sl.prec = prec_of_cls[cls[s]]; // the first joint of the class writes the record
+        }
+      }
     }
     for (size_t l = 0; l < links.size(); ++l) {
-      int s = b.slot_of_link[l];
-      if (s >= 0 && b.slots[s].jrec >= 0) jrec_of_joint[links[l].jid] = b.slots[s].jrec;
+      const int s = b.slot_of_link[l];
+      if (s < 0 || b.slots[s].arec < 0) continue;
+      arec_of_joint[links[l].jid] = b.slots[s].arec;
+      prec_of_joint[links[l].jid] = b.slots[s].kind == SLOT_REVOLUTE ? prec_of_cls[cls[s]] : -1;
     }
   }
   for (int c = 0; c < n_cols; ++c) {
-    cols[c].jrec = jac ? jrec_of_joint[key.joint_ids[c]] : -1;
+    cols[c].arec = jac ? arec_of_joint[key.joint_ids[c]] : -1;
+    cols[c].prec = jac ? prec_of_joint[key.joint_ids[c]] : -1;
     cols[c].prismatic = model.joints()[key.joint_ids[c]].type == JT_PRISMATIC ? 1 : 0;
+    cols[c].pad_ = 0;
+  }
+
+  // running-inverse bookkeeping: `inv` = GetInverse(q of the running frame) is computed only where a
+  // vector rotation needs it and it is not already there (the reference recomputes it in every
+  // Rotation::operator*(Vector3), pose.h:265-282; same operands, same bits)
+  {
+    bool valid = false;
+    for (PlanSlot &sl : b.slots) {
+      if (sl.frame_ld != FRAME_RUNNING) valid = false;
+      if (sl.trn != V_NONE) {
+        if (!valid) sl.flags |= SF_INV_BEFORE;
+        valid = true;
+      }
+      if (sl.rot != ROT_NONE) valid = false;
+      if (sl.arec >= 0) {
+        if (!valid) sl.flags |= SF_INV_AFTER;
+        valid = true;
+      }
+    }
   }
 
   // link records: one per distinct requested link
@@ -149,7 +227,8 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.n_slots = (int)b.slots.size();
   h.n_out = n_out;
   h.n_cols = n_cols;
-  h.n_jrec = n_jrec;
+  h.n_arec = n_arec;
+  h.n_prec = n_prec;
   h.n_lrec = n_lrec;
   h.rot_type = key.rot_type;
   h.base_type = key.base_type;
@@ -162,9 +241,16 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.lrec_size = key.rot_type == ROT_IGNORE ? 3 : 7;
   h.off_base = 0;
   const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 0;
-  h.off_jrec = h.off_base + base_rec;
-  h.off_lrec = h.off_jrec + 6 * n_jrec;
-  h.rec_size = h.off_lrec + h.lrec_size * n_lrec;
+  h.off_arec = h.off_base + base_rec;
+  h.off_prec = h.off_arec + 3 * n_arec;
+  h.off_lrec = h.off_prec + 3 * n_prec;
+  h.off_frame = h.off_lrec + h.lrec_size * n_lrec;
+  h.rec_size = h.off_frame + 7 * b.frames_max;
+  // fused single-link kernel: the link pose and the base context stay in registers
+  h.fz_arec = base_rec ? 7 : 0;
+  h.fz_prec = h.fz_arec + 3 * n_arec;
+  h.fz_frame = h.fz_prec + 3 * n_prec;
+  h.fz_size = h.fz_frame + 7 * b.frames_max;
   h.root_lrec = root_lrec;
   h.mask_words = mask_words;
   h.n_frames = b.frames_max;
