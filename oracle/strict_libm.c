@@ -24,3 +24,9 @@ void tfkm_cos_v(const double *x, double *o, long n) { for (long i = 0; i < n; ++
 void tfkm_asin_v(const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_asin(x[i]); }
 void tfkm_atan2_v(const double *y, const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_atan2(y[i], x[i]); }
 void tfkm_sincos_v(const double *x, double *s, double *c, long n) { for (long i = 0; i < n; ++i) tfk_sincos(x[i], s + i, c + i); }
+
+/* SIMT-restructured variants (tinyfk_b200/csrc/fkmath_simt.h): must be bit-identical to the above */
+#include "../tinyfk_b200/csrc/fkmath_simt.h"
+void tfkm_sincos_simt_v(const double *x, double *s, double *c, long n) { for (long i = 0; i < n; ++i) { TfkSinCos r = tfk_sincos_simt(x[i]); s[i] = r.s; c[i] = r.c; } }
+void tfkm_asin_simt_v(const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_asin_simt(x[i]); }
+void tfkm_atan2_simt_v(const double *y, const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_atan2_simt(y[i], x[i]); }

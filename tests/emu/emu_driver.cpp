@@ -17,6 +17,12 @@ using namespace tfk;
 
 static thread_local std::string g_err;
 
+template <class T> struct DirectFactory { // the fused driver builds its sink after the walk
+  typedef DirectSink<T> Sink;
+  DirectSink<T> proto;
+  Sink make() const { return proto; }
+};
+
 template <class Core, class T>
 static void run(const std::vector<unsigned char> &blob, const double *qs, long n, double *Pd, double *Jd, bool two_phase) {
   PlanView pv = plan_view(blob.data());
@@ -36,7 +42,9 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
     for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
     if (fused) {
       out.head = i;
-      Core::run_fused(pv, qrow.data(), rec.data(), 1, out);
+      DirectFactory<T> f;
+      f.proto = out;
+      Core::run_fused(pv, qrow.data(), rec.data(), 1, f);
     } else {
       Core::phase_a(pv, qrow.data(), rec.data(), 1);
       for (int o = 0; o < h.n_out; ++o) {
@@ -51,6 +59,10 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
 }
 
 extern "C" {
+// MathPortable::div_ (shared-reciprocal IEEE division, fk_math.h) on arrays: must equal a[i] / b[i]
+void emu_div(const double *a, const double *b, double *o, long n) {
+  for (long i = 0; i < n; ++i) o[i] = MathPortable::div_(a[i], MathPortable::den_(b[i]));
+}
 const char *emu_last_error() { return g_err.c_str(); }
 
 void *emu_create(const char *xml, int system_libm) {

@@ -90,3 +90,76 @@ def test_atan2_below_two_ulp_and_special_values(lib):
     lib.tfkm_atan2_v(sy.ctypes.data_as(_dp), sx.ctypes.data_as(_dp), so.ctypes.data_as(_dp), ctypes.c_long(sx.size))
     g = np.arctan2(sy, sx)
     assert np.allclose(so, g, rtol=0, atol=3e-16) and (np.signbit(so) == np.signbit(g)).all()
+
+
+def _special_doubles():
+    return np.array([0.0, -0.0, 1.0, -1.0, 0.5, -0.5, 0.3, 0.78125, 0.7853981633974483, 0.7853981633974484, 0.975,
+                     0.4375, 0.6875, 1.1875, 2.4375, 1e-300, -1e-300, 5e-324, 1e300, np.inf, -np.inf, np.nan,
+                     7.450580596923828125e-9, 1.862645149230957e-9, 1647099.0, 1646592.0, 2.0 ** 66, 2.0 ** -29,
+                     math.pi, -math.pi, math.pi / 2, 3 * math.pi / 2, 1e6, -1e6, 2.7e11, 1.0 - 2 ** -53, 1.0 + 2 ** -52])
+
+
+def _bits_equal(a, b):
+    return np.array_equal(np.asarray(a).view(np.uint64), np.asarray(b).view(np.uint64))
+
+
+def test_simt_variants_are_bit_identical(lib):
+    """fkmath_simt.h (what the kernels run) against fkmath.h (what the pinned reference links): same bits,
+    including signs of zeros and NaN payload-free specials."""
+    rng = np.random.default_rng(11)
+    sp = _special_doubles()
+    n = 2_000_000
+    x = np.concatenate([rng.uniform(-3.2, 3.2, n), rng.uniform(-0.8, 0.8, n // 4), rng.uniform(-1e6, 1e6, n // 4),
+                        rng.uniform(-3e11, 3e11, 10000), rng.normal(size=n // 4) * 10.0 ** rng.integers(-12, 3, n // 4),
+                        np.concatenate([k * math.pi / 2 + rng.uniform(-1e-9, 1e-9, 200) for k in range(-40, 41)]), sp])
+    s0, c0, s1, c1 = (np.empty_like(x) for _ in range(4))
+    lib.tfkm_sincos_v(x.ctypes.data_as(_dp), s0.ctypes.data_as(_dp), c0.ctypes.data_as(_dp), ctypes.c_long(x.size))
+    lib.tfkm_sincos_simt_v(x.ctypes.data_as(_dp), s1.ctypes.data_as(_dp), c1.ctypes.data_as(_dp), ctypes.c_long(x.size))
+    nn = ~np.isnan(s0)
+    assert _bits_equal(s0[nn], s1[nn]) and _bits_equal(c0[nn], c1[nn]) and np.isnan(s1[~nn]).all() and np.isnan(c1[~nn]).all()
+
+    x = np.concatenate([rng.uniform(-1, 1, n), rng.uniform(0.9, 1.0, n // 4), -rng.uniform(0.4, 0.6, n // 4),
+                        rng.normal(size=n // 4) * 10.0 ** rng.integers(-12, 0, n // 4), sp])
+    a0, a1 = _call1(lib, "tfkm_asin_v", x), _call1(lib, "tfkm_asin_simt_v", x)
+    nn = ~np.isnan(a0)
+    assert _bits_equal(a0[nn], a1[nn]) and np.isnan(a1[~nn]).all()
+
+    y = np.concatenate([rng.normal(size=n), rng.normal(size=n // 2) * 10.0 ** rng.integers(-20, 20, n // 2),
+                        rng.uniform(-1, 1, n // 2), np.repeat(sp, sp.size)])
+    x = np.concatenate([rng.normal(size=n), rng.normal(size=n // 2) * 10.0 ** rng.integers(-20, 20, n // 2),
+                        rng.uniform(0.4, 2.5, n // 2) * rng.choice([-1, 1], n // 2), np.tile(sp, sp.size)])
+    # interval edges of atan: |y/x| right at the thresholds
+    for thr in (0.4375, 0.6875, 1.1875, 2.4375):
+        xe = rng.uniform(0.5, 2.0, 2000)
+        y = np.concatenate([y, xe * thr, np.nextafter(xe * thr, 0), np.nextafter(xe * thr, 9)])
+        x = np.concatenate([x, xe, xe, xe])
+    o0, o1 = np.empty_like(x), np.empty_like(x)
+    lib.tfkm_atan2_v(y.ctypes.data_as(_dp), x.ctypes.data_as(_dp), o0.ctypes.data_as(_dp), ctypes.c_long(x.size))
+    lib.tfkm_atan2_simt_v(y.ctypes.data_as(_dp), x.ctypes.data_as(_dp), o1.ctypes.data_as(_dp), ctypes.c_long(x.size))
+    nn = ~np.isnan(o0)
+    assert _bits_equal(o0[nn], o1[nn]) and np.isnan(o1[~nn]).all()
+
+
+def test_shared_reciprocal_division_is_ieee_division():
+    """MathPortable::div_ (fk_math.h: one correctly rounded reciprocal + two FMA residual corrections per
+    quotient) against the hardware division, bit for bit -- random operands, denominators within a few
+    ulp of 1 (quaternion norms), the constant 1e-7, tiny / huge / zero / non-finite operands."""
+    import emuapi
+    L = emuapi.lib()
+    L.emu_div.argtypes = [_dp, _dp, _dp, ctypes.c_long]
+    rng = np.random.default_rng(12)
+    n = 4_000_000
+    one = 1.0 + rng.integers(-64, 64, n) * 2.0 ** -53
+    sp = _special_doubles()
+    a = np.concatenate([rng.uniform(-1, 1, n), rng.uniform(-1, 1, n), rng.normal(size=n) * 1e-8,
+                        rng.normal(size=n) * 10.0 ** rng.integers(-300, 300, n), np.repeat(sp, sp.size)])
+    b = np.concatenate([one, rng.uniform(0.5, 2.0, n), np.full(n, 1e-7),
+                        rng.normal(size=n) * 10.0 ** rng.integers(-300, 300, n), np.tile(sp, sp.size)])
+    o = np.empty_like(a)
+    L.emu_div(a.ctypes.data_as(_dp), b.ctypes.data_as(_dp), o.ctypes.data_as(_dp), ctypes.c_long(a.size))
+    with np.errstate(all="ignore"):
+        ref = a / b
+    nn = ~np.isnan(ref)
+    # an exact-zero quotient may differ in sign only where the numerator is an exact zero (DESIGN.md)
+    same = o[nn].view(np.uint64) == ref[nn].view(np.uint64)
+    assert (same | ((o[nn] == 0) & (ref[nn] == 0))).all() and np.isnan(o[~nn]).all()

@@ -24,6 +24,14 @@
 #include "fk_math.h"
 #include "fk_plan.h"
 
+#if defined(__CUDACC__)
+#define TFK_UNROLL _Pragma("unroll")
+#define TFK_NOUNROLL _Pragma("unroll 1")
+#else
+#define TFK_UNROLL
+#define TFK_NOUNROLL
+#endif
+
 namespace tfk {
 
 // Views into a plan blob (host memory on the CPU, shared memory on the GPU).
@@ -68,14 +76,6 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
   typedef Vec3<T> V;
   typedef Quat<T> Q;
   typedef PoseT<T> P;
-
-  // what the base columns of the Jacobian need, derived once per configuration from the base pose
-  struct BaseCtx {
-    P base;
-    P binv;  // strict: Pose::inverse of the base pose (src/kinematics.cpp:186)
-    Q bk[3]; // strict: setFromRPY(rpy_b + eps*e_k) (src/kinematics.cpp:205-210)
-    V w[3];  // analytic: world angular-velocity axes of roll, pitch, yaw
-  };
 
   static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
     rec[(at + 0) * stride] = a.p.x;
@@ -157,8 +157,9 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       if (n == T(0)) {
         base.q = O::qidentity();
       } else {
-        base.q.z = s / n;
-        base.q.w = c / n;
+        const typename M::Den d = M::den_(n);
+        base.q.z = M::div_(s, d);
+        base.q.w = M::div_(c, d);
       }
     } else {
       base.p.z = b[2];
@@ -167,73 +168,94 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     return base;
   }
 
-  // src/kinematics.cpp:186-187,201-210 hoisted out of the per-link loop (same operands per link)
-  static TFK_FN void make_base_ctx(const PlanHeader &h, const P &base, BaseCtx &c) {
-    c.base = base;
-    const V rpy_b = O::to_rpy(base.q); // src/kinematics.cpp:187
-    if (ANALYTIC_BASE) {
-      // world angular-velocity axes of roll, pitch, yaw for R = Rz(yaw) Ry(pitch) Rx(roll)
-      T sp, cp, sy, cy;
-      M::sincos_(rpy_b.y, &sp, &cp);
-      M::sincos_(rpy_b.z, &sy, &cy);
-      c.w[0].x = cy * cp;
-      c.w[0].y = sy * cp;
-      c.w[0].z = -sp;
-      c.w[1].x = -sy;
-      c.w[1].y = cy;
-      c.w[1].z = T(0);
-      c.w[2].x = T(0);
-      c.w[2].y = T(0);
-      c.w[2].z = T(1);
-      return;
-    }
-    c.binv = O::inverse(base); // src/kinematics.cpp:186
-    const T eps = T(1e-7);     // src/kinematics.cpp:201
-    for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) {
-      V t = rpy_b;
-      if (k == 0) t.x += eps;
-      if (k == 1) t.y += eps;
-      if (k == 2) t.z += eps;
-      c.bk[k] = O::from_rpy(t.x, t.y, t.z); // src/kinematics.cpp:205-210
-    }
+  // ---------------------------------------------------------------------------------------------
+  // What the base columns of the Jacobian need (src/kinematics.cpp:182-232), derived from the base
+  // pose.  The reference recomputes all of it per link; the operands are the same for every link of a
+  // configuration, so hoisting is exact.
+  //   strict:   rpy_b = getRPY(base) (:187), binv = Pose::inverse(base) (:186),
+  //             bk[k] = setFromRPY(rpy_b + eps*e_k) (:201-210)
+  //   analytic: world angular-velocity axes of roll, pitch, yaw for R = Rz(yaw) Ry(pitch) Rx(roll)
+  static TFK_FN Q tweaked_rotation(const V &rpy_b, int k) {
+    const T eps = T(1e-7); // src/kinematics.cpp:201
+    V t = rpy_b;
+    if (k == 0) t.x += eps;
+    if (k == 1) t.y += eps;
+    if (k == 2) t.z += eps;
+    return O::from_rpy(t.x, t.y, t.z);
+  }
+  static TFK_FN void analytic_axes(const V &rpy_b, V (&w)[3]) {
+    T sp, cp, sy, cy;
+    M::sincos_(rpy_b.y, &sp, &cp);
+    M::sincos_(rpy_b.z, &sy, &cy);
+    w[0].x = cy * cp;
+    w[0].y = sy * cp;
+    w[0].z = -sp;
+    w[1].x = -sy;
+    w[1].y = cy;
+    w[1].z = T(0);
+    w[2].x = T(0);
+    w[2].y = T(0);
+    w[2].z = T(1);
   }
 
-  static TFK_FN void store_base_ctx(const PlanHeader &h, const BaseCtx &c, T *rec, int stride) {
-    put_pose(rec, stride, h.off_base, c.base);
+  // two-phase: phase A stores the context once per configuration, phase B reads what it needs, late
+  static TFK_FN void store_base_ctx(const PlanHeader &h, const P &base, T *rec, int stride) {
+    const V rpy_b = O::to_rpy(base.q);
     if (ANALYTIC_BASE) {
-      for (int k = 0; k < 3; ++k) put_vec(rec, stride, h.off_base + 7 + 3 * k, c.w[k]);
-    } else {
-      put_pose(rec, stride, h.off_base + 7, c.binv);
-      for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) put_quat(rec, stride, h.off_base + 14 + 4 * k, c.bk[k]);
+      V w[3];
+      analytic_axes(rpy_b, w);
+      TFK_UNROLL
+      for (int k = 0; k < 3; ++k) put_vec(rec, stride, h.off_base + 7 + 3 * k, w[k]);
+      return;
     }
+    put_pose(rec, stride, h.off_base + 7, O::inverse(base));
+    TFK_NOUNROLL
+    for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k)
+      put_quat(rec, stride, h.off_base + 14 + 4 * k, tweaked_rotation(rpy_b, k));
   }
-  static TFK_FN void load_base_ctx(const PlanHeader &h, const T *rec, int stride, BaseCtx &c) {
-    c.base = get_pose(rec, stride, h.off_base);
-    if (ANALYTIC_BASE) {
-      for (int k = 0; k < 3; ++k) c.w[k] = get_vec(rec, stride, h.off_base + 7 + 3 * k);
-    } else {
-      c.binv = get_pose(rec, stride, h.off_base + 7);
-      for (int k = (h.base_type == 1 ? 2 : 0); k < 3; ++k) c.bk[k] = get_quat(rec, stride, h.off_base + 14 + 4 * k);
+  struct BaseFromRec {
+    const T *rec;
+    int stride, at;
+    TFK_FN void prepare() {}
+    TFK_FN V base_p() const { return get_vec(rec, stride, at); }
+    TFK_FN P binv() const { return get_pose(rec, stride, at + 7); }
+    TFK_FN Q bk(int k) const { return get_quat(rec, stride, at + 14 + 4 * k); }
+    TFK_FN V w(int k) const { return get_vec(rec, stride, at + 7 + 3 * k); }
+  };
+  // fused: one link per configuration, so everything is computed where it is used; only the base
+  // pose itself is re-read from the record
+  struct BaseComputed {
+    const T *rec;
+    int stride;
+    P b;
+    V rpy_b;
+    V wk[3];
+    TFK_FN void prepare() {
+      b = get_pose(rec, stride, 0);
+      rpy_b = O::to_rpy(b.q);
+      if (ANALYTIC_BASE) analytic_axes(rpy_b, wk);
     }
-  }
+    TFK_FN V base_p() const { return b.p; }
+    TFK_FN P binv() const { return O::inverse(b); }
+    TFK_FN Q bk(int k) const { return tweaked_rotation(rpy_b, k); }
+    TFK_FN V w(int k) const { return (k == 0) ? wk[0] : ((k == 1) ? wk[1] : wk[2]); }
+  };
 
   // ---------------------------------------------------------------------------------------------
   // One pass down the tree.  qrow: this configuration's input row.  rec: this configuration's records
-  // (element k at rec[k*stride]); o_arec / o_prec / o_frame: where the axis, position and frame records
-  // start.  sink.link(lrec, pose) is called for every requested link, in tree order.
+  // (element k at rec[k*stride]); o_base / o_arec / o_prec / o_frame: where the base pose (already
+  // stored by the caller), axis, position and frame records are.  sink.link(lrec, pose) is called for
+  // every requested link, in tree order.  Returns the pose of the last slot.
   template <class LinkSink>
-  static TFK_FN void walk(const PlanView &pv, const T *qrow, T *rec, int stride, int o_arec, int o_prec, int o_frame,
-                          const P &base, LinkSink &sink) {
+  static TFK_FN P walk(const PlanView &pv, const T *qrow, T *rec, int stride, int o_base, int o_arec, int o_prec,
+                       int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
-    P cur = base;
     Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
+    TFK_NOUNROLL
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
-      if (sl.frame_ld == FRAME_BASE) {
-        cur = base;
-      } else if (sl.frame_ld != FRAME_RUNNING) {
-        cur = get_pose(rec, stride, o_frame + 7 * sl.frame_ld);
-      }
+      if (sl.frame_ld != FRAME_RUNNING) // a child of the root, or the second.. child of a branch point
+        cur = get_pose(rec, stride, sl.frame_ld == FRAME_BASE ? o_base : o_frame + 7 * sl.frame_ld);
       // pose_transform(parent, local), pose.cpp:139-146: position first (it uses the parent's rotation)
       T ang = T(0);
       if (sl.kind != SLOT_FIXED) ang = qrow[sl.qcol];
@@ -267,9 +289,9 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
         cur.p.z = r.z + cur.p.z;
       }
       if (sl.rot != ROT_NONE) {
+        Q oq;
+        oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
         if (sl.rot == ROT_CONST) {
-          Q oq;
-          oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
           cur.q = O::qmul(cur.q, oq);
         } else {
           // Joint::transform for REVOLUTE/CONTINUOUS, joint.h:231-240 (axis is NOT normalised)
@@ -277,13 +299,10 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
           M::sincos_(ang * T(0.5), &sn, &cs);
           V ax;
           ax.x = T(sl.axis[0]), ax.y = T(sl.axis[1]), ax.z = T(sl.axis[2]);
-          if (sl.rot == ROT_REV) {
+          if (sl.rot == ROT_REV)
             cur.q = O::qmul_axis(cur.q, sl.axc, ax, sn, cs);
-          } else {
-            Q oq;
-            oq.x = T(sl.oquat[0]), oq.y = T(sl.oquat[1]), oq.z = T(sl.oquat[2]), oq.w = T(sl.oquat[3]);
+          else
             cur.q = O::qmul(cur.q, O::qmul_axis(oq, sl.axc, ax, sn, cs));
-          }
         }
       }
       if (sl.frame_st >= 0) put_pose(rec, stride, o_frame + 7 * sl.frame_st, cur);
@@ -296,16 +315,19 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       }
       if (sl.lrec >= 0) sink.link(sl.lrec, cur);
     }
+    return cur;
   }
 
   // ---------------------------------------------------------------------------------------------
   // One (configuration, requested link) pair: pose row (src/wrapper.cpp:98-112) and Jacobian
   // (src/kinematics.cpp:105-235).  e: the link's pose; o: index into elink_ids; rec/o_arec/o_prec: the
-  // configuration's joint records; ctx: base context (only read with a moving base and a Jacobian).
-  // `out` gets put_P(d, value) and put_J(column, values[pose_dim]) -- every entry of J is written.
-  template <class OutSink>
+  // configuration's joint records; bs: where the base context comes from (only touched with a moving
+  // base and a Jacobian, and only after the joint columns, to keep few values live).
+  // `out` gets put_P(d, value) and put_J(column, values[pose_dim]); columns arrive in increasing
+  // order and every entry of J is written.
+  template <class BaseSrc, class OutSink>
   static TFK_FN void emit_link(const PlanView &pv, const P &e, int o, const T *rec, int stride, int o_arec, int o_prec,
-                               const BaseCtx &ctx, OutSink &out) {
+                               BaseSrc &bs, OutSink &out) {
     const PlanHeader &h = *pv.h;
     out.begin();
     out.put_P(0, e.p.x);
@@ -334,6 +356,7 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
 
     // joint columns, src/kinematics.cpp:131-180
     const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
+    TFK_NOUNROLL
     for (int c = 0; c < h.n_cols; ++c) {
       T v[7];
       v[0] = v[1] = v[2] = v[3] = v[4] = v[5] = v[6] = T(0);
@@ -375,6 +398,7 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     if (h.base_type == 0) return;
     // base translation columns, src/kinematics.cpp:194-196
     const int n_trans = (h.base_type == 1) ? 2 : 3;
+    TFK_NOUNROLL
     for (int k = 0; k < n_trans; ++k) {
       T v[7];
       v[0] = (k == 0) ? T(1) : T(0);
@@ -384,17 +408,19 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       out.put_J(h.n_cols + k, v);
     }
     // base rotation columns: FLOATING keeps roll, pitch, yaw; PLANER keeps yaw only
-    const P &base = ctx.base;
+    bs.prepare();
+    const V base_p = bs.base_p();
     const int k0 = (h.base_type == 1) ? 2 : 0;
     if (ANALYTIC_BASE) {
       V d;
-      d.x = e.p.x - base.p.x;
-      d.y = e.p.y - base.p.y;
-      d.z = e.p.z - base.p.z;
+      d.x = e.p.x - base_p.x;
+      d.y = e.p.y - base_p.y;
+      d.z = e.p.z - base_p.z;
+      TFK_NOUNROLL
       for (int k = k0; k < 3; ++k) {
         T v[7];
         v[6] = T(0);
-        const V w = ctx.w[k];
+        const V w = bs.w(k);
         const V dpos = O::cross(w, d);
         v[0] = dpos.x;
         v[1] = dpos.y;
@@ -417,22 +443,25 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       return;
     }
     // forward finite difference replica, src/kinematics.cpp:182-232
-    const T eps = T(1e-7);
-    const P &binv = ctx.binv;
+    const typename M::Den deps = M::den_(T(1e-7));
     P be; // tf_blink_to_elink = pose_transform(tf_blink_to_rlink, tf_rlink_to_elink)
-    if (h.lrec_size == 7) {
-      be = O::compose(binv, e);
-    } else { // IGNORE: only the position rows exist and they never read the link rotation
-      const V r = O::rotate(binv.q, e.p);
-      be.p.x = r.x + binv.p.x;
-      be.p.y = r.y + binv.p.y;
-      be.p.z = r.z + binv.p.z;
-      be.q = O::qidentity();
+    {
+      const P binv = bs.binv();
+      if (h.lrec_size == 7) {
+        be = O::compose(binv, e);
+      } else { // IGNORE: only the position rows exist and they never read the link rotation
+        const V r = O::rotate(binv.q, e.p);
+        be.p.x = r.x + binv.p.x;
+        be.p.y = r.y + binv.p.y;
+        be.p.z = r.z + binv.p.z;
+        be.q = O::qidentity();
+      }
     }
-    for (int k = k0; k < 3; ++k) {
+    TFK_NOUNROLL
+    for (int k = k0; k < 3; ++k) { // one copy of the code
       P bk;
-      bk.p = base.p;
-      bk.q = ctx.bk[k];
+      bk.p = base_p;
+      bk.q = bs.bk(k);
       V pk;
       Q qk = O::qidentity();
       if (h.lrec_size == 7) {
@@ -447,19 +476,19 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       }
       T v[7];
       v[3] = v[4] = v[5] = v[6] = T(0);
-      v[0] = (pk.x - e.p.x) / eps;
-      v[1] = (pk.y - e.p.y) / eps;
-      v[2] = (pk.z - e.p.z) / eps;
+      v[0] = M::div_(pk.x - e.p.x, deps);
+      v[1] = M::div_(pk.y - e.p.y, deps);
+      v[2] = M::div_(pk.z - e.p.z, deps);
       if (h.rot_type == 1) {
         const V rk = O::to_rpy(qk);
-        v[3] = (rk.x - erpy.x) / eps;
-        v[4] = (rk.y - erpy.y) / eps;
-        v[5] = (rk.z - erpy.z) / eps;
+        v[3] = M::div_(rk.x - erpy.x, deps);
+        v[4] = M::div_(rk.y - erpy.y, deps);
+        v[5] = M::div_(rk.z - erpy.z, deps);
       } else if (h.rot_type == 2) {
-        v[3] = (qk.x - e.q.x) / eps;
-        v[4] = (qk.y - e.q.y) / eps;
-        v[5] = (qk.z - e.q.z) / eps;
-        v[6] = (qk.w - e.q.w) / eps;
+        v[3] = M::div_(qk.x - e.q.x, deps);
+        v[4] = M::div_(qk.y - e.q.y, deps);
+        v[5] = M::div_(qk.z - e.q.z, deps);
+        v[6] = M::div_(qk.w - e.q.w, deps);
       }
       out.put_J(h.n_cols + n_trans + (k - k0), v);
     }
@@ -480,17 +509,14 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
   static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
-    if (h.off_arec > h.off_base) { // base record wanted (Jacobian with a moving base)
-      BaseCtx ctx;
-      make_base_ctx(h, base, ctx);
-      store_base_ctx(h, ctx, rec, stride);
-    }
+    put_pose(rec, stride, h.off_base, base);
+    if (h.off_arec - h.off_base > 7) store_base_ctx(h, base, rec, stride); // Jacobian with a moving base
     StoreLinks sink;
     sink.h = &h;
     sink.rec = rec;
     sink.stride = stride;
     if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
-    walk(pv, qrow, rec, stride, h.off_arec, h.off_prec, h.off_frame, base, sink);
+    walk(pv, qrow, rec, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
   }
 
   // two-phase driver, phase B: one thread per (configuration, requested link)
@@ -501,38 +527,32 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     e.p = get_vec(rec, stride, lat);
     e.q = O::qidentity();
     if (h.lrec_size == 7) e.q = get_quat(rec, stride, lat + 3);
-    BaseCtx ctx;
-    if (h.with_jacobian && h.base_type != 0) load_base_ctx(h, rec, stride, ctx);
-    emit_link(pv, e, o, rec, stride, h.off_arec, h.off_prec, ctx, out);
+    BaseFromRec bs;
+    bs.rec = rec;
+    bs.stride = stride;
+    bs.at = h.off_base;
+    emit_link(pv, e, o, rec, stride, h.off_arec, h.off_prec, bs, out);
   }
 
   // ---------------------------------------------------------------------------------------------
-  // fused driver (n_out == 1): walk and emit in the same thread; records use the fz_* layout
-  template <class OutSink> struct EmitAtLink {
-    const PlanView *pv;
-    const T *qrow;
-    T *rec;
-    int stride;
-    OutSink *out;
-    TFK_FN void link(int, const P &cur) const {
-      const PlanHeader &h = *pv->h;
-      BaseCtx ctx;
-      if (h.with_jacobian && h.base_type != 0) make_base_ctx(h, get_pose(rec, stride, 0), ctx);
-      emit_link(*pv, cur, 0, rec, stride, h.fz_arec, h.fz_prec, ctx, *out);
-    }
+  // fused driver (n_out == 1): the requested link is the last slot of the pruned chain (or the root),
+  // so walk() returns its pose and the same thread emits the outputs; records use the fz_* layout.
+  // OutFactory::make() builds the output sink only once the walk is done (nothing of it stays live
+  // across the walk).
+  struct NoLinks {
+    TFK_FN void link(int, const P &) const {}
   };
-  template <class OutSink> static TFK_FN void run_fused(const PlanView &pv, const T *qrow, T *rec, int stride, OutSink &out) {
+  template <class OutFactory>
+  static TFK_FN void run_fused(const PlanView &pv, const T *qrow, T *rec, int stride, const OutFactory &make_out) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
-    if (h.fz_arec > 0) put_pose(rec, stride, 0, base); // re-read when the link is reached (base columns)
-    EmitAtLink<OutSink> sink;
-    sink.pv = &pv;
-    sink.qrow = qrow;
-    sink.rec = rec;
-    sink.stride = stride;
-    sink.out = &out;
-    if (h.root_lrec >= 0) sink.link(h.root_lrec, base);
-    walk(pv, qrow, rec, stride, h.fz_arec, h.fz_prec, h.fz_frame, base, sink);
+    put_pose(rec, stride, 0, base);
+    const P e = walk(pv, qrow, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
+    typename OutFactory::Sink out = make_out.make();
+    BaseComputed bs;
+    bs.rec = rec;
+    bs.stride = stride;
+    emit_link(pv, e, 0, rec, stride, h.fz_arec, h.fz_prec, bs, out);
   }
 };
 

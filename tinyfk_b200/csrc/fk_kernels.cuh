@@ -34,34 +34,67 @@ namespace tfk {
 
 enum { TFK_STG = 32 * 7 }; // reals in a warp's staging strip: 32 rows x pose_dim <= 7
 
-// Output sink of the kernels.  put_J must be called by all 32 lanes of the warp together.
+// Output sink of the kernels.  put_J must be called by all 32 lanes of the warp together, once per
+// Jacobian column, in increasing column order (it advances a running column pointer).
 template <class T> struct StagedSink {
-  T *P, *J;
+  T *pP;   // P + head: this lane's row in column 0 of P (head = row*n_out + o)
+  T *pJ;   // J + head0*D + lane: this lane's first element of the warp's run in the current column of J
   long long ldP, ldJ;
-  long long head;  // this lane's row of P (= row*n_out + o)
-  long long head0; // lane 0's row
-  int D, lane, nvalid;
+  T *stg_w; // warp-private strip of TFK_STG reals, + lane*D (where this lane's column entries go)
+  T *stg_r; // the strip + lane (what this lane copies out)
+  int D, lane, cnt; // cnt = valid lanes * D
   bool valid;
-  T *stg; // warp-private strip of TFK_STG reals
 
   __device__ __forceinline__ void begin() const { __syncwarp(); }
   __device__ __forceinline__ void put_P(int d, T v) const {
-    if (valid) __stcs(P + d * ldP + head, v);
+    if (valid) __stcs(pP + d * ldP, v);
   }
-  __device__ __forceinline__ void put_J(int c, const T (&v)[7]) const {
-    T *w = stg + lane * D;
+  template <int DD> __device__ __forceinline__ void put_rows(const T (&v)[7]) {
 #pragma unroll
-    for (int r = 0; r < 7; ++r)
-      if (r < D) w[r] = v[r];
+    for (int r = 0; r < DD; ++r) stg_w[r] = v[r];
     __syncwarp();
-    T *dst = J + c * ldJ + head0 * D;
-    const int cnt = nvalid * D;
+    if (cnt == 32 * DD) { // full warp: DD coalesced 256-byte (FP64) stores, no predicates
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
-      const int e = lane + 32 * k;
-      if (e < cnt) __stcs(dst + e, stg[e]);
+      for (int k = 0; k < DD; ++k) __stcs(pJ + 32 * k, stg_r[32 * k]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < DD; ++k)
+        if (lane + 32 * k < cnt) __stcs(pJ + 32 * k, stg_r[32 * k]);
     }
     __syncwarp();
+    pJ += ldJ;
+  }
+  __device__ __forceinline__ void put_J(int, const T (&v)[7]) {
+    if (D == 6)
+      put_rows<6>(v);
+    else if (D == 3)
+      put_rows<3>(v);
+    else
+      put_rows<7>(v);
+  }
+};
+
+// builds the sink of one warp-load of consecutive rows: head0 = P row of lane 0, nvalid = rows present
+template <class T> struct StagedFactory {
+  typedef StagedSink<T> Sink;
+  T *P, *J;
+  long long ldP, head0;
+  int D, nvalid;
+  T *stg;
+  __device__ __forceinline__ Sink make() const {
+    Sink s;
+    const int lane = threadIdx.x & 31;
+    s.lane = lane;
+    s.D = D;
+    s.ldP = ldP;
+    s.ldJ = ldP * D;
+    s.pP = P + head0 + lane;
+    s.pJ = J + head0 * D + lane;
+    s.stg_w = stg + lane * D;
+    s.stg_r = stg + lane;
+    s.cnt = nvalid * D;
+    s.valid = lane < nvalid;
+    return s;
   }
 };
 
@@ -101,14 +134,12 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs 
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-  StagedSink<T> out;
-  out.P = static_cast<T *>(a.P);
-  out.J = static_cast<T *>(a.J);
-  out.ldP = a.ld_cfg; // n_out == 1
-  out.ldJ = out.ldP * h.pose_dim;
-  out.D = h.pose_dim;
-  out.lane = lane;
-  out.stg = qs + warp * 32 * L.q_pitch; // the warp's own q rows, dead once the walk has read them
+  StagedFactory<T> fac;
+  fac.P = static_cast<T *>(a.P);
+  fac.J = static_cast<T *>(a.J);
+  fac.ldP = a.ld_cfg; // n_out == 1
+  fac.D = h.pose_dim;
+  fac.stg = qs + warp * 32 * L.q_pitch; // the warp's own q rows, dead once the walk has read them
 
   const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -120,11 +151,9 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs 
     nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
     if (nvalid > 0) {
       const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1; // tail lanes redo the last row, store nothing
-      out.valid = (int)threadIdx.x < nv;
-      out.nvalid = nvalid;
-      out.head = a.row0 + i0 + threadIdx.x;
-      out.head0 = a.row0 + i0 + warp * 32;
-      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, out);
+      fac.nvalid = nvalid;
+      fac.head0 = a.row0 + i0 + warp * 32;
+      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, fac);
     }
     __syncthreads();
   }
@@ -145,14 +174,12 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-  StagedSink<T> out;
-  out.P = static_cast<T *>(a.P);
-  out.J = static_cast<T *>(a.J);
-  out.ldP = a.ld_cfg * h.n_out;
-  out.ldJ = out.ldP * h.pose_dim;
-  out.D = h.pose_dim;
-  out.lane = lane;
-  out.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
+  StagedFactory<T> fac;
+  fac.P = static_cast<T *>(a.P);
+  fac.J = static_cast<T *>(a.J);
+  fac.ldP = a.ld_cfg * h.n_out;
+  fac.D = h.pose_dim;
+  fac.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
 
   const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -169,10 +196,9 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
       const int itc = it < items ? it : items - 1;
       const int il = itc / h.n_out;
       const int o = itc - il * h.n_out;
-      out.valid = it < items;
-      out.nvalid = items - it0 < 32 ? items - it0 : 32;
-      out.head = hbase + it;
-      out.head0 = hbase + it0;
+      fac.nvalid = items - it0 < 32 ? items - it0 : 32;
+      fac.head0 = hbase + it0;
+      StagedSink<T> out = fac.make();
       Core::phase_b(pv, rec + il, TFK_TILE, o, out);
     }
     __syncthreads();

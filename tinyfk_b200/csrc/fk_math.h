@@ -16,6 +16,7 @@
 #define TFK_FK_MATH_H
 
 #include "fkmath.h"
+#include "fkmath_simt.h"
 
 #if defined(__CUDACC__)
 #define TFK_FN __host__ __device__ __forceinline__
@@ -42,10 +43,65 @@ struct MathPortable {
   typedef double real;
   static TFK_FN double sin_(double x) { return tfk_sin(x); }
   static TFK_FN double cos_(double x) { return tfk_cos(x); }
-  static TFK_FN void sincos_(double x, double *s, double *c) { tfk_sincos(x, s, c); }
-  static TFK_FN double asin_(double x) { return tfk_asin(x); }
-  static TFK_FN double atan2_(double y, double x) { return tfk_atan2(y, x); }
+  // fkmath_simt.h: bit-identical to fkmath.h's functions, restructured for warps
+  static TFK_FN void sincos_(double x, double *s, double *c) {
+    const TfkSinCos r = tfk_sincos_simt(x);
+    *s = r.s;
+    *c = r.c;
+  }
+  static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
+  static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
   static TFK_FN double sqrt_(double x) { return sqrt(x); }
+
+  // ---- several IEEE divisions by the same denominator ------------------------------------------
+  // The reference divides the four components of a quaternion by one norm (pose.h:284-299,
+  // 230-250), five rpy_derivative coefficients by one cosine (kinematics.cpp:14-21) and every
+  // finite-difference entry by eps (kinematics.cpp:212-231).  den_() takes y = RN(1/b) once
+  // (correctly rounded reciprocal: __drcp_rn on the device, 1.0/b on the host); div_() then gets
+  // RN(a/b) with two residual corrections (Markstein): q0 = RN(a*y) is within 1.5 ulp of a/b,
+  // r0 = a - b*q0 is exact in an FMA, q1 = RN(q0 + r0*y) is a faithful quotient (its unrounded value
+  // is a/b*(1 + O(2^-104))), and for a faithful q1 and a correctly rounded y the second step
+  // q2 = RN(q1 + (a - b*q1)*y) is the correctly rounded quotient [Markstein 1990; Muller et al.,
+  // Handbook of Floating-Point Arithmetic, sec. 4.7].  Exponent ranges that could leave the
+  // normal range on the way (and NaN/Inf/0 denominators) use the plain division instead; an exact
+  // zero numerator gives a*y = +-0 with the quotient's sign.  tests/test_fkmath.py compares
+  // div_() with `/` bit for bit.
+  struct Den {
+    double b, y;
+    bool ok;
+  };
+  static TFK_FN Den den_(double b) {
+    Den d;
+    d.b = b;
+    const uint32_t t = (uint32_t)tfk_hi32(b) & 0x7fffffffu;
+    d.ok = (t - 0x20000000u) < 0x40000000u; // 2^-511 <= |b| < 2^513
+#if defined(__CUDA_ARCH__)
+    d.y = __drcp_rn(b);
+#else
+    d.y = 1.0 / b;
+#endif
+    return d;
+  }
+  static TFK_FN double div_(double a, const Den &d) {
+    const uint32_t t = (uint32_t)tfk_hi32(a) & 0x7fffffffu;
+    if (!d.ok || (t - 0x27000000u) >= 0x32000000u) { // |a| outside [2^-399, 2^401): rare, or an exact zero
+      if (d.ok && (t | (uint32_t)tfk_lo32(a)) == 0u) return a * d.y;
+      return a / d.b;
+    }
+#if defined(__CUDA_ARCH__)
+    double q = __dmul_rn(a, d.y);
+    double r = __fma_rn(-d.b, q, a);
+    q = __fma_rn(r, d.y, q);
+    r = __fma_rn(-d.b, q, a);
+    return __fma_rn(r, d.y, q);
+#else
+    double q = a * d.y;
+    double r = fma(-d.b, q, a);
+    q = fma(r, d.y, q);
+    r = fma(-d.b, q, a);
+    return fma(r, d.y, q);
+#endif
+  }
 };
 
 // The platform's own libm (glibc on the host, libdevice on the GPU).
@@ -64,6 +120,15 @@ struct MathNative64 {
   static TFK_FN double asin_(double x) { return ::asin(x); }
   static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
   static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
+  struct Den {
+    double b;
+  };
+  static TFK_FN Den den_(double b) {
+    Den d;
+    d.b = b;
+    return d;
+  }
+  static TFK_FN double div_(double a, const Den &d) { return a / d.b; }
 };
 
 struct MathNative32 {
@@ -81,6 +146,15 @@ struct MathNative32 {
   static TFK_FN float asin_(float x) { return ::asinf(x); }
   static TFK_FN float atan2_(float y, float x) { return ::atan2f(y, x); }
   static TFK_FN float sqrt_(float x) { return ::sqrtf(x); }
+  struct Den {
+    float b;
+  };
+  static TFK_FN Den den_(float b) {
+    Den d;
+    d.b = b;
+    return d;
+  }
+  static TFK_FN float div_(float a, const Den &d) { return a / d.b; }
 };
 
 template <class M> struct Ops {
@@ -111,10 +185,11 @@ template <class M> struct Ops {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r = qidentity();
     if (norm > T(0)) {
-      r.w = q.w / norm;
-      r.x = -q.x / norm;
-      r.y = -q.y / norm;
-      r.z = -q.z / norm;
+      const typename M::Den d = M::den_(norm);
+      r.w = M::div_(q.w, d);
+      r.x = M::div_(-q.x, d);
+      r.y = M::div_(-q.y, d);
+      r.z = M::div_(-q.z, d);
     }
     return r;
   }
@@ -123,10 +198,11 @@ template <class M> struct Ops {
   static TFK_FN Q qinverse(const Q &q) {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r;
-    r.x = -q.x / norm;
-    r.y = -q.y / norm;
-    r.z = -q.z / norm;
-    r.w = q.w / norm;
+    const typename M::Den d = M::den_(norm);
+    r.x = M::div_(-q.x, d);
+    r.y = M::div_(-q.y, d);
+    r.z = M::div_(-q.z, d);
+    r.w = M::div_(q.w, d);
     return r;
   }
 
@@ -256,10 +332,11 @@ template <class M> struct Ops {
     if (s == T(0)) {
       q = qidentity();
     } else {
-      q.x /= s;
-      q.y /= s;
-      q.z /= s;
-      q.w /= s;
+      const typename M::Den d = M::den_(s);
+      q.x = M::div_(q.x, d);
+      q.y = M::div_(q.y, d);
+      q.z = M::div_(q.z, d);
+      q.w = M::div_(q.w, d);
     }
   }
 
@@ -337,10 +414,11 @@ template <class M> struct Ops {
   static TFK_FN P inverse(const P &a) {
     P o;
     T norm = a.q.w * a.q.w + a.q.x * a.q.x + a.q.y * a.q.y + a.q.z * a.q.z;
-    o.q.w = a.q.w / norm;
-    o.q.x = -a.q.x / norm;
-    o.q.y = -a.q.y / norm;
-    o.q.z = -a.q.z / norm;
+    const typename M::Den d = M::den_(norm);
+    o.q.w = M::div_(a.q.w, d);
+    o.q.x = M::div_(-a.q.x, d);
+    o.q.y = M::div_(-a.q.y, d);
+    o.q.z = M::div_(-a.q.z, d);
     V n;
     n.x = a.p.x * T(-1);
     n.y = a.p.y * T(-1);
@@ -371,12 +449,13 @@ template <class M> struct Ops {
     M::sincos_(a2, &s2, &c2);
     M::sincos_(a3, &s3, &c3);
     RpyCoef k;
-    k.k_xx = c3 / c2;
-    k.k_xy = s3 / c2;
+    const typename M::Den d = M::den_(c2);
+    k.k_xx = M::div_(c3, d);
+    k.k_xy = M::div_(s3, d);
     k.s3 = s3;
     k.c3 = c3;
-    k.k_zx = -c3 * s2 / c2;
-    k.k_zy = s3 * s2 / c2;
+    k.k_zx = M::div_(-c3 * s2, d);
+    k.k_zy = M::div_(s3 * s2, d);
     return k;
   }
   static TFK_FN V rpy_derivative(const RpyCoef &k, const V &axis) {

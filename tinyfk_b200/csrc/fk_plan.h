@@ -81,8 +81,9 @@ struct PlanHeader {
   int32_t n_in;       // reals per input row: n_cols (+3 PLANER, +6 FLOATING)
   int32_t n_out_cols; // Jacobian columns: same count (PLANER keeps x, y, yaw: __init__.py:154-158)
   int32_t lrec_size;  // 3 (IGNORE) or 7
-  // per-config record layout, in reals.  Two-phase kernel: [base | arec | prec | lrec | frames];
-  // fused single-link kernel: [base pose 7 | arec | prec | frames] (fz_*).
+  // per-config record layout, in reals.  Two-phase kernel: [base 7|26 | arec | prec | lrec | frames];
+  // fused single-link kernel: [base pose 7 | arec | prec | frames] (fz_*).  has_base_ctx: the base record
+  // carries the inverse pose and tweaked rotations (Jacobian with a moving base).
   int32_t off_base, off_arec, off_prec, off_lrec, off_frame, rec_size;
   int32_t fz_arec, fz_prec, fz_frame, fz_size;
   int32_t root_lrec;  // link record that receives the base pose (root link requested), or -1

@@ -32,8 +32,12 @@
 
 #if defined(__CUDACC__)
 #define TFK_HD __host__ __device__ inline
+/* out-of-line on the device: the kernels call these from a dozen sites and the instruction cache is
+   the scarcer resource ("code size") */
+#define TFK_HD_CALL static __host__ __device__ __noinline__
 #else
 #define TFK_HD static inline
+#define TFK_HD_CALL static inline
 #endif
 
 #include "fkmath_consts.inc"
@@ -189,7 +193,7 @@ TFK_HD double tfk_cos(double x) {
 
 /* sin and cos of the same argument with one reduction; results are bit-identical to the two
    separate calls (same kernels on the same reduced argument). */
-TFK_HD void tfk_sincos(double x, double *s, double *c) {
+TFK_HD_CALL void tfk_sincos(double x, double *s, double *c) {
   if (fabs(x) <= TFK_PIO4_HI) {
     *s = tfk_ksin(x, 0.0);
     *c = tfk_kcos(x, 0.0);
@@ -227,7 +231,7 @@ TFK_HD double tfk_asin_pq(double z, double *q) {
   return z * (TFK_AP0 + z * (TFK_AP1 + z * (TFK_AP2 + z * (TFK_AP3 + z * (TFK_AP4 + z * TFK_AP5)))));
 }
 
-TFK_HD double tfk_asin(double x) {
+TFK_HD_CALL double tfk_asin(double x) {
   double ax = fabs(x);
   if (!(ax < 1.0)) {
     if (ax == 1.0) return x * TFK_PIO2_HI + x * TFK_PIO2_LO;
@@ -306,7 +310,7 @@ TFK_HD double tfk_atan(double x) {
   return (x < 0.0) ? -r : r;
 }
 
-TFK_HD double tfk_atan2(double y, double x) {
+TFK_HD_CALL double tfk_atan2(double y, double x) {
   if (x != x || y != y) return x + y;
   if (x == 1.0) return tfk_atan(y);
   int m = tfk_signbit(y) | (tfk_signbit(x) << 1);

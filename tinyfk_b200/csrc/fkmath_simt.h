@@ -1,0 +1,250 @@
+/*
+ * fkmath_simt.h -- the SAME functions as fkmath.h (tfk_sincos, tfk_asin, tfk_atan2), restructured for
+ * a SIMT machine.  Every result is BIT-IDENTICAL to the fkmath.h function of the same name
+ * (tests/test_fkmath.py::test_simt_variants_are_bit_identical compares them on millions of arguments;
+ * the GPU parity tests compare the kernels, which use these, with the reference linked against
+ * fkmath.h).  What changes is only the control flow:
+ *
+ *   - data-dependent branches that split a warp (|x| <= pi/4 or not, the quadrant switch, the three
+ *     cosine kernels, asin below/above 0.5, the five atan intervals) become selects around ONE copy
+ *     of the arithmetic, so a warp executes the polynomial and the division once instead of once per
+ *     taken path;
+ *   - rare inputs (huge arguments, NaN/Inf, exact zeros, |y/x| beyond 2^60) are detected with integer
+ *     tests on the exponent word and handed to the fkmath.h function itself;
+ *   - FP64 compares against thresholds whose low word is zero are done on the high word (the FP64
+ *     pipe is the bottleneck of the strict kernels; integer compares run on the ALU pipe);
+ *   - on the device the polynomial coefficients come from constant memory (operands of the FP64
+ *     instructions) instead of being rebuilt from immediates at every use.
+ *
+ * Why identical: each value is produced by the same sequence of IEEE operations on the same
+ * operands; where two code paths of fkmath.h are merged the merged expression reduces to each of
+ * them exactly (x - 0.0 = x, 1.0 - 0.0 = 1.0, x / 1.0 = x, 1.0 * x = x, 0.0 * x + c = c for finite x,
+ * -(a - b) = b - a), as noted at each merge.
+ */
+#ifndef TFK_FKMATH_SIMT_H
+#define TFK_FKMATH_SIMT_H
+
+#include "fkmath.h"
+
+#if defined(__CUDACC__)
+/* constant-bank copies of the coefficients (same literals, so same bits) */
+struct TfkKc {
+  double s1, s2, s3, s4, s5, s6;
+  double c1, c2, c3, c4, c5, c6;
+  double ap0, ap1, ap2, ap3, ap4, ap5, aq1, aq2, aq3, aq4;
+  double at[11];
+  double invpio2, pio2_1, pio2_1t;
+  /* atan intervals: t = (na*ax + nb) / (da*ax + db), result hi - ((t*s - lo) - t) */
+  double iv[5][6];
+};
+static __constant__ TfkKc tfk_kc = {
+    TFK_S1, TFK_S2, TFK_S3, TFK_S4, TFK_S5, TFK_S6,
+    TFK_C1, TFK_C2, TFK_C3, TFK_C4, TFK_C5, TFK_C6,
+    TFK_AP0, TFK_AP1, TFK_AP2, TFK_AP3, TFK_AP4, TFK_AP5, TFK_AQ1, TFK_AQ2, TFK_AQ3, TFK_AQ4,
+    {TFK_AT0, TFK_AT1, TFK_AT2, TFK_AT3, TFK_AT4, TFK_AT5, TFK_AT6, TFK_AT7, TFK_AT8, TFK_AT9, TFK_AT10},
+    TFK_INVPIO2, TFK_PIO2_1, TFK_PIO2_1T,
+    {{1.0, 0.0, 0.0, 1.0, 0.0, 0.0},
+     {2.0, -1.0, 1.0, 2.0, TFK_ATANHI0, TFK_ATANLO0},
+     {1.0, -1.0, 1.0, 1.0, TFK_ATANHI1, TFK_ATANLO1},
+     {1.0, -1.5, 1.5, 1.0, TFK_ATANHI2, TFK_ATANLO2},
+     {0.0, -1.0, 1.0, 0.0, TFK_ATANHI3, TFK_ATANLO3}}};
+#endif
+
+#if defined(__CUDA_ARCH__)
+#define TFK_KC(field, lit) (tfk_kc.field)
+#else
+#define TFK_KC(field, lit) (lit)
+#endif
+
+TFK_HD int32_t tfk_lo32(double x) {
+#if defined(__CUDA_ARCH__)
+  return __double2loint(x);
+#else
+  uint64_t u;
+  memcpy(&u, &x, sizeof u);
+  return (int32_t)(uint32_t)u;
+#endif
+}
+
+/* tfk_ksin / tfk_kcos with the early exits turned into final selects */
+TFK_HD double tfk_ksin_simt(double x, double y) {
+  double z = x * x;
+  double v = z * x;
+  double r = TFK_KC(s2, TFK_S2) +
+             z * (TFK_KC(s3, TFK_S3) + z * (TFK_KC(s4, TFK_S4) + z * (TFK_KC(s5, TFK_S5) + z * TFK_KC(s6, TFK_S6))));
+  double p = x - ((z * (0.5 * y - v * r) - y) - v * TFK_KC(s1, TFK_S1));
+  /* |x| < 2^-27 <=> high word (sign cleared) < 0x3e400000 (the threshold's low word is zero) */
+  return ((tfk_hi32(x) & 0x7fffffff) < 0x3e400000) ? x : p;
+}
+
+TFK_HD double tfk_kcos_simt(double x, double y) {
+  const int32_t hx = tfk_hi32(x) & 0x7fffffff;
+  double ax = fabs(x);
+  double z = x * x;
+  double r = z * (TFK_KC(c1, TFK_C1) +
+                  z * (TFK_KC(c2, TFK_C2) +
+                       z * (TFK_KC(c3, TFK_C3) + z * (TFK_KC(c4, TFK_C4) + z * (TFK_KC(c5, TFK_C5) + z * TFK_KC(c6, TFK_C6))))));
+  /* ax < 0.3: qx = 0 gives hz = 0.5*z - 0 = 0.5*z and a = 1 - 0 = 1, i.e. fkmath.h's first form.
+     (0.3 has a non-zero low word: keep the FP64 compare.)  0.78125 = 0x3fe90000_00000000. */
+  double qx = tfk_from_hi32(hx - 0x00200000);
+  if (hx > 0x3fe90000 || (hx == 0x3fe90000 && tfk_lo32(x) != 0)) qx = 0.28125;
+  if (ax < 0.3) qx = 0.0;
+  double hz = 0.5 * z - qx;
+  double a = 1.0 - qx;
+  double p = a - (hz - (z * r - x * y));
+  return (hx < 0x3e400000) ? 1.0 : p;
+}
+
+typedef struct {
+  double s, c;
+} TfkSinCos;
+
+/* sin and cos of x; bit-identical to tfk_sincos (fkmath.h) */
+TFK_HD_CALL TfkSinCos tfk_sincos_simt(double x) {
+  TfkSinCos out;
+  const int32_t hx = tfk_hi32(x) & 0x7fffffff;
+  if (hx >= 0x41392000) { /* |x| >= ~1.64e6 (1647099.0 = 0x413921fb_00000000), inf, nan: rare */
+    tfk_sincos(x, &out.s, &out.c);
+    return out;
+  }
+  const double t = fabs(x);
+  const int small = t <= TFK_PIO4_HI;
+  /* first reduction stage for every lane (harmless when small) */
+  int n = (int)(t * TFK_KC(invpio2, TFK_INVPIO2) + 0.5);
+  const double fn = (double)n;
+  double r = t - fn * TFK_KC(pio2_1, TFK_PIO2_1);
+  double w = fn * TFK_KC(pio2_1t, TFK_PIO2_1T);
+  double a0 = r - w;
+  if (!small) {
+    const int j = (hx >> 20) & 0x7ff;
+    int i = j - ((tfk_hi32(a0) >> 20) & 0x7ff);
+    if (i > 16) { /* cancellation near a multiple of pi/2: rare */
+      double t2 = r;
+      w = fn * TFK_PIO2_2;
+      r = t2 - w;
+      w = fn * TFK_PIO2_2T - ((t2 - r) - w);
+      a0 = r - w;
+      i = j - ((tfk_hi32(a0) >> 20) & 0x7ff);
+      if (i > 49) {
+        t2 = r;
+        w = fn * TFK_PIO2_3;
+        r = t2 - w;
+        w = fn * TFK_PIO2_3T - ((t2 - r) - w);
+        a0 = r - w;
+      }
+    }
+  }
+  double a1 = (r - a0) - w;
+  if (small) {
+    n = 0;
+    a0 = t;
+    a1 = 0.0;
+  }
+  /* fkmath.h: small -> kernels on (x, 0.0); else on (+-a0, +-a1) with n negated for x < 0 */
+  const int neg = tfk_hi32(x) < 0;
+  const double y0 = neg ? -a0 : a0;
+  const double y1 = (neg && !small) ? -a1 : a1;
+  if (neg) n = -n;
+  const double ks = tfk_ksin_simt(y0, y1), kc = tfk_kcos_simt(y0, y1);
+  /* n&3: 0 (ks, kc)  1 (kc, -ks)  2 (-ks, -kc)  3 (-kc, ks) */
+  double ss = (n & 1) ? kc : ks;
+  double cc = (n & 1) ? ks : kc;
+  if (n & 2) ss = -ss;
+  if ((n + 1) & 2) cc = -cc;
+  out.s = ss;
+  out.c = cc;
+  return out;
+}
+
+TFK_HD double tfk_asin_pq_simt(double z, double *q) {
+  *q = 1.0 + z * (TFK_KC(aq1, TFK_AQ1) + z * (TFK_KC(aq2, TFK_AQ2) + z * (TFK_KC(aq3, TFK_AQ3) + z * TFK_KC(aq4, TFK_AQ4))));
+  return z * (TFK_KC(ap0, TFK_AP0) +
+              z * (TFK_KC(ap1, TFK_AP1) +
+                   z * (TFK_KC(ap2, TFK_AP2) + z * (TFK_KC(ap3, TFK_AP3) + z * (TFK_KC(ap4, TFK_AP4) + z * TFK_KC(ap5, TFK_AP5))))));
+}
+
+/* bit-identical to tfk_asin (fkmath.h): one rational kernel + one division for both ranges */
+TFK_HD_CALL double tfk_asin_simt(double x) {
+  const int32_t hx = tfk_hi32(x) & 0x7fffffff;
+  if (hx >= 0x3ff00000) return tfk_asin(x); /* |x| >= 1, nan: rare */
+  if (hx < 0x3e400000) return x;            /* |x| < 2^-27 */
+  const double ax = fabs(x);
+  const int big = hx >= 0x3fe00000; /* |x| >= 0.5 */
+  const double t = (1.0 - ax) * 0.5;
+  double q;
+  const double p = tfk_asin_pq_simt(big ? t : x * x, &q);
+  const double rr = p / q;
+  if (!big) return x + x * rr;
+  const double s = sqrt(t);
+  double res;
+  if (ax >= 0.975) {
+    res = TFK_PIO2_HI - (2.0 * (s + s * rr) - TFK_PIO2_LO);
+  } else {
+    const double w = tfk_from_hi32(tfk_hi32(s));
+    const double c = (t - w * w) / (s + w);
+    const double pp = 2.0 * s * rr - (TFK_PIO2_LO - 2.0 * c);
+    const double qq = TFK_PIO4_HI - 2.0 * w;
+    res = TFK_PIO4_HI - (pp - qq);
+  }
+  return (x > 0.0) ? res : -res;
+}
+
+/* atan of ax >= 2^-29, finite, < 2^66; returns atan(ax) >= 0.  Bit-identical to tfk_atan(ax):
+   interval id from the high word (all four thresholds have a zero low word), its six constants from a
+   table, ONE division:  t = (na*ax + nb) / (da*ax + db)
+     id -1: (1*ax + 0) / (0*ax + 1) = ax / 1 = ax            fkmath.h: t = x
+     id  0: (2*ax - 1) / (1*ax + 2)                          (2.0*ax - 1.0) / (2.0 + ax)
+     id  1: (1*ax - 1) / (1*ax + 1)                          (ax - 1.0) / (ax + 1.0)
+     id  2: (1*ax - 1.5) / (1.5*ax + 1)                      (ax - 1.5) / (1.0 + 1.5*ax)
+     id  3: (0*ax - 1) / (1*ax + 0) = -1 / ax                -1.0 / ax
+   and hi - ((t*s - lo) - t) with hi = lo = 0 for id -1 equals -(t*s - t) = t - t*s. */
+TFK_HD double tfk_atan_pos_simt(double ax) {
+  const int32_t hx = tfk_hi32(ax);
+  const int id = (hx >= 0x3fdc0000) + (hx >= 0x3fe60000) + (hx >= 0x3ff30000) + (hx >= 0x40038000);
+#if defined(__CUDA_ARCH__)
+  const double *iv = tfk_kc.iv[id];
+  const double na = iv[0], nb = iv[1], da = iv[2], db = iv[3], hi = iv[4], lo = iv[5];
+#else
+  static const double tab[5][6] = {{1.0, 0.0, 0.0, 1.0, 0.0, 0.0},
+                                   {2.0, -1.0, 1.0, 2.0, TFK_ATANHI0, TFK_ATANLO0},
+                                   {1.0, -1.0, 1.0, 1.0, TFK_ATANHI1, TFK_ATANLO1},
+                                   {1.0, -1.5, 1.5, 1.0, TFK_ATANHI2, TFK_ATANLO2},
+                                   {0.0, -1.0, 1.0, 0.0, TFK_ATANHI3, TFK_ATANLO3}};
+  const double na = tab[id][0], nb = tab[id][1], da = tab[id][2], db = tab[id][3], hi = tab[id][4], lo = tab[id][5];
+#endif
+  const double t = (na * ax + nb) / (da * ax + db);
+  const double z = t * t;
+  double s = TFK_KC(at[10], TFK_AT10);
+  s = TFK_KC(at[9], TFK_AT9) + z * s;
+  s = TFK_KC(at[8], TFK_AT8) + z * s;
+  s = TFK_KC(at[7], TFK_AT7) + z * s;
+  s = TFK_KC(at[6], TFK_AT6) + z * s;
+  s = TFK_KC(at[5], TFK_AT5) + z * s;
+  s = TFK_KC(at[4], TFK_AT4) + z * s;
+  s = TFK_KC(at[3], TFK_AT3) + z * s;
+  s = TFK_KC(at[2], TFK_AT2) + z * s;
+  s = TFK_KC(at[1], TFK_AT1) + z * s;
+  s = TFK_KC(at[0], TFK_AT0) + z * s;
+  s = z * s;
+  return hi - ((t * s - lo) - t);
+}
+
+/* bit-identical to tfk_atan2 (fkmath.h) */
+TFK_HD_CALL double tfk_atan2_simt(double y, double x) {
+  const int32_t hxs = tfk_hi32(x), hys = tfk_hi32(y);
+  const int32_t hx = hxs & 0x7fffffff, hy = hys & 0x7fffffff;
+  const int k = (hy >> 20) - (hx >> 20);
+  /* rare: nan/inf, x == 1.0, y == 0, x == 0, exponents more than 60 apart, |y/x| outside atan's
+     plain range -- the fkmath.h function handles them */
+  const int special = (hx >= 0x7ff00000) | (hy >= 0x7ff00000) | ((hy | tfk_lo32(y)) == 0) | ((hx | tfk_lo32(x)) == 0) |
+                      ((hxs == 0x3ff00000) & (tfk_lo32(x) == 0)) | (k > 60) | (k < -60);
+  if (special) return tfk_atan2(y, x);
+  const double a = fabs(y / x);
+  const int32_t ha = tfk_hi32(a);
+  double z = (ha < 0x3e200000) ? a : tfk_atan_pos_simt(a); /* |a| < 2^-29: atan(a) = a */
+  /* m = signbit(y) | signbit(x) << 1:  0: z   1: -z   2: pi - (z - pi_lo)   3: (z - pi_lo) - pi */
+  if (hxs < 0) z = TFK_PI - (z - TFK_PI_LO);
+  return (hys < 0) ? -z : z;
+}
+
+#endif /* TFK_FKMATH_SIMT_H */

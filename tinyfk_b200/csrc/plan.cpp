@@ -240,14 +240,16 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   // link's rotation (src/kinematics.cpp:189-219 with pose.cpp:139-146)
   h.lrec_size = key.rot_type == ROT_IGNORE ? 3 : 7;
   h.off_base = 0;
-  const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 0;
+  // the base pose always has a record (7 reals; children of the root re-read it); a Jacobian with a moving
+  // base adds the inverse pose and the tweaked rotations of the finite-difference columns
+  const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 7;
   h.off_arec = h.off_base + base_rec;
   h.off_prec = h.off_arec + 3 * n_arec;
   h.off_lrec = h.off_prec + 3 * n_prec;
   h.off_frame = h.off_lrec + h.lrec_size * n_lrec;
   h.rec_size = h.off_frame + 7 * b.frames_max;
   // fused single-link kernel: the link pose and the base context stay in registers
-  h.fz_arec = base_rec ? 7 : 0;
+  h.fz_arec = 7;
   h.fz_prec = h.fz_arec + 3 * n_arec;
   h.fz_frame = h.fz_prec + 3 * n_prec;
   h.fz_size = h.fz_frame + 7 * b.frames_max;
