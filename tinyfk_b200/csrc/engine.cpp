@@ -152,6 +152,7 @@ Engine::PlanEntry &Engine::plan_for(const SolveSpec &spec) {
   std::unique_ptr<PlanEntry> e(new PlanEntry);
   e->key = key;
   e->blob.swap(blob);
+  e->params = make_plan_params(e->blob);
   plans_.push_back(std::move(e));
   return *plans_.back();
 }
@@ -193,8 +194,10 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (n <= 0 || h->n_out == 0) return;
   if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
-  const int plan_bytes = (int)e.blob.size();
   const int rb = (int)real_size(precision);
+  // per-output tables of the two-phase kernel: [lrec_of_out | masks], contiguous inside the blob
+  const int table_bytes = h->n_out == 1 ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
+  const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
   int variant, rec_reals;
@@ -235,16 +238,16 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(rec_reals, 1) * real_size(precision);
     a.scratch = workspace(device, stream, rec_bytes).scratch;
   }
-  a.plan = plan_on_device(e, device, stream);
-  a.plan_bytes = plan_bytes;
+  a.tables = table_bytes ? plan_on_device(e, device, stream) + h->off_outs : nullptr;
+  a.table_bytes = table_bytes;
   a.q = d_q;
   a.n = n;
   a.row0 = row0;
   a.ld_cfg = ld_cfg;
   a.P = d_P;
   a.J = d_J;
-  ck(precision == PREC_F32 ? launch_fk_f32(a, variant, grid, smem, stream)
-                           : launch_fk_f64_strict(a, variant, grid, smem, stream),
+  ck(precision == PREC_F32 ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
+                           : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
      "kernel launch");
   g_launches.fetch_add(1);
   last_launch.grid = grid;

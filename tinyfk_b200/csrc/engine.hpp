@@ -56,6 +56,7 @@ private:
   struct PlanEntry {
     PlanKey key;
     std::vector<unsigned char> blob;
+    std::unique_ptr<PlanParams> params; // the kernel-parameter form of the blob (fk_plan.h)
     std::map<int, unsigned char *> on_device; // device ordinal -> uploaded copy
   };
   struct Workspace { // one per (device, stream): concurrent launches never share records

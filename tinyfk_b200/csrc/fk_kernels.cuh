@@ -21,7 +21,8 @@
 //   records  fused: [fz_size][TILE] in shared memory (global scratch only if they do not fit);
 //            two-phase: [grid][rec_size][TILE] block-private scratch, written in phase A and re-read in
 //            phase B of the same tile (L2-resident; the output stores are streaming so they do not evict it).
-//   plan     a few KB, copied to shared memory once per block, read with warp-uniform loads.
+//   plan     a by-value __grid_constant__ kernel parameter (PlanParams, fk_plan.h): constant bank, uniform
+//            datapath; only the two-phase kernel's per-output tables (indexed per lane) go to shared memory.
 #ifndef TFK_FK_KERNELS_CUH
 #define TFK_FK_KERNELS_CUH
 
@@ -117,16 +118,26 @@ __device__ __forceinline__ void stage_q_tile(T *qs, int q_pitch, const T *q, lon
   }
 }
 
+// pull the block's NEXT tile of q into L2 while this one is being worked on (no registers, no smem)
+template <class T> __device__ __forceinline__ void prefetch_q_tile(const T *q, long long i0, long long n, int n_in) {
+  if (i0 >= n || n_in == 0) return;
+  const long long rows = (n - i0 < TFK_TILE) ? (n - i0) : (long long)TFK_TILE;
+  const char *p = reinterpret_cast<const char *>(q + i0 * n_in) + (size_t)threadIdx.x * 128;
+  if ((long long)threadIdx.x * 128 < rows * n_in * (long long)sizeof(T)) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 template <class Core, bool SMEM_REC>
-__global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs a) {
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
-  for (int i = threadIdx.x * 16; i < a.plan_bytes; i += TFK_TILE * 16)
-    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.plan + i);
-  __syncthreads();
-  const PlanView pv = plan_view(smem);
-  const PlanHeader &h = *pv.h;
-  const SmemLayout L = smem_layout(a.plan_bytes, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.masks = pp.mask0;
+  pv.lrec_of_out = nullptr; // one output: never read
+  const PlanHeader &h = pp.h;
+  const SmemLayout L = smem_layout(0, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
   T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
                     : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.fz_size;
@@ -146,6 +157,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs 
     const long long i0 = tile * TFK_TILE;
     const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
     __syncthreads();
     int nvalid = nv - warp * 32;
     nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
@@ -160,15 +172,21 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs 
 }
 
 template <class Core>
-__global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a) {
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
-  for (int i = threadIdx.x * 16; i < a.plan_bytes; i += TFK_TILE * 16)
-    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.plan + i);
+  // per-output tables (indexed per lane in phase B) -> shared memory; everything else stays in the constant bank
+  for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
   __syncthreads();
-  const PlanView pv = plan_view(smem);
-  const PlanHeader &h = *pv.h;
-  const SmemLayout L = smem_layout(a.plan_bytes, h.n_in, 0, (int)sizeof(T));
+  const PlanHeader &h = pp.h;
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
+  pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
+  const SmemLayout L = smem_layout(a.table_bytes, h.n_in, 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
   T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
   const T *q = static_cast<const T *>(a.q);
@@ -186,6 +204,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
     const long long i0 = tile * TFK_TILE;
     const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
     __syncthreads();
     if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
     __syncthreads();
@@ -205,13 +224,14 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   }
 }
 
-template <class Core> cudaError_t launch_fk(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream) {
+template <class Core>
+cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
   if (variant == KV_FUSED_SMEM)
-    fk_fused_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
+    fk_fused_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_FUSED_GMEM)
-    fk_fused_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
+    fk_fused_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else
-    fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a);
+    fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
 }
 

@@ -22,8 +22,8 @@ enum KernelVariant {
 };
 
 struct KernelArgs {
-  const unsigned char *plan; // device copy of the plan blob (16-byte aligned, padded to 16)
-  int plan_bytes;
+  const unsigned char *tables; // two-phase: device copy of the plan's per-output tables (lrec_of_out, masks)
+  int table_bytes;             // 16-byte multiple
   const void *q;     // [n][n_in] reals
   long long n;       // configurations in this launch
   long long row0;    // global row of configuration 0 inside P / J
@@ -32,7 +32,7 @@ struct KernelArgs {
   void *scratch;     // grid * TFK_TILE * (rec_size | fz_size) reals (unused by KV_FUSED_SMEM)
 };
 
-// Dynamic shared memory of a block: [plan | q tile (doubles as the warps' staging strips) | records]
+// Dynamic shared memory of a block: [per-output tables | q tile (doubles as the warps' staging strips) | records]
 struct SmemLayout {
   int plan_bytes, q_pitch, q_off, rec_off, total;
 };
@@ -44,9 +44,9 @@ struct SmemLayout {
 // q tile pitch: odd (conflict-free 64-bit reads at one row per thread) and >= 7 so that a warp's own 32
 // rows can double as its staging strip (32 x pose_dim reals) once the angles have been consumed
 TFK_HDI int q_pitch_of(int n_in) { return (n_in < 7 ? 7 : n_in) | 1; }
-TFK_HDI SmemLayout smem_layout(int plan_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
+TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
   SmemLayout L;
-  L.plan_bytes = (plan_bytes + 15) & ~15;
+  L.plan_bytes = (table_bytes + 15) & ~15;
   L.q_pitch = q_pitch_of(n_in);
   L.q_off = L.plan_bytes;
   L.rec_off = L.q_off + ((TFK_TILE * L.q_pitch * real_bytes + 15) & ~15);
@@ -54,9 +54,11 @@ TFK_HDI SmemLayout smem_layout(int plan_bytes, int n_in, int rec_reals_in_smem, 
   return L;
 }
 
-cudaError_t launch_fk_f64_strict(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream);
+cudaError_t launch_fk_f64_strict(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
+                                 cudaStream_t stream);
 cudaError_t occupancy_fk_f64_strict(int variant, int smem_bytes, int *blocks_per_sm);
-cudaError_t launch_fk_f32(const KernelArgs &a, int variant, int grid, int smem_bytes, cudaStream_t stream);
+cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
+                          cudaStream_t stream);
 cudaError_t occupancy_fk_f32(int variant, int smem_bytes, int *blocks_per_sm);
 
 } // namespace tfk

@@ -20,8 +20,12 @@
 
 #if defined(__CUDACC__)
 #define TFK_FN __host__ __device__ __forceinline__
+// out-of-line on the device: called from several sites, each holding two or three independent libm
+// evaluations that the compiler interleaves (ILP) -- one copy keeps the instruction cache footprint small
+#define TFK_FN_CALL __host__ __device__ __noinline__
 #else
 #define TFK_FN inline
+#define TFK_FN_CALL inline
 #endif
 
 namespace tfk {
@@ -51,6 +55,7 @@ struct MathPortable {
   }
   static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
   static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
+  static TFK_FN double atan2_rare_(double y, double x) { return tfk_atan2(y, x); } // same bits, out of line
   static TFK_FN double sqrt_(double x) { return sqrt(x); }
 
   // ---- several IEEE divisions by the same denominator ------------------------------------------
@@ -119,6 +124,7 @@ struct MathNative64 {
   }
   static TFK_FN double asin_(double x) { return ::asin(x); }
   static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
+  static TFK_FN double atan2_rare_(double y, double x) { return ::atan2(y, x); }
   static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
   struct Den {
     double b;
@@ -145,6 +151,7 @@ struct MathNative32 {
   }
   static TFK_FN float asin_(float x) { return ::asinf(x); }
   static TFK_FN float atan2_(float y, float x) { return ::atan2f(y, x); }
+  static TFK_FN float atan2_rare_(float y, float x) { return ::atan2f(y, x); }
   static TFK_FN float sqrt_(float x) { return ::sqrtf(x); }
   struct Den {
     float b;
@@ -341,7 +348,7 @@ template <class M> struct Ops {
   }
 
   // Rotation::setFromRPY, pose.h:202-216
-  static TFK_FN Q from_rpy(T roll, T pitch, T yaw) {
+  static TFK_FN_CALL Q from_rpy(T roll, T pitch, T yaw) {
     T phi = roll / T(2), the = pitch / T(2), psi = yaw / T(2);
     T sph, cph, sth, cth, sps, cps;
     M::sincos_(phi, &sph, &cph);
@@ -357,7 +364,7 @@ template <class M> struct Ops {
   }
 
   // Rotation::getRPY, pose.h:161-192
-  static TFK_FN V to_rpy(const Q &q) {
+  static TFK_FN_CALL V to_rpy(Q q) {
     T sqx = q.x * q.x, sqy = q.y * q.y, sqz = q.z * q.z, sqw = q.w * q.w;
     T sarg = T(-2) * (q.x * q.z - q.w * q.y);
     const T pi_2 = T(1.57079632679489661923);
@@ -365,11 +372,11 @@ template <class M> struct Ops {
     if (sarg <= T(-0.99999)) {
       r.y = -pi_2;
       r.x = T(0);
-      r.z = T(2) * M::atan2_(q.x, -q.y);
+      r.z = T(2) * M::atan2_rare_(q.x, -q.y);
     } else if (sarg >= T(0.99999)) {
       r.y = pi_2;
       r.x = T(0);
-      r.z = T(2) * M::atan2_(-q.x, q.y);
+      r.z = T(2) * M::atan2_rare_(-q.x, q.y);
     } else {
       r.y = M::asin_(sarg);
       r.x = M::atan2_(T(2) * (q.y * q.z + q.w * q.x), sqw - sqx - sqy + sqz);
@@ -443,7 +450,7 @@ template <class M> struct Ops {
     T s3, c3;     //  sin(a3), cos(a3)
     T k_zx, k_zy; // -cos(a3)*sin(a2)/cos(a2),  sin(a3)*sin(a2)/cos(a2)
   };
-  static TFK_FN RpyCoef rpy_coef(const V &rpy) {
+  static TFK_FN_CALL RpyCoef rpy_coef(V rpy) {
     T a2 = -rpy.y, a3 = -rpy.z;
     T s2, c2, s3, c3;
     M::sincos_(a2, &s2, &c2);

@@ -95,5 +95,19 @@ struct PlanHeader {
   double base_pose[7]; // stored base pose used when base_type == FIXED (include/tinyfk.hpp:72)
 };
 
+// What the kernels read on their hot path, passed BY VALUE as a __grid_constant__ kernel parameter: it
+// lives in the constant bank, so slot fields arrive through the uniform datapath (no shared-memory
+// loads, branches on them are uniform branches) and FP64 instructions take the constants as operands.
+// The per-output tables (lrec_of_out, masks) of the two-phase kernel are indexed per lane and stay in
+// shared memory; mask0 is the relevance mask of the fused kernel's only output.
+enum { TFK_PSLOTS = 176, TFK_PCOLS = 64 };
+struct PlanParams {
+  PlanHeader h;
+  PlanSlot slots[TFK_PSLOTS];
+  PlanCol cols[TFK_PCOLS];
+  uint32_t mask0[2];
+  uint32_t pad_[2];
+};
+
 } // namespace tfk
 #endif

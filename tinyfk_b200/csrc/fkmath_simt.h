@@ -100,7 +100,7 @@ typedef struct {
 } TfkSinCos;
 
 /* sin and cos of x; bit-identical to tfk_sincos (fkmath.h) */
-TFK_HD_CALL TfkSinCos tfk_sincos_simt(double x) {
+TFK_HD TfkSinCos tfk_sincos_simt(double x) {
   TfkSinCos out;
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
   if (hx >= 0x41392000) { /* |x| >= ~1.64e6 (1647099.0 = 0x413921fb_00000000), inf, nan: rare */
@@ -164,7 +164,7 @@ TFK_HD double tfk_asin_pq_simt(double z, double *q) {
 }
 
 /* bit-identical to tfk_asin (fkmath.h): one rational kernel + one division for both ranges */
-TFK_HD_CALL double tfk_asin_simt(double x) {
+TFK_HD double tfk_asin_simt(double x) {
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
   if (hx >= 0x3ff00000) return tfk_asin(x); /* |x| >= 1, nan: rare */
   if (hx < 0x3e400000) return x;            /* |x| < 2^-27 */
@@ -230,7 +230,7 @@ TFK_HD double tfk_atan_pos_simt(double ax) {
 }
 
 /* bit-identical to tfk_atan2 (fkmath.h) */
-TFK_HD_CALL double tfk_atan2_simt(double y, double x) {
+TFK_HD double tfk_atan2_simt(double y, double x) {
   const int32_t hxs = tfk_hi32(x), hys = tfk_hi32(y);
   const int32_t hx = hxs & 0x7fffffff, hy = hys & 0x7fffffff;
   const int k = (hy >> 20) - (hx >> 20);

@@ -268,6 +268,7 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   size_t off = sizeof(PlanHeader);
   h.off_slots = (int)off;
   off += sizeof(PlanSlot) * b.slots.size();
+  off = (off + 15) & ~(size_t)15; // the two-phase kernel copies [outs | masks] to shared memory with 16-byte loads
   h.off_outs = (int)off;
   off += sizeof(int32_t) * n_out;
   h.off_masks = (int)off;
@@ -284,6 +285,23 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   if (!masks.empty()) std::memcpy(blob.data() + h.off_masks, masks.data(), sizeof(uint32_t) * masks.size());
   if (n_cols) std::memcpy(blob.data() + h.off_cols, cols.data(), sizeof(PlanCol) * n_cols);
   return blob;
+}
+
+std::unique_ptr<PlanParams> make_plan_params(const std::vector<unsigned char> &blob) {
+  const PlanHeader *h = reinterpret_cast<const PlanHeader *>(blob.data());
+  if (h->n_slots > (int)TFK_PSLOTS)
+    throw std::invalid_argument("request needs " + std::to_string(h->n_slots) + " links of the tree; the kernels take at most " +
+                                std::to_string((int)TFK_PSLOTS));
+  if (h->n_cols > (int)TFK_PCOLS)
+    throw std::invalid_argument("request names " + std::to_string(h->n_cols) + " joints; the kernels take at most " +
+                                std::to_string((int)TFK_PCOLS));
+  std::unique_ptr<PlanParams> p(new PlanParams);
+  std::memset(p.get(), 0, sizeof(PlanParams));
+  p->h = *h;
+  if (h->n_slots) std::memcpy(p->slots, blob.data() + h->off_slots, sizeof(PlanSlot) * h->n_slots);
+  if (h->n_cols) std::memcpy(p->cols, blob.data() + h->off_cols, sizeof(PlanCol) * h->n_cols);
+  if (h->n_out >= 1) std::memcpy(p->mask0, blob.data() + h->off_masks, sizeof(uint32_t) * (h->mask_words < 2 ? h->mask_words : 2));
+  return p;
 }
 
 } // namespace tfk

@@ -3,6 +3,7 @@
 #define TFK_PLAN_HPP
 
 #include <cstdint>
+#include <memory>
 #include <vector>
 
 #include "fk_plan.h"
@@ -22,6 +23,10 @@ struct PlanKey {
 
 // Builds the plan blob.  Throws std::invalid_argument on out-of-range ids or too deep branching.
 std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey &key);
+
+// Kernel-parameter form of a plan blob.  Throws std::invalid_argument if the pruned tree or the column
+// list exceeds what the parameter block holds (TFK_PSLOTS links, TFK_PCOLS joints).
+std::unique_ptr<PlanParams> make_plan_params(const std::vector<unsigned char> &blob);
 
 inline int pose_dim_of(int rot_type) { return 3 + (rot_type == ROT_RPY) * 3 + (rot_type == ROT_XYZW) * 4; }
 inline int base_dof_of(int base_type) { return base_type == BASE_PLANER ? 3 : (base_type == BASE_FLOATING ? 6 : 0); }
