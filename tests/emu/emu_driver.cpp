@@ -119,12 +119,22 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     std::vector<unsigned char> blob = build_plan(*static_cast<KinematicModel *>(m), key);
     const bool two_phase = (mode & 16) != 0;
     mode &= 15;
-    if (mode == 0)
-      run<FkCore<MathPortable, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
-    else if (mode == 1)
-      run<FkCore<MathNative32, true>, float>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
-    else
-      run<FkCore<MathNative64, false>, double>(blob, qs, n, P, with_jacobian ? J : nullptr, two_phase);
+    double *Jp = with_jacobian ? J : nullptr;
+#define TFK_EMU_RUN(R)                                                                      \
+  if (mode == 0)                                                                            \
+    run<FkCore<MathPortable, false, R>, double>(blob, qs, n, P, Jp, two_phase);             \
+  else if (mode == 1)                                                                       \
+    run<FkCore<MathNative32, true, R>, float>(blob, qs, n, P, Jp, two_phase);               \
+  else                                                                                      \
+    run<FkCore<MathNative64, false, R>, double>(blob, qs, n, P, Jp, two_phase);
+    if (rot_type == 0) {
+      TFK_EMU_RUN(0)
+    } else if (rot_type == 1) {
+      TFK_EMU_RUN(1)
+    } else {
+      TFK_EMU_RUN(2)
+    }
+#undef TFK_EMU_RUN
     return 0;
   } catch (const std::exception &e) {
     g_err = e.what();

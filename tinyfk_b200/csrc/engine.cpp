@@ -217,12 +217,13 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   }
   const int smem = L.total;
   if (smem > 200 * 1024) throw std::invalid_argument("plan too large for shared memory");
-  auto okey = std::make_tuple(device, precision, variant, smem);
+  auto okey = std::make_tuple(device, precision * 4 + h->rot_type, variant, smem);
   auto oit = occupancy_.find(okey);
   int bps = 0;
   if (oit == occupancy_.end()) {
     // also raises the kernel's dynamic shared memory limit on this device when smem > 48 KB
-    ck(precision == PREC_F32 ? occupancy_fk_f32(variant, smem, &bps) : occupancy_fk_f64_strict(variant, smem, &bps),
+    ck(precision == PREC_F32 ? occupancy_fk_f32(h->rot_type, variant, smem, &bps)
+                             : occupancy_fk_f64_strict(h->rot_type, variant, smem, &bps),
        "occupancy query");
     if (bps < 1) throw CudaError("kernel does not fit on an SM");
     occupancy_[okey] = bps;

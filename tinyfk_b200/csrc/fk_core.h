@@ -70,7 +70,10 @@ template <class T> struct DirectSink {
 
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
 // instead of the reference's forward difference (FP32 mode: eps = 1e-7 is below one FP32 ulp).
-template <class M, bool ANALYTIC_BASE> struct FkCore {
+// ROT: the call's RotationType (0 IGNORE, 1 RPY, 2 XYZW) as a compile-time constant -- it fixes the
+// pose dimension, so the kernels are instantiated once per value instead of branching per column.
+template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
+  enum { D = ROT == 0 ? 3 : (ROT == 1 ? 6 : 7), LREC = ROT == 0 ? 3 : 7 };
   typedef typename M::real T;
   typedef Ops<M> O;
   typedef Vec3<T> V;
@@ -335,12 +338,12 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     out.put_P(2, e.p.z);
     V erpy;
     erpy.x = erpy.y = erpy.z = T(0);
-    if (h.rot_type == 1) { // src/wrapper.cpp:101-106
+    if (ROT == 1) { // src/wrapper.cpp:101-106
       erpy = O::to_rpy(e.q);
       out.put_P(3, erpy.x);
       out.put_P(4, erpy.y);
       out.put_P(5, erpy.z);
-    } else if (h.rot_type == 2) { // src/wrapper.cpp:107-112
+    } else if (ROT == 2) { // src/wrapper.cpp:107-112
       out.put_P(3, e.q.x);
       out.put_P(4, e.q.y);
       out.put_P(5, e.q.z);
@@ -351,8 +354,8 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     typename O::RpyCoef coef;
     coef.k_xx = coef.k_xy = coef.s3 = coef.c3 = coef.k_zx = coef.k_zy = T(0);
     Q einv = O::qidentity();
-    if (h.rot_type == 1) coef = O::rpy_coef(erpy);  // src/kinematics.cpp:121-123 + :14-21
-    if (h.rot_type == 2) einv = O::qinverse(e.q);   // src/kinematics.cpp:124-126
+    if (ROT == 1) coef = O::rpy_coef(erpy);  // src/kinematics.cpp:121-123 + :14-21
+    if (ROT == 2) einv = O::qinverse(e.q);   // src/kinematics.cpp:124-126
 
     // joint columns, src/kinematics.cpp:131-180
     const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
@@ -378,12 +381,12 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
           v[0] = dpos.x;
           v[1] = dpos.y;
           v[2] = dpos.z;
-          if (h.rot_type == 1) {
+          if (ROT == 1) {
             const V dr = O::rpy_derivative(coef, aw);
             v[3] = dr.x;
             v[4] = dr.y;
             v[5] = dr.z;
-          } else if (h.rot_type == 2) {
+          } else if (ROT == 2) {
             const Q dq = O::q_derivative(einv, aw);
             v[3] = dq.x;
             v[4] = dq.y;
@@ -426,12 +429,12 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
         v[1] = dpos.y;
         v[2] = dpos.z;
         v[3] = v[4] = v[5] = T(0);
-        if (h.rot_type == 1) {
+        if (ROT == 1) {
           const V dr = O::rpy_derivative(coef, w);
           v[3] = dr.x;
           v[4] = dr.y;
           v[5] = dr.z;
-        } else if (h.rot_type == 2) {
+        } else if (ROT == 2) {
           const Q dq = O::q_derivative(einv, w);
           v[3] = dq.x;
           v[4] = dq.y;
@@ -447,7 +450,7 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     P be; // tf_blink_to_elink = pose_transform(tf_blink_to_rlink, tf_rlink_to_elink)
     {
       const P binv = bs.binv();
-      if (h.lrec_size == 7) {
+      if (LREC == 7) {
         be = O::compose(binv, e);
       } else { // IGNORE: only the position rows exist and they never read the link rotation
         const V r = O::rotate(binv.q, e.p);
@@ -464,7 +467,7 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
       bk.q = bs.bk(k);
       V pk;
       Q qk = O::qidentity();
-      if (h.lrec_size == 7) {
+      if (LREC == 7) {
         const P t = O::compose(bk, be);
         pk = t.p;
         qk = t.q;
@@ -475,20 +478,28 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
         pk.z = r.z + bk.p.z;
       }
       T v[7];
+      v[0] = pk.x - e.p.x;
+      v[1] = pk.y - e.p.y;
+      v[2] = pk.z - e.p.z;
       v[3] = v[4] = v[5] = v[6] = T(0);
-      v[0] = M::div_(pk.x - e.p.x, deps);
-      v[1] = M::div_(pk.y - e.p.y, deps);
-      v[2] = M::div_(pk.z - e.p.z, deps);
-      if (h.rot_type == 1) {
+      if (ROT == 1) {
         const V rk = O::to_rpy(qk);
-        v[3] = M::div_(rk.x - erpy.x, deps);
-        v[4] = M::div_(rk.y - erpy.y, deps);
-        v[5] = M::div_(rk.z - erpy.z, deps);
-      } else if (h.rot_type == 2) {
-        v[3] = M::div_(qk.x - e.q.x, deps);
-        v[4] = M::div_(qk.y - e.q.y, deps);
-        v[5] = M::div_(qk.z - e.q.z, deps);
-        v[6] = M::div_(qk.w - e.q.w, deps);
+        v[3] = rk.x - erpy.x;
+        v[4] = rk.y - erpy.y;
+        v[5] = rk.z - erpy.z;
+      } else if (ROT == 2) {
+        v[3] = qk.x - e.q.x;
+        v[4] = qk.y - e.q.y;
+        v[5] = qk.z - e.q.z;
+        v[6] = qk.w - e.q.w;
+      }
+      { // (.. - ..) / eps for the D entries of the column, src/kinematics.cpp:212-231
+        T num[D];
+        TFK_UNROLL
+        for (int r = 0; r < D; ++r) num[r] = v[r];
+        M::divn_(num, deps);
+        TFK_UNROLL
+        for (int r = 0; r < D; ++r) v[r] = num[r];
       }
       out.put_J(h.n_cols + n_trans + (k - k0), v);
     }
@@ -501,9 +512,9 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
     T *rec;
     int stride;
     TFK_FN void link(int lrec, const P &cur) const {
-      const int at = h->off_lrec + lrec * h->lrec_size;
+      const int at = h->off_lrec + lrec * LREC;
       put_vec(rec, stride, at, cur.p);
-      if (h->lrec_size == 7) put_quat(rec, stride, at + 3, cur.q);
+      if (LREC == 7) put_quat(rec, stride, at + 3, cur.q);
     }
   };
   static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) {
@@ -522,11 +533,11 @@ template <class M, bool ANALYTIC_BASE> struct FkCore {
   // two-phase driver, phase B: one thread per (configuration, requested link)
   template <class OutSink> static TFK_FN void phase_b(const PlanView &pv, const T *rec, int stride, int o, OutSink &out) {
     const PlanHeader &h = *pv.h;
-    const int lat = h.off_lrec + pv.lrec_of_out[o] * h.lrec_size;
+    const int lat = h.off_lrec + pv.lrec_of_out[o] * LREC;
     P e;
     e.p = get_vec(rec, stride, lat);
     e.q = O::qidentity();
-    if (h.lrec_size == 7) e.q = get_quat(rec, stride, lat + 3);
+    if (LREC == 7) e.q = get_quat(rec, stride, lat + 3);
     BaseFromRec bs;
     bs.rec = rec;
     bs.stride = stride;

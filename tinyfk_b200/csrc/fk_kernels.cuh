@@ -37,56 +37,47 @@ enum { TFK_STG = 32 * 7 }; // reals in a warp's staging strip: 32 rows x pose_di
 
 // Output sink of the kernels.  put_J must be called by all 32 lanes of the warp together, once per
 // Jacobian column, in increasing column order (it advances a running column pointer).
-template <class T> struct StagedSink {
+template <class T, int D> struct StagedSink {
   T *pP;   // P + head: this lane's row in column 0 of P (head = row*n_out + o)
   T *pJ;   // J + head0*D + lane: this lane's first element of the warp's run in the current column of J
   long long ldP, ldJ;
   T *stg_w; // warp-private strip of TFK_STG reals, + lane*D (where this lane's column entries go)
   T *stg_r; // the strip + lane (what this lane copies out)
-  int D, lane, cnt; // cnt = valid lanes * D
+  int lane, cnt; // cnt = valid lanes * D
   bool valid;
 
   __device__ __forceinline__ void begin() const { __syncwarp(); }
   __device__ __forceinline__ void put_P(int d, T v) const {
     if (valid) __stcs(pP + d * ldP, v);
   }
-  template <int DD> __device__ __forceinline__ void put_rows(const T (&v)[7]) {
+  __device__ __forceinline__ void put_J(int, const T (&v)[7]) {
 #pragma unroll
-    for (int r = 0; r < DD; ++r) stg_w[r] = v[r];
+    for (int r = 0; r < D; ++r) stg_w[r] = v[r];
     __syncwarp();
-    if (cnt == 32 * DD) { // full warp: DD coalesced 256-byte (FP64) stores, no predicates
+    if (cnt == 32 * D) { // full warp: D coalesced 256-byte (FP64) stores, no predicates
 #pragma unroll
-      for (int k = 0; k < DD; ++k) __stcs(pJ + 32 * k, stg_r[32 * k]);
+      for (int k = 0; k < D; ++k) __stcs(pJ + 32 * k, stg_r[32 * k]);
     } else {
 #pragma unroll
-      for (int k = 0; k < DD; ++k)
+      for (int k = 0; k < D; ++k)
         if (lane + 32 * k < cnt) __stcs(pJ + 32 * k, stg_r[32 * k]);
     }
     __syncwarp();
     pJ += ldJ;
   }
-  __device__ __forceinline__ void put_J(int, const T (&v)[7]) {
-    if (D == 6)
-      put_rows<6>(v);
-    else if (D == 3)
-      put_rows<3>(v);
-    else
-      put_rows<7>(v);
-  }
 };
 
 // builds the sink of one warp-load of consecutive rows: head0 = P row of lane 0, nvalid = rows present
-template <class T> struct StagedFactory {
-  typedef StagedSink<T> Sink;
+template <class T, int D> struct StagedFactory {
+  typedef StagedSink<T, D> Sink;
   T *P, *J;
   long long ldP, head0;
-  int D, nvalid;
+  int nvalid;
   T *stg;
   __device__ __forceinline__ Sink make() const {
     Sink s;
     const int lane = threadIdx.x & 31;
     s.lane = lane;
-    s.D = D;
     s.ldP = ldP;
     s.ldJ = ldP * D;
     s.pP = P + head0 + lane;
@@ -145,11 +136,10 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs 
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-  StagedFactory<T> fac;
+  StagedFactory<T, Core::D> fac;
   fac.P = static_cast<T *>(a.P);
   fac.J = static_cast<T *>(a.J);
   fac.ldP = a.ld_cfg; // n_out == 1
-  fac.D = h.pose_dim;
   fac.stg = qs + warp * 32 * L.q_pitch; // the warp's own q rows, dead once the walk has read them
 
   const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
@@ -192,11 +182,10 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-  StagedFactory<T> fac;
+  StagedFactory<T, Core::D> fac;
   fac.P = static_cast<T *>(a.P);
   fac.J = static_cast<T *>(a.J);
   fac.ldP = a.ld_cfg * h.n_out;
-  fac.D = h.pose_dim;
   fac.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
 
   const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
@@ -217,7 +206,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
       const int o = itc - il * h.n_out;
       fac.nvalid = items - it0 < 32 ? items - it0 : 32;
       fac.head0 = hbase + it0;
-      StagedSink<T> out = fac.make();
+      StagedSink<T, Core::D> out = fac.make();
       Core::phase_b(pv, rec + il, TFK_TILE, o, out);
     }
     __syncthreads();
@@ -225,7 +214,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
 }
 
 template <class Core>
-cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
+cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
   if (variant == KV_FUSED_SMEM)
     fk_fused_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_FUSED_GMEM)
@@ -235,7 +224,7 @@ cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, in
   return cudaGetLastError();
 }
 
-template <class Core> cudaError_t occupancy_fk(int variant, int smem_bytes, int *blocks_per_sm) {
+template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
   const void *fn = variant == KV_FUSED_SMEM   ? (const void *)fk_fused_kernel<Core, true>
                    : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false>
                                               : (const void *)fk_twophase_kernel<Core>;
@@ -243,6 +232,19 @@ template <class Core> cudaError_t occupancy_fk(int variant, int smem_bytes, int 
   if (smem_bytes > 48 * 1024) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fn, TFK_TILE, smem_bytes);
+}
+
+// one instantiation per RotationType (the pose dimension is a compile-time constant of the kernels)
+template <class M, bool ANALYTIC_BASE>
+cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
+  if (pp.h.rot_type == 0) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 0>>(a, pp, variant, grid, smem_bytes, stream);
+  if (pp.h.rot_type == 1) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 1>>(a, pp, variant, grid, smem_bytes, stream);
+  return launch_fk_core<FkCore<M, ANALYTIC_BASE, 2>>(a, pp, variant, grid, smem_bytes, stream);
+}
+template <class M, bool ANALYTIC_BASE> cudaError_t occupancy_fk(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
+  if (rot_type == 0) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 0>>(variant, smem_bytes, blocks_per_sm);
+  if (rot_type == 1) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 1>>(variant, smem_bytes, blocks_per_sm);
+  return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 2>>(variant, smem_bytes, blocks_per_sm);
 }
 
 } // namespace tfk

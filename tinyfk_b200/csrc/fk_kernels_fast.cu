@@ -4,13 +4,11 @@
 #include "fk_kernels.cuh"
 
 namespace tfk {
-typedef FkCore<MathNative32, true> CoreF32;
-
 cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
     cudaStream_t stream) {
-  return launch_fk<CoreF32>(a, pp, variant, grid, smem_bytes, stream);
+  return launch_fk<MathNative32, true>(a, pp, variant, grid, smem_bytes, stream);
 }
-cudaError_t occupancy_fk_f32(int variant, int smem_bytes, int *blocks_per_sm) {
-  return occupancy_fk<CoreF32>(variant, smem_bytes, blocks_per_sm);
+cudaError_t occupancy_fk_f32(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
+  return occupancy_fk<MathNative32, true>(rot_type, variant, smem_bytes, blocks_per_sm);
 }
 } // namespace tfk

@@ -4,13 +4,11 @@
 #include "fk_kernels.cuh"
 
 namespace tfk {
-typedef FkCore<MathPortable, false> CoreStrict64;
-
 cudaError_t launch_fk_f64_strict(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
     cudaStream_t stream) {
-  return launch_fk<CoreStrict64>(a, pp, variant, grid, smem_bytes, stream);
+  return launch_fk<MathPortable, false>(a, pp, variant, grid, smem_bytes, stream);
 }
-cudaError_t occupancy_fk_f64_strict(int variant, int smem_bytes, int *blocks_per_sm) {
-  return occupancy_fk<CoreStrict64>(variant, smem_bytes, blocks_per_sm);
+cudaError_t occupancy_fk_f64_strict(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
+  return occupancy_fk<MathPortable, false>(rot_type, variant, smem_bytes, blocks_per_sm);
 }
 } // namespace tfk

@@ -56,10 +56,10 @@ TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem,
 
 cudaError_t launch_fk_f64_strict(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
                                  cudaStream_t stream);
-cudaError_t occupancy_fk_f64_strict(int variant, int smem_bytes, int *blocks_per_sm);
+cudaError_t occupancy_fk_f64_strict(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
 cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
                           cudaStream_t stream);
-cudaError_t occupancy_fk_f32(int variant, int smem_bytes, int *blocks_per_sm);
+cudaError_t occupancy_fk_f32(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
 
 } // namespace tfk
 #endif

@@ -27,6 +27,11 @@
 #define TFK_FN inline
 #define TFK_FN_CALL inline
 #endif
+#if defined(__CUDACC__)
+#define TFK_MATH_UNROLL _Pragma("unroll")
+#else
+#define TFK_MATH_UNROLL
+#endif
 
 namespace tfk {
 
@@ -107,6 +112,34 @@ struct MathPortable {
     return fma(r, d.y, q);
 #endif
   }
+  // N quotients by one denominator with ONE range test for all numerators (the common case: every
+  // numerator is an ordinary number); otherwise each goes through div_ on its own.
+  template <int N> static TFK_FN void divn_(double (&a)[N], const Den &d) {
+    uint32_t bad = d.ok ? 0u : 1u;
+    TFK_MATH_UNROLL
+    for (int i = 0; i < N; ++i) bad |= (((uint32_t)tfk_hi32(a[i]) & 0x7fffffffu) - 0x27000000u) >= 0x32000000u ? 1u : 0u;
+    if (bad) {
+      TFK_MATH_UNROLL
+      for (int i = 0; i < N; ++i) a[i] = div_(a[i], d);
+      return;
+    }
+    TFK_MATH_UNROLL
+    for (int i = 0; i < N; ++i) {
+#if defined(__CUDA_ARCH__)
+      double q = __dmul_rn(a[i], d.y);
+      double r = __fma_rn(-d.b, q, a[i]);
+      q = __fma_rn(r, d.y, q);
+      r = __fma_rn(-d.b, q, a[i]);
+      a[i] = __fma_rn(r, d.y, q);
+#else
+      double q = a[i] * d.y;
+      double r = fma(-d.b, q, a[i]);
+      q = fma(r, d.y, q);
+      r = fma(-d.b, q, a[i]);
+      a[i] = fma(r, d.y, q);
+#endif
+    }
+  }
 };
 
 // The platform's own libm (glibc on the host, libdevice on the GPU).
@@ -135,6 +168,9 @@ struct MathNative64 {
     return d;
   }
   static TFK_FN double div_(double a, const Den &d) { return a / d.b; }
+  template <int N> static TFK_FN void divn_(double (&a)[N], const Den &d) {
+    for (int i = 0; i < N; ++i) a[i] = a[i] / d.b;
+  }
 };
 
 struct MathNative32 {
@@ -162,6 +198,9 @@ struct MathNative32 {
     return d;
   }
   static TFK_FN float div_(float a, const Den &d) { return a / d.b; }
+  template <int N> static TFK_FN void divn_(float (&a)[N], const Den &d) {
+    for (int i = 0; i < N; ++i) a[i] = a[i] / d.b;
+  }
 };
 
 template <class M> struct Ops {
@@ -192,11 +231,12 @@ template <class M> struct Ops {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r = qidentity();
     if (norm > T(0)) {
-      const typename M::Den d = M::den_(norm);
-      r.w = M::div_(q.w, d);
-      r.x = M::div_(-q.x, d);
-      r.y = M::div_(-q.y, d);
-      r.z = M::div_(-q.z, d);
+      T a[4] = {q.w, -q.x, -q.y, -q.z};
+      M::divn_(a, M::den_(norm));
+      r.w = a[0];
+      r.x = a[1];
+      r.y = a[2];
+      r.z = a[3];
     }
     return r;
   }
@@ -205,11 +245,12 @@ template <class M> struct Ops {
   static TFK_FN Q qinverse(const Q &q) {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r;
-    const typename M::Den d = M::den_(norm);
-    r.x = M::div_(-q.x, d);
-    r.y = M::div_(-q.y, d);
-    r.z = M::div_(-q.z, d);
-    r.w = M::div_(q.w, d);
+    T a[4] = {-q.x, -q.y, -q.z, q.w};
+    M::divn_(a, M::den_(norm));
+    r.x = a[0];
+    r.y = a[1];
+    r.z = a[2];
+    r.w = a[3];
     return r;
   }
 
@@ -339,11 +380,12 @@ template <class M> struct Ops {
     if (s == T(0)) {
       q = qidentity();
     } else {
-      const typename M::Den d = M::den_(s);
-      q.x = M::div_(q.x, d);
-      q.y = M::div_(q.y, d);
-      q.z = M::div_(q.z, d);
-      q.w = M::div_(q.w, d);
+      T a[4] = {q.x, q.y, q.z, q.w};
+      M::divn_(a, M::den_(s));
+      q.x = a[0];
+      q.y = a[1];
+      q.z = a[2];
+      q.w = a[3];
     }
   }
 
@@ -421,11 +463,12 @@ template <class M> struct Ops {
   static TFK_FN P inverse(const P &a) {
     P o;
     T norm = a.q.w * a.q.w + a.q.x * a.q.x + a.q.y * a.q.y + a.q.z * a.q.z;
-    const typename M::Den d = M::den_(norm);
-    o.q.w = M::div_(a.q.w, d);
-    o.q.x = M::div_(-a.q.x, d);
-    o.q.y = M::div_(-a.q.y, d);
-    o.q.z = M::div_(-a.q.z, d);
+    T qa[4] = {a.q.w, -a.q.x, -a.q.y, -a.q.z};
+    M::divn_(qa, M::den_(norm));
+    o.q.w = qa[0];
+    o.q.x = qa[1];
+    o.q.y = qa[2];
+    o.q.z = qa[3];
     V n;
     n.x = a.p.x * T(-1);
     n.y = a.p.y * T(-1);
@@ -456,13 +499,14 @@ template <class M> struct Ops {
     M::sincos_(a2, &s2, &c2);
     M::sincos_(a3, &s3, &c3);
     RpyCoef k;
-    const typename M::Den d = M::den_(c2);
-    k.k_xx = M::div_(c3, d);
-    k.k_xy = M::div_(s3, d);
+    T a[4] = {c3, s3, -c3 * s2, s3 * s2};
+    M::divn_(a, M::den_(c2));
+    k.k_xx = a[0];
+    k.k_xy = a[1];
     k.s3 = s3;
     k.c3 = c3;
-    k.k_zx = M::div_(-c3 * s2, d);
-    k.k_zy = M::div_(s3 * s2, d);
+    k.k_zx = a[2];
+    k.k_zy = a[3];
     return k;
   }
   static TFK_FN V rpy_derivative(const RpyCoef &k, const V &axis) {

@@ -66,6 +66,25 @@ TFK_HD int32_t tfk_lo32(double x) {
 #endif
 }
 
+/* x with its sign bit XORed with bit 31 of `mask` (a conditional negation as ONE integer instruction on
+   the high word; -x is exact, so this equals `cond ? -x : x`) */
+TFK_HD double tfk_xor_sign(double x, int32_t mask) {
+#if defined(__CUDA_ARCH__)
+  return __hiloint2double(__double2hiint(x) ^ (mask & (int32_t)0x80000000), __double2loint(x));
+#else
+  uint64_t u;
+  memcpy(&u, &x, sizeof u);
+  u ^= ((uint64_t)((uint32_t)mask & 0x80000000u)) << 32;
+  memcpy(&x, &u, sizeof x);
+  return x;
+#endif
+}
+/* bits of |x| as an unsigned integer: for non-NaN doubles a < b  <=>  bits(|a|) < bits(|b|), so
+   threshold tests run on the integer pipe instead of the FP64 pipe */
+TFK_HD uint64_t tfk_abs_bits(double x) {
+  return (((uint64_t)((uint32_t)tfk_hi32(x) & 0x7fffffffu)) << 32) | (uint32_t)tfk_lo32(x);
+}
+
 /* tfk_ksin / tfk_kcos with the early exits turned into final selects */
 TFK_HD double tfk_ksin_simt(double x, double y) {
   double z = x * x;
@@ -79,16 +98,16 @@ TFK_HD double tfk_ksin_simt(double x, double y) {
 
 TFK_HD double tfk_kcos_simt(double x, double y) {
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
-  double ax = fabs(x);
   double z = x * x;
   double r = z * (TFK_KC(c1, TFK_C1) +
                   z * (TFK_KC(c2, TFK_C2) +
                        z * (TFK_KC(c3, TFK_C3) + z * (TFK_KC(c4, TFK_C4) + z * (TFK_KC(c5, TFK_C5) + z * TFK_KC(c6, TFK_C6))))));
   /* ax < 0.3: qx = 0 gives hz = 0.5*z - 0 = 0.5*z and a = 1 - 0 = 1, i.e. fkmath.h's first form.
      (0.3 has a non-zero low word: keep the FP64 compare.)  0.78125 = 0x3fe90000_00000000. */
+  const uint64_t ux = tfk_abs_bits(x);
   double qx = tfk_from_hi32(hx - 0x00200000);
-  if (hx > 0x3fe90000 || (hx == 0x3fe90000 && tfk_lo32(x) != 0)) qx = 0.28125;
-  if (ax < 0.3) qx = 0.0;
+  qx = (ux > 0x3fe9000000000000ull) ? 0.28125 : qx; /* ax > 0.78125 */
+  qx = (ux < 0x3fd3333333333333ull) ? 0.0 : qx;     /* ax < 0.3 = 0x3fd33333_33333333 */
   double hz = 0.5 * z - qx;
   double a = 1.0 - qx;
   double p = a - (hz - (z * r - x * y));
@@ -108,7 +127,7 @@ TFK_HD TfkSinCos tfk_sincos_simt(double x) {
     return out;
   }
   const double t = fabs(x);
-  const int small = t <= TFK_PIO4_HI;
+  const int small = tfk_abs_bits(x) <= 0x3fe921fb54442d18ull; /* |x| <= TFK_PIO4_HI */
   /* first reduction stage for every lane (harmless when small) */
   int n = (int)(t * TFK_KC(invpio2, TFK_INVPIO2) + 0.5);
   const double fn = (double)n;
@@ -141,16 +160,16 @@ TFK_HD TfkSinCos tfk_sincos_simt(double x) {
     a1 = 0.0;
   }
   /* fkmath.h: small -> kernels on (x, 0.0); else on (+-a0, +-a1) with n negated for x < 0 */
-  const int neg = tfk_hi32(x) < 0;
-  const double y0 = neg ? -a0 : a0;
-  const double y1 = (neg && !small) ? -a1 : a1;
-  if (neg) n = -n;
+  const int32_t sx = tfk_hi32(x); /* bit 31 = sign of x */
+  const double y0 = tfk_xor_sign(a0, sx);
+  const double y1 = tfk_xor_sign(a1, small ? 0 : sx);
+  if (sx < 0) n = -n;
   const double ks = tfk_ksin_simt(y0, y1), kc = tfk_kcos_simt(y0, y1);
   /* n&3: 0 (ks, kc)  1 (kc, -ks)  2 (-ks, -kc)  3 (-kc, ks) */
   double ss = (n & 1) ? kc : ks;
   double cc = (n & 1) ? ks : kc;
-  if (n & 2) ss = -ss;
-  if ((n + 1) & 2) cc = -cc;
+  ss = tfk_xor_sign(ss, (int32_t)((uint32_t)n << 30));       /* n & 2 */
+  cc = tfk_xor_sign(cc, (int32_t)((uint32_t)(n + 1) << 30)); /* (n + 1) & 2 */
   out.s = ss;
   out.c = cc;
   return out;
@@ -177,7 +196,7 @@ TFK_HD double tfk_asin_simt(double x) {
   if (!big) return x + x * rr;
   const double s = sqrt(t);
   double res;
-  if (ax >= 0.975) {
+  if (tfk_abs_bits(x) >= 0x3fef333333333333ull) { /* ax >= 0.975 */
     res = TFK_PIO2_HI - (2.0 * (s + s * rr) - TFK_PIO2_LO);
   } else {
     const double w = tfk_from_hi32(tfk_hi32(s));
@@ -186,7 +205,7 @@ TFK_HD double tfk_asin_simt(double x) {
     const double qq = TFK_PIO4_HI - 2.0 * w;
     res = TFK_PIO4_HI - (pp - qq);
   }
-  return (x > 0.0) ? res : -res;
+  return tfk_xor_sign(res, tfk_hi32(x)); /* x > 0 ? res : -res (x is neither 0 nor NaN here) */
 }
 
 /* atan of ax >= 2^-29, finite, < 2^66; returns atan(ax) >= 0.  Bit-identical to tfk_atan(ax):
@@ -244,7 +263,7 @@ TFK_HD double tfk_atan2_simt(double y, double x) {
   double z = (ha < 0x3e200000) ? a : tfk_atan_pos_simt(a); /* |a| < 2^-29: atan(a) = a */
   /* m = signbit(y) | signbit(x) << 1:  0: z   1: -z   2: pi - (z - pi_lo)   3: (z - pi_lo) - pi */
   if (hxs < 0) z = TFK_PI - (z - TFK_PI_LO);
-  return (hys < 0) ? -z : z;
+  return tfk_xor_sign(z, hys);
 }
 
 #endif /* TFK_FKMATH_SIMT_H */
