@@ -204,7 +204,9 @@ def measured_peaks():
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from the committed
 # `ncu --set full` capture (profiles/), keyed by workload; None until a capture exists
-NCU_TRAFFIC_BYTES = {}
+NCU_TRAFFIC_BYTES = {
+    ("cfg2", "fp64"): 577.5e6,  # profiles/r1_full_cfg2_strict_v5.txt: 84.0 MB read + 493.5 MB written (algorithmic 637.5 MB)
+}
 
 
 # ---- our arm ---------------------------------------------------------------------------------------
@@ -324,8 +326,10 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES.get((cfg, args.precision)),
                          "peak_source": peak_src, "algorithmic_bytes_per_config": bytes_per_cfg,
-                         "kernel": "fk_batch_kernel", "kernel_ms": kern_ms,
-                         "note": "strict FP64 is FP64-pipe bound, not HBM bound (DESIGN.md)"},
+                         "kernel": info.get("kernel"), "kernel_ms": kern_ms,
+                         "note": ("bit-faithful FP64 (no FMA contraction, IEEE divisions, portable libm) is bound by "
+                                  "instruction issue / the FP64 pipe, not by HBM: DESIGN.md section 3") if not prec
+                                 else "FP32 opt-in mode"},
         }
         if e2e is not None:
             out["e2e"] = e2e

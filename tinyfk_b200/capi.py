@@ -22,7 +22,7 @@ SYMBOLS = [
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
     "tfk_solve_fk_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
-    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_version",
+    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
 ]
 
 _lib = None
@@ -253,7 +253,12 @@ class Model:
     def last_launch_info(self):
         v = [ctypes.c_int() for _ in range(5)]
         _check(self._L.tfk_last_launch_info(self._h, *[ctypes.byref(x) for x in v]))
-        return dict(zip(("grid", "block", "smem_bytes", "blocks_per_sm", "rec_reals"), [x.value for x in v]))
+        d = dict(zip(("grid", "block", "smem_bytes", "blocks_per_sm", "rec_reals"), [x.value for x in v]))
+        self._L.tfk_last_launch_variant.argtypes = [_vp]
+        k = int(self._L.tfk_last_launch_variant(self._h))
+        d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
+                       2: "fk_twophase_kernel"}.get(k, "none")
+        return d
 
 
 def kernel_launch_count():

@@ -263,4 +263,6 @@ int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int *smem_by
   });
 }
 
+int tfk_last_launch_variant(const tfk_model *m) { return m ? m->engine.last_launch.variant : -1; }
+
 } // extern "C"
