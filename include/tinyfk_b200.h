@@ -128,7 +128,7 @@ TFK_API int64_t tfk_kernel_launch_count(void);
 TFK_API int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int *smem_bytes, int *blocks_per_sm,
                                  int *rec_reals);
 /* which kernel the last launch used: 0 fused single-link (records in shared memory), 1 fused single-link
-   (records in global scratch), 2 two-phase multi-link -- see tinyfk_b200/csrc/fk_kernels.cuh */
+   (records in global scratch), 2 two-phase multi-link, 3 = 0 built for five resident blocks per SM -- see tinyfk_b200/csrc/fk_kernels.cuh */
 TFK_API int tfk_last_launch_variant(const tfk_model *m);
 TFK_API const char *tfk_version(void);
 

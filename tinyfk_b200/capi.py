@@ -257,7 +257,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>"}.get(k, "none")
         return d
 
 

@@ -209,6 +209,8 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     if (L.total > 100 * 1024) { // keep at least two blocks per SM; beyond that records go to L2
       L = smem_layout(plan_bytes, h->n_in, 0, rb);
       variant = KV_FUSED_GMEM;
+    } else if (5 * (L.total + 1024) <= 228 * 1024) {
+      variant = KV_FUSED_SMEM5; // a fifth block fits next to four: take the build that leaves registers for it
     }
   } else {
     rec_reals = h->rec_size;

@@ -131,7 +131,9 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
   // Base pose of this configuration.  FIXED: the model's stored pose (include/tinyfk.hpp:72,
   // kinematics.cpp:51); otherwise src/wrapper.cpp:25-35 on the row tail (PLANER rows are (x, y, yaw),
   // padded to (x, y, 0, 0, 0, yaw) by python/tinyfk/__init__.py:98-103).
-  static TFK_FN P base_pose_of(const PlanHeader &h, const T *qrow) {
+  static TFK_FN P base_pose_of(const PlanHeader &h, const T *qrow) { return base_pose_from_tail(h, qrow + h.n_cols); }
+  // b: the row tail (x, y, yaw | x, y, z, roll, pitch, yaw); not read for a FIXED base
+  static TFK_FN P base_pose_from_tail(const PlanHeader &h, const T *b) {
     P base;
     if (h.base_type == 0) {
       base.p.x = T(h.base_pose[0]);
@@ -143,7 +145,6 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
       base.q.w = T(h.base_pose[6]);
       return base;
     }
-    const T *b = qrow + h.n_cols;
     base.p.x = b[0];
     base.p.y = b[1];
     if (h.base_type == 1) {
@@ -225,8 +226,8 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
     TFK_FN Q bk(int k) const { return get_quat(rec, stride, at + 14 + 4 * k); }
     TFK_FN V w(int k) const { return get_vec(rec, stride, at + 7 + 3 * k); }
   };
-  // fused: one link per configuration, so everything is computed where it is used; only the base
-  // pose itself is re-read from the record
+  // fused: one link per configuration, so everything is computed where it is used; only the base pose
+  // itself is re-read from the record (it exists only for a Jacobian with a moving base)
   struct BaseComputed {
     const T *rec;
     int stride;
@@ -249,7 +250,9 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
   // (element k at rec[k*stride]); o_base / o_arec / o_prec / o_frame: where the base pose (already
   // stored by the caller), axis, position and frame records are.  sink.link(lrec, pose) is called for
   // every requested link, in tree order.  Returns the pose of the last slot.
-  template <class LinkSink>
+  // BASE_REC = false (fused driver): no base record; the only child of the root that is walked is slot 0,
+  // whose parent frame is the initial `cur`.
+  template <bool BASE_REC, class LinkSink>
   static TFK_FN P walk(const PlanView &pv, const T *qrow, T *rec, int stride, int o_base, int o_arec, int o_prec,
                        int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
@@ -257,8 +260,8 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
     TFK_NOUNROLL
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
-      if (sl.frame_ld != FRAME_RUNNING) // a child of the root, or the second.. child of a branch point
-        cur = get_pose(rec, stride, sl.frame_ld == FRAME_BASE ? o_base : o_frame + 7 * sl.frame_ld);
+      if (sl.frame_ld != FRAME_RUNNING && (BASE_REC || sl.frame_ld != FRAME_BASE)) // a child of the root, or the
+        cur = get_pose(rec, stride, sl.frame_ld == FRAME_BASE ? o_base : o_frame + 7 * sl.frame_ld); // 2nd.. child of a branch point
       // pose_transform(parent, local), pose.cpp:139-146: position first (it uses the parent's rotation)
       T ang = T(0);
       if (sl.kind != SLOT_FIXED) ang = qrow[sl.qcol];
@@ -527,7 +530,7 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
     sink.rec = rec;
     sink.stride = stride;
     if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
-    walk(pv, qrow, rec, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
+    walk<true>(pv, qrow, rec, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
   }
 
   // two-phase driver, phase B: one thread per (configuration, requested link)
@@ -557,12 +560,12 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
   static TFK_FN void run_fused(const PlanView &pv, const T *qrow, T *rec, int stride, const OutFactory &make_out) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
-    put_pose(rec, stride, 0, base);
-    const P e = walk(pv, qrow, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
-    typename OutFactory::Sink out = make_out.make();
+    if (h.fz_arec > 0) put_pose(rec, stride, 0, base); // Jacobian with a moving base: re-read for the base columns
+    const P e = walk<false>(pv, qrow, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
     BaseComputed bs;
     bs.rec = rec;
     bs.stride = stride;
+    typename OutFactory::Sink out = make_out.make();
     emit_link(pv, e, 0, rec, stride, h.fz_arec, h.fz_prec, bs, out);
   }
 };

@@ -117,8 +117,9 @@ template <class T> __device__ __forceinline__ void prefetch_q_tile(const T *q, l
   if ((long long)threadIdx.x * 128 < rows * n_in * (long long)sizeof(T)) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
-template <class Core, bool SMEM_REC>
-__global__ void __launch_bounds__(TFK_TILE, 4) fk_fused_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+// BPS: resident blocks per SM the register allocation aims at (5 when the shared-memory footprint allows it)
+template <class Core, bool SMEM_REC, int BPS>
+__global__ void __launch_bounds__(TFK_TILE, BPS) fk_fused_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
   PlanView pv;
@@ -215,18 +216,21 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
 
 template <class Core>
 cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
-  if (variant == KV_FUSED_SMEM)
-    fk_fused_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+  if (variant == KV_FUSED_SMEM5)
+    fk_fused_kernel<Core, true, 5><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+  else if (variant == KV_FUSED_SMEM)
+    fk_fused_kernel<Core, true, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_FUSED_GMEM)
-    fk_fused_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+    fk_fused_kernel<Core, false, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else
     fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
 }
 
 template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
-  const void *fn = variant == KV_FUSED_SMEM   ? (const void *)fk_fused_kernel<Core, true>
-                   : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false>
+  const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>
+                   : variant == KV_FUSED_SMEM ? (const void *)fk_fused_kernel<Core, true, 4>
+                   : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false, 4>
                                               : (const void *)fk_twophase_kernel<Core>;
   cudaError_t e = cudaSuccess;
   if (smem_bytes > 48 * 1024) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);

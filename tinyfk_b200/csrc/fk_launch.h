@@ -19,6 +19,8 @@ enum KernelVariant {
   KV_FUSED_SMEM = 0, // one requested link, joint records in shared memory
   KV_FUSED_GMEM = 1, // one requested link, records too large for shared memory: block-private global scratch
   KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
+  KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
+                      // shared-memory footprint leaves room for the fifth block
 };
 
 struct KernelArgs {

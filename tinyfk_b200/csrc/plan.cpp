@@ -249,7 +249,7 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.off_frame = h.off_lrec + h.lrec_size * n_lrec;
   h.rec_size = h.off_frame + 7 * b.frames_max;
   // fused single-link kernel: the link pose and the base context stay in registers
-  h.fz_arec = 7;
+  h.fz_arec = (jac && key.base_type != BASE_FIXED) ? 7 : 0; // base pose, re-read for the base columns
   h.fz_prec = h.fz_arec + 3 * n_arec;
   h.fz_frame = h.fz_prec + 3 * n_prec;
   h.fz_size = h.fz_frame + 7 * b.frames_max;
