@@ -117,6 +117,24 @@ TFK_API int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const vo
                                 int rot_type, int base_type, int with_jacobian, int precision, void *d_P,
                                 void *d_J, int64_t ld_cfg, int64_t row0);
 
+/* ---- inter-link squared distances ------------------------------- */
+/* KinematicsModelPyWrapper::compute_inter_link_squared_dists (src/wrapper.cpp:189-237) + the facade glue of
+ * KinematicModel.compute_inter_link_sqdists (python/tinyfk/__init__.py:233-266), batched on the GPU: for every
+ * configuration i and pair j = (link_ids1[j], link_ids2[j])
+ *     sqdists[i*n_check + j] = |p1 - p2|^2
+ *     grads[c * (N*n_check) + i*n_check + j] = 2 * (J1[:,c] - J2[:,c]) . (p1 - p2)       (column-major, n_dof columns)
+ * with J1, J2 the position Jacobians of the two links (never materialised).  q, base_type, n_dof, precision
+ * and the stored-state rule are those of tfk_solve_fk_host; grads may be NULL when with_grads == 0.  Runs on the
+ * current device. */
+TFK_API int tfk_inter_link_sqdists_host(tfk_model *m, const void *q, int64_t n, const int *link_ids1,
+                                        const int *link_ids2, int n_check, const int *joint_ids, int n_joint,
+                                        int base_type, int with_grads, int precision, void *sqdists, void *grads);
+/* same on device-resident buffers (see tfk_solve_fk_device for stream / ld_cfg / row0) */
+TFK_API int tfk_inter_link_sqdists_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                          const int *link_ids1, const int *link_ids2, int n_check,
+                                          const int *joint_ids, int n_joint, int base_type, int with_grads,
+                                          int precision, void *d_sqdists, void *d_grads, int64_t ld_cfg, int64_t row0);
+
 /* ---- helpers ---------------------------------------------------------------------------------- */
 TFK_API int tfk_device_count(int *count);
 /* pinned host memory for the host path (pooled; tfk_host_free returns the block to the pool) */

@@ -265,6 +265,73 @@ int tfkref_solve_fk(void *p, const double *qs, long n_wp, const int *elink_ids, 
   }
 }
 
+/*
+ * compute_inter_link_sqdists as the Python user sees it (python/tinyfk/__init__.py:233-266 +
+ * src/wrapper.cpp:189-237).  The link poses and Jacobians come from the reference's own get_link_pose /
+ * get_jacobian; the last three lines of arithmetic are Eigen expressions in the reference
+ * (diff_vec.squaredNorm(), 2 * (jac1 - jac2).transpose() * diff_vec) and Eigen is not available here, so
+ * they are restated in the order written below -- Eigen's internal summation order is NOT pinned (parity
+ * for this entry is a 1e-12 statement, not a bit statement).
+ *   sq     n_wp*n_check values, head = i*n_check + j
+ *   G      column-major (n_wp*n_check) x n_dof_out (n_joint (+3 PLANER: columns n, n+1, n+5 | +6)); may be NULL
+ */
+int tfkref_sqdists(void *p, const double *qs, long n_wp, const int *link_ids1, const int *link_ids2, int n_check,
+                   const int *joint_ids, int n_joint, int base_type, int with_grads, int use_cache, double *sq,
+                   double *G) {
+  try {
+    KinematicModel *kin = static_cast<Handle *>(p)->kin;
+    const bool with_base = base_type != 0;
+    const int n_in = n_joint + (base_type == 1 ? 3 : (base_type == 2 ? 6 : 0));
+    const int n_out = n_in;
+    std::vector<size_t> jids(joint_ids, joint_ids + n_joint);
+    const size_t ld = (size_t)n_wp * n_check;
+    std::vector<double> q(n_joint), b(6);
+    for (long i = 0; i < n_wp; ++i) {
+      const double *row = qs + (size_t)i * n_in;
+      for (int k = 0; k < n_joint; ++k) q[k] = row[k];
+      kin->_set_joint_angles(jids, q); // wrapper.cpp:205
+      if (with_base) {                 // wrapper.cpp:206-209 (+ __init__.py:243-246 for PLANER)
+        if (base_type == 1) {
+          b[0] = row[n_joint];
+          b[1] = row[n_joint + 1];
+          b[2] = 0.0;
+          b[3] = 0.0;
+          b[4] = 0.0;
+          b[5] = row[n_joint + 2];
+        } else {
+          for (int k = 0; k < 6; ++k) b[k] = row[n_joint + k];
+        }
+        set_base_xyzrpy(kin, b.data());
+      }
+      if (!use_cache) kin->clear_cache(); // wrapper.cpp:210-212
+      for (int j = 0; j < n_check; ++j) {
+        const size_t head = (size_t)i * n_check + j;
+        Transform pose1, pose2;
+        kin->get_link_pose(link_ids1[j], pose1);
+        kin->get_link_pose(link_ids2[j], pose2);
+        const urdf::Vector3 diff = pose1.position - pose2.position; // wrapper.cpp:219
+        const double d[3] = {diff.x, diff.y, diff.z};
+        sq[head] = (d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]; // squaredNorm(), wrapper.cpp:222
+        if (with_grads && G) {
+          Eigen::MatrixXd jac1 = kin->get_jacobian(link_ids1[j], jids, RotationType::IGNORE, with_base);
+          Eigen::MatrixXd jac2 = kin->get_jacobian(link_ids2[j], jids, RotationType::IGNORE, with_base);
+          for (int c = 0; c < n_out; ++c) {
+            int src = c; // __init__.py:259-264: PLANER keeps columns [joints, n, n+1, n+5]
+            if (base_type == 1 && c == n_joint + 2) src = n_joint + 5;
+            const double a0 = jac1(0, src) - jac2(0, src), a1 = jac1(1, src) - jac2(1, src),
+                         a2 = jac1(2, src) - jac2(2, src);
+            G[(size_t)c * ld + head] = 2.0 * ((a0 * d[0] + a1 * d[1]) + a2 * d[2]); // wrapper.cpp:230-232
+          }
+        }
+      }
+    }
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
+
 /* which libm is this object bound to?  (tests check the strict build really is pinned) */
 double tfkref_probe_sin(double x) {
   volatile double v = x;

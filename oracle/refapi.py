@@ -94,6 +94,9 @@ def _load_ref(strict):
     lib.tfkref_solve_fk.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp]
     lib.tfkref_solve_fk.restype = ctypes.c_int
+    lib.tfkref_sqdists.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
+                                   ctypes.c_int, ctypes.c_int, _dp, _dp]
+    lib.tfkref_sqdists.restype = ctypes.c_int
     lib.tfkref_probe_sin.argtypes = [ctypes.c_double]
     lib.tfkref_probe_sin.restype = ctypes.c_double
     lib.tfkref_probe_atan2.argtypes = [ctypes.c_double, ctypes.c_double]
@@ -220,6 +223,24 @@ class RefModel:
         if rc:
             raise ValueError(self._lib.tfkref_last_error().decode())
         return P, J
+
+    def inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=0, with_jacobian=False, use_cache=False):
+        """compute_inter_link_sqdists (python/tinyfk/__init__.py:233-266): (sqdists [n*n_check], grads F-order)"""
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        l1 = _as_int_array([p[0] for p in link_id_pairs])
+        l2 = _as_int_array([p[1] for p in link_id_pairs])
+        jids = _as_int_array(joint_ids)
+        n_wp, n_in = qs.shape
+        assert n_in == jids.size + base_dof(base_type), (n_in, jids.size, base_type)
+        sq = np.zeros(n_wp * l1.size)
+        G = np.zeros((n_wp * l1.size, n_in), order="F") if with_jacobian else np.zeros((1, 1))
+        rc = self._lib.tfkref_sqdists(self._h, qs.ctypes.data_as(_dp), n_wp, l1.ctypes.data_as(_ip), l2.ctypes.data_as(_ip),
+                                      l1.size, jids.ctypes.data_as(_ip), jids.size, int(base_type),
+                                      int(bool(with_jacobian)), int(bool(use_cache)), sq.ctypes.data_as(_dp),
+                                      G.ctypes.data_as(_dp) if with_jacobian else None)
+        if rc:
+            raise ValueError(self._lib.tfkref_last_error().decode())
+        return sq, G
 
     def probe_sin(self, x):
         return self._lib.tfkref_probe_sin(float(x))

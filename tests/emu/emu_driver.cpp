@@ -58,7 +58,59 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
     for (size_t k = 0; k < J.size(); ++k) Jd[k] = (double)J[k];
 }
 
+// the pair kernel's per-thread code (FkCore::phase_a + pair_sqdist) on the CPU
+template <class Core, class T>
+static void run_pairs(const std::vector<unsigned char> &blob, const std::vector<int> &o12, int n_check, const double *qs, long n,
+                      double *sq, double *G) {
+  PlanView pv = plan_view(blob.data());
+  const PlanHeader &h = *pv.h;
+  std::vector<T> rec((size_t)(h.rec_size > 0 ? h.rec_size : 1)), qrow((size_t)(h.n_in > 0 ? h.n_in : 1));
+  const long long ld = (long long)n * n_check;
+  std::vector<T> s((size_t)ld), g(G ? (size_t)ld * h.n_out_cols : 1);
+  for (long i = 0; i < n; ++i) {
+    for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
+    Core::phase_a(pv, qrow.data(), rec.data(), 1);
+    for (int j = 0; j < n_check; ++j) {
+      const long long head = (long long)i * n_check + j;
+      Core::pair_sqdist(pv, rec.data(), o12[j], o12[n_check + j], true, &s[head], G ? &g[head] : nullptr, ld);
+    }
+  }
+  for (long long k = 0; k < ld; ++k) sq[k] = (double)s[k];
+  if (G)
+    for (size_t k = 0; k < (size_t)ld * h.n_out_cols; ++k) G[k] = (double)g[k];
+}
+
 extern "C" {
+int emu_sqdists(void *m, const double *qs, long n, const int *l1, const int *l2, int n_check, const int *joints, int n_joint,
+                int base_type, int with_grads, int mode, double *sq, double *G) {
+  try {
+    std::vector<int> links, o12((size_t)2 * n_check);
+    for (int side = 0; side < 2; ++side)
+      for (int j = 0; j < n_check; ++j) {
+        const int id = side == 0 ? l1[j] : l2[j];
+        size_t k = 0;
+        while (k < links.size() && links[k] != id) ++k;
+        if (k == links.size()) links.push_back(id);
+        o12[(size_t)side * n_check + j] = (int)k;
+      }
+    PlanKey key;
+    key.elink_ids = links;
+    key.joint_ids.assign(joints, joints + n_joint);
+    key.rot_type = 0;
+    key.base_type = base_type;
+    key.with_jacobian = with_grads;
+    key.model_version = static_cast<KinematicModel *>(m)->version();
+    std::vector<unsigned char> blob = build_plan(*static_cast<KinematicModel *>(m), key);
+    if (mode == 1)
+      run_pairs<FkCore<MathNative32, true, 0, 1>, float>(blob, o12, n_check, qs, n, sq, with_grads ? G : nullptr);
+    else
+      run_pairs<FkCore<MathPortable, false, 0, 1>, double>(blob, o12, n_check, qs, n, sq, with_grads ? G : nullptr);
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
 // MathPortable::div_ (shared-reciprocal IEEE division, fk_math.h) on arrays: must equal a[i] / b[i]
 void emu_div(const double *a, const double *b, double *o, long n) {
   for (long i = 0; i < n; ++i) o[i] = MathPortable::div_(a[i], MathPortable::den_(b[i]));
@@ -122,11 +174,11 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     double *Jp = with_jacobian ? J : nullptr;
 #define TFK_EMU_RUN(R)                                                                      \
   if (mode == 0)                                                                            \
-    run<FkCore<MathPortable, false, R>, double>(blob, qs, n, P, Jp, two_phase);             \
+    run<FkCore<MathPortable, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);             \
   else if (mode == 1)                                                                       \
-    run<FkCore<MathNative32, true, R>, float>(blob, qs, n, P, Jp, two_phase);               \
+    run<FkCore<MathNative32, true, R, 1>, float>(blob, qs, n, P, Jp, two_phase);               \
   else                                                                                      \
-    run<FkCore<MathNative64, false, R>, double>(blob, qs, n, P, Jp, two_phase);
+    run<FkCore<MathNative64, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);
     if (rot_type == 0) {
       TFK_EMU_RUN(0)
     } else if (rot_type == 1) {

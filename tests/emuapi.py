@@ -44,6 +44,8 @@ def lib():
     L.emu_is_relevant.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
     L.emu_solve.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
                             ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp]
+    L.emu_sqdists.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
+                              ctypes.c_int, ctypes.c_int, _dp, _dp]
     _lib = L
     return L
 
@@ -131,3 +133,17 @@ class EmuModel:
         if rc:
             raise ValueError(self._L.emu_last_error().decode())
         return P, J
+
+    def inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=0, with_jacobian=False, mode=MODE_STRICT64):
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        l1, l2, j = _ints([p[0] for p in link_id_pairs]), _ints([p[1] for p in link_id_pairs]), _ints(joint_ids)
+        n, n_in = qs.shape
+        assert n_in == j.size + {0: 0, 1: 3, 2: 6}[int(base_type)]
+        sq = np.zeros(n * l1.size)
+        G = np.zeros((n * l1.size, n_in), order="F")
+        rc = self._L.emu_sqdists(self._h, qs.ctypes.data_as(_dp), n, l1.ctypes.data_as(_ip), l2.ctypes.data_as(_ip), l1.size,
+                                 j.ctypes.data_as(_ip), j.size, int(base_type), int(bool(with_jacobian)), int(mode),
+                                 sq.ctypes.data_as(_dp), G.ctypes.data_as(_dp))
+        if rc:
+            raise ValueError(self._L.emu_last_error().decode())
+        return sq, G

@@ -156,8 +156,15 @@ class KinematicModel:
     def compute_total_inertia_matrix(self, *args, **kwargs):
         raise NotImplementedError("compute_total_inertia_matrix is outside the accelerated FK path")
 
-    def compute_inter_link_sqdists(self, *args, **kwargs):
-        raise NotImplementedError("compute_inter_link_sqdists is outside the accelerated FK path (next: SURVEY 8f)")
+    def compute_inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=BaseType.FIXED, with_jacobian=False,
+                                   use_cache=False, precision="fp64"):
+        """reference python/tinyfk/__init__.py:233-266 (batched on the GPU; the PLANER pad and column pick are
+        fused into the kernel).  Returns (sqdists [n*n_pairs], grads (n*n_pairs, n_dof)); grads is a 1x1 zero
+        matrix when with_jacobian is false, as in the reference.  use_cache is accepted and ignored."""
+        qs = np.atleast_2d(np.asarray(qs))
+        link_ids1, link_ids2 = (list(x) for x in zip(*link_id_pairs)) if len(link_id_pairs) else ([], [])
+        return self._robot.compute_inter_link_squared_dists_batch(
+            qs, link_ids1, link_ids2, list(joint_ids), base_type.value, bool(with_jacobian), _PRECISION[precision])
 
     def get_joint_names(self) -> List[str]:
         return self._robot.get_joint_names()

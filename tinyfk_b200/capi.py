@@ -21,7 +21,7 @@ SYMBOLS = [
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
-    "tfk_solve_fk_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
+    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
 ]
 
@@ -63,6 +63,10 @@ def lib():
                                     ctypes.c_int, ctypes.c_int, _ip, ctypes.c_int, _vp, _vp]
     L.tfk_solve_fk_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, _ip, ctypes.c_int,
                                       ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
+    L.tfk_inter_link_sqdists_host.argtypes = [_vp, _vp, _i64, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, _vp, _vp]
+    L.tfk_inter_link_sqdists_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int,
+                                                ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
     L.tfk_device_count.argtypes = [_ip]
     L.tfk_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(_vp)]
     L.tfk_host_free.argtypes = [_vp]
@@ -240,6 +244,31 @@ class Model:
                                          J.ctypes.data if with_jacobian else None))
         return P, J
 
+    def inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=0, with_jacobian=False, precision=0):
+        """Host buffers through tfk_inter_link_sqdists_host.  Returns (sqdists [n*n_check], grads F-ordered)."""
+        dt = np.float32 if precision == 1 else np.float64
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=dt)))
+        l1, l2, j = _ints([p[0] for p in link_id_pairs]), _ints([p[1] for p in link_id_pairs]), _ints(joint_ids)
+        n, n_in = qs.shape
+        if n_in != j.size + base_dof(base_type):
+            raise ValueError("dof mismatch")
+        sq = np.zeros(n * l1.size, dtype=dt)
+        G = np.zeros((n * l1.size, n_in), dtype=dt, order="F") if with_jacobian else np.zeros((1, 1), dtype=dt)
+        _check(self._L.tfk_inter_link_sqdists_host(self._h, qs.ctypes.data, n, l1.ctypes.data_as(_ip), l2.ctypes.data_as(_ip),
+                                                   l1.size, j.ctypes.data_as(_ip), j.size, int(base_type),
+                                                   int(bool(with_jacobian)), int(precision), sq.ctypes.data,
+                                                   G.ctypes.data if with_jacobian else None))
+        return sq, G
+
+    def inter_link_sqdists_device(self, device, stream, d_q, n, link_id_pairs, joint_ids, base_type, with_jacobian, precision,
+                                  d_sq, d_G, ld_cfg=None, row0=0):
+        l1, l2, j = _ints([p[0] for p in link_id_pairs]), _ints([p[1] for p in link_id_pairs]), _ints(joint_ids)
+        _check(self._L.tfk_inter_link_sqdists_device(self._h, int(device), _vp(stream), _vp(d_q), int(n),
+                                                     l1.ctypes.data_as(_ip), l2.ctypes.data_as(_ip), l1.size,
+                                                     j.ctypes.data_as(_ip), j.size, int(base_type), int(bool(with_jacobian)),
+                                                     int(precision), _vp(d_sq), _vp(d_G) if d_G else None,
+                                                     int(ld_cfg if ld_cfg is not None else n), int(row0)))
+
     def solve_fk_device(self, device, stream, d_q, n, elink_ids, joint_ids, rot_type, base_type, with_jacobian,
                         precision, d_P, d_J, ld_cfg=None, row0=0):
         """Raw device pointers (ints) through tfk_solve_fk_device; asynchronous on `stream`."""
@@ -257,7 +286,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel"}.get(k, "none")
         return d
 
 

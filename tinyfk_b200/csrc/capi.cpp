@@ -230,6 +230,49 @@ int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const void *d_q,
   });
 }
 
+static PairSpec make_pair_spec(const tfk_model *m, const int *l1, const int *l2, int n_check, const int *joint_ids, int n_joint,
+                               int base_type, int with_grads, int precision) {
+  if (n_check < 0 || (n_check > 0 && (!l1 || !l2))) throw std::invalid_argument("bad link pair arrays");
+  if (n_joint < 0 || (n_joint > 0 && !joint_ids)) throw std::invalid_argument("bad joint id array");
+  ids_of(l1, n_check, m->engine.model.n_links(), "link");
+  ids_of(l2, n_check, m->engine.model.n_links(), "link");
+  ids_of(joint_ids, n_joint, m->engine.model.n_joints(), "joint");
+  if (base_type < 0 || base_type > 2) throw std::invalid_argument("base_type must be 0 (FIXED), 1 (PLANER) or 2 (FLOATING)");
+  PairSpec ps;
+  ps.link_ids1 = l1;
+  ps.link_ids2 = l2;
+  ps.n_check = n_check;
+  ps.joint_ids = joint_ids;
+  ps.n_joint = n_joint;
+  ps.base_type = base_type;
+  ps.with_grads = with_grads ? 1 : 0;
+  ps.precision = precision;
+  return ps;
+}
+
+int tfk_inter_link_sqdists_host(tfk_model *m, const void *q, int64_t n, const int *link_ids1, const int *link_ids2,
+                                int n_check, const int *joint_ids, int n_joint, int base_type, int with_grads,
+                                int precision, void *sqdists, void *grads) {
+  return guarded([&] {
+    need(m, "model");
+    PairSpec ps = make_pair_spec(m, link_ids1, link_ids2, n_check, joint_ids, n_joint, base_type, with_grads, precision);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.sqdists_host(q, n, ps, sqdists, grads);
+  });
+}
+
+int tfk_inter_link_sqdists_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                  const int *link_ids1, const int *link_ids2, int n_check, const int *joint_ids,
+                                  int n_joint, int base_type, int with_grads, int precision, void *d_sqdists,
+                                  void *d_grads, int64_t ld_cfg, int64_t row0) {
+  return guarded([&] {
+    need(m, "model");
+    PairSpec ps = make_pair_spec(m, link_ids1, link_ids2, n_check, joint_ids, n_joint, base_type, with_grads, precision);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.sqdists_device(device, static_cast<cudaStream_t>(stream), d_q, n, ps, d_sqdists, d_grads, ld_cfg, row0);
+  });
+}
+
 int tfk_device_count(int *count) {
   return guarded([&] {
     need(count, "count");

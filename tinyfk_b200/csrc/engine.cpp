@@ -103,6 +103,11 @@ void Engine::release_device_memory() {
     }
   }
   pipes_.clear();
+  for (auto &kv : pair_bufs_) {
+    cudaSetDevice(kv.first.first);
+    cudaFree(kv.second.d);
+  }
+  pair_bufs_.clear();
   cudaSetDevice(prev);
 }
 
@@ -190,19 +195,24 @@ Engine::Workspace &Engine::workspace(int device, cudaStream_t stream, size_t byt
 }
 
 void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n,
-                    void *d_P, void *d_J, int64_t ld_cfg, int64_t row0) {
+                    void *d_P, void *d_J, int64_t ld_cfg, int64_t row0, const int *d_pairs, int n_pairs) {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (n <= 0 || h->n_out == 0) return;
+  const bool sqdist = d_pairs != nullptr;
   if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
   const int rb = (int)real_size(precision);
   // per-output tables of the two-phase kernel: [lrec_of_out | masks], contiguous inside the blob
-  const int table_bytes = h->n_out == 1 ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
+  const int table_bytes = (h->n_out == 1 && !sqdist) ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
   const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
   int variant, rec_reals;
   SmemLayout L;
-  if (h->n_out == 1) {
+  if (sqdist) {
+    rec_reals = h->rec_size;
+    L = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, 0, rb);
+    variant = KV_SQDIST;
+  } else if (h->n_out == 1) {
     rec_reals = h->fz_size;
     L = smem_layout(plan_bytes, h->n_in, rec_reals, rb);
     variant = KV_FUSED_SMEM;
@@ -249,6 +259,8 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.ld_cfg = ld_cfg;
   a.P = d_P;
   a.J = d_J;
+  a.pairs = d_pairs;
+  a.n_pairs = n_pairs;
   ck(precision == PREC_F32 ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
                            : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
      "kernel launch");
@@ -294,6 +306,115 @@ static void grow(void **buf, size_t *cap, size_t need, cudaStream_t st) {
   ck(cudaMalloc(buf, need), "cudaMalloc(staging)");
   *cap = need;
 }
+
+// ---- inter-link squared distances (reference src/wrapper.cpp:189-237) ------------------------------------
+// The plan is built over the distinct links of the pairs (RotationType IGNORE); o1/o2 index into it.
+Engine::PlanEntry &Engine::plan_for_pairs(const PairSpec &ps, std::vector<int> &o12) {
+  if (ps.n_check < 0 || ps.n_joint < 0) throw std::invalid_argument("negative id count");
+  std::vector<int> links;
+  o12.assign((size_t)2 * ps.n_check, 0);
+  for (int side = 0; side < 2; ++side)
+    for (int j = 0; j < ps.n_check; ++j) {
+      const int id = side == 0 ? ps.link_ids1[j] : ps.link_ids2[j];
+      size_t k = 0;
+      while (k < links.size() && links[k] != id) ++k;
+      if (k == links.size()) links.push_back(id);
+      o12[(size_t)side * ps.n_check + j] = (int)k;
+    }
+  SolveSpec s;
+  s.elink_ids = links.data();
+  s.n_link = (int)links.size();
+  s.joint_ids = ps.joint_ids;
+  s.n_joint = ps.n_joint;
+  s.rot_type = ROT_IGNORE;
+  s.base_type = ps.base_type;
+  s.with_jacobian = ps.with_grads;
+  s.precision = ps.precision;
+  return plan_for(s);
+}
+
+void Engine::sqdists_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const PairSpec &ps, void *d_sq,
+                            void *d_G, int64_t ld_cfg, int64_t row0) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (row0 < 0 || row0 + n > ld_cfg) throw std::invalid_argument("rows [row0, row0+n) exceed ld_cfg");
+  std::vector<int> o12;
+  PlanEntry &e = plan_for_pairs(ps, o12);
+  if (n == 0 || ps.n_check == 0) return;
+  if (!d_q && reinterpret_cast<const PlanHeader *>(e.blob.data())->n_in > 0) throw std::invalid_argument("q is null");
+  if (!d_sq) throw std::invalid_argument("sqdists is null");
+  if (ps.with_grads && !d_G) throw std::invalid_argument("grads is null but with_grads is set");
+  DeviceGuard g(device);
+  // the pair table is tiny and changes per call: staged through a per-(device, stream) buffer
+  PairBuf &pb = pair_bufs_[std::make_pair(device, stream)];
+  const size_t need = o12.size() * sizeof(int);
+  if (pb.bytes < need) {
+    if (pb.d) {
+      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(pairs)");
+      cudaFree(pb.d);
+      pb.d = nullptr;
+      pb.bytes = 0;
+    }
+    ck(cudaMalloc(reinterpret_cast<void **>(&pb.d), need), "cudaMalloc(pairs)");
+    pb.bytes = need;
+  }
+  if (pb.host != o12) { // unchanged table: nothing to copy
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(pairs)"); // earlier launches still read the old table
+    ck(cudaMemcpyAsync(pb.d, o12.data(), need, cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(pairs)");
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(pairs)"); // o12 is a pageable temporary
+    pb.host = o12;
+  }
+  launch(device, stream, e, ps.precision, d_q, n, d_sq, ps.with_grads ? d_G : nullptr, ld_cfg, row0, pb.d, ps.n_check);
+}
+
+// Host buffers in, host buffers out, current device.  Outputs are small next to the FK arrays
+// (n*n_check*(1+n_dof) reals), so the slice is processed in plain chunks on one stream.
+void Engine::sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq, void *G) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  std::vector<int> o12;
+  PlanEntry &e = plan_for_pairs(ps, o12);
+  const PlanHeader h = *reinterpret_cast<const PlanHeader *>(e.blob.data());
+  if (n == 0 || ps.n_check == 0) return;
+  if (!q && h.n_in > 0) throw std::invalid_argument("q is null");
+  if (!sq) throw std::invalid_argument("sqdists is null");
+  if (ps.with_grads && !G) throw std::invalid_argument("grads is null but with_grads is set");
+  int cur = 0;
+  ck(cudaGetDevice(&cur), "cudaGetDevice (is a CUDA device present? there is no CPU fallback)");
+  HostPipe &pp = pipe(cur);
+  cudaStream_t st = pp.stream[0];
+  const size_t sz = real_size(ps.precision);
+  const size_t in_row = (size_t)h.n_in * sz, row_out = (size_t)ps.n_check * sz;
+  const int64_t chunk = std::max<int64_t>(8192, (int64_t)((size_t(64) << 20) / std::max<size_t>(row_out * (1 + h.n_out_cols), 1)));
+  const int64_t capn = std::min<int64_t>(chunk, n);
+  grow(&pp.dq[0], &pp.cap_q[0], std::max<size_t>((size_t)capn * in_row, 16), st);
+  grow(&pp.dP[0], &pp.cap_P[0], (size_t)capn * row_out, st);
+  if (ps.with_grads) grow(&pp.dJ[0], &pp.cap_J[0], (size_t)capn * row_out * h.n_out_cols, st);
+  const char *qb = static_cast<const char *>(q);
+  for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+    const int64_t nc = std::min<int64_t>(chunk, n - r0);
+    if (in_row) ck(cudaMemcpyAsync(pp.dq[0], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(q)");
+    sqdists_device(cur, st, pp.dq[0], nc, ps, pp.dP[0], ps.with_grads ? pp.dJ[0] : nullptr, nc, 0);
+    ck(cudaMemcpyAsync(static_cast<char *>(sq) + (size_t)r0 * row_out, pp.dP[0], (size_t)nc * row_out, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(sq)");
+    if (ps.with_grads)
+      for (int c = 0; c < h.n_out_cols; ++c)
+        ck(cudaMemcpyAsync(static_cast<char *>(G) + ((size_t)c * n + r0) * row_out, static_cast<char *>(pp.dJ[0]) + (size_t)c * nc * row_out,
+                           (size_t)nc * row_out, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(G)");
+    ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+  }
+  // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:205-209)
+  std::vector<size_t> ids(ps.joint_ids, ps.joint_ids + ps.n_joint);
+  std::vector<double> last((size_t)h.n_in);
+  for (int c = 0; c < h.n_in; ++c)
+    last[c] = ps.precision == PREC_F32 ? (double)reinterpret_cast<const float *>(qb)[(size_t)(n - 1) * h.n_in + c]
+                                       : reinterpret_cast<const double *>(qb)[(size_t)(n - 1) * h.n_in + c];
+  if (ps.n_joint > 0) model.set_joint_angles(ids, std::vector<double>(last.begin(), last.begin() + ps.n_joint));
+  if (h.base_type == BASE_PLANER) {
+    const double b[6] = {last[ps.n_joint], last[ps.n_joint + 1], 0.0, 0.0, 0.0, last[ps.n_joint + 2]};
+    model.set_base_pose_xyzrpy(b);
+  } else if (h.base_type == BASE_FLOATING) {
+    model.set_base_pose_xyzrpy(&last[ps.n_joint]);
+  }
+}
+
 
 // Host buffers in, host buffers out.  The batch is cut into contiguous per-device slices (no
 // collective: configurations are independent) and each slice into chunks that ping-pong between two

@@ -35,6 +35,14 @@ struct SolveSpec {
   int rot_type, base_type, with_jacobian, precision;
 };
 
+struct PairSpec { // compute_inter_link_squared_dists (reference src/wrapper.cpp:189-237)
+  const int *link_ids1, *link_ids2;
+  int n_check;
+  const int *joint_ids;
+  int n_joint;
+  int base_type, with_grads, precision;
+};
+
 struct LaunchInfo {
   int grid, block, smem_bytes, blocks_per_sm, rec_reals, variant;
 };
@@ -50,6 +58,9 @@ public:
   void solve_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec, void *d_P,
                     void *d_J, int64_t ld_cfg, int64_t row0);
   void solve_host(const void *q, int64_t n, const SolveSpec &spec, const int *devices, int n_devices, void *P, void *J);
+  void sqdists_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const PairSpec &ps, void *d_sq,
+                      void *d_G, int64_t ld_cfg, int64_t row0);
+  void sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq, void *G);
   LaunchInfo last_launch;
 
 private:
@@ -76,7 +87,14 @@ private:
   HostPipe &pipe(int device);
   int sm_count(int device);
   void launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n, void *d_P,
-              void *d_J, int64_t ld_cfg, int64_t row0);
+              void *d_J, int64_t ld_cfg, int64_t row0, const int *d_pairs = nullptr, int n_pairs = 0);
+  PlanEntry &plan_for_pairs(const PairSpec &ps, std::vector<int> &o12);
+  struct PairBuf {
+    int *d = nullptr;
+    size_t bytes = 0;
+    std::vector<int> host;
+  };
+  std::map<std::pair<int, cudaStream_t>, PairBuf> pair_bufs_;
   void release_device_memory();
 
   std::vector<std::unique_ptr<PlanEntry>> plans_;

@@ -72,7 +72,10 @@ template <class T> struct DirectSink {
 // instead of the reference's forward difference (FP32 mode: eps = 1e-7 is below one FP32 ulp).
 // ROT: the call's RotationType (0 IGNORE, 1 RPY, 2 XYZW) as a compile-time constant -- it fixes the
 // pose dimension, so the kernels are instantiated once per value instead of branching per column.
-template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
+// STRIDE: distance in reals between consecutive record elements of one configuration ([k][STRIDE] layout:
+// TFK_TILE in the kernels, 1 in the CPU harness) -- compile-time, so record addresses are immediates; the
+// `stride` arguments below must equal it.
+template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   enum { D = ROT == 0 ? 3 : (ROT == 1 ? 6 : 7), LREC = ROT == 0 ? 3 : 7 };
   typedef typename M::real T;
   typedef Ops<M> O;
@@ -81,50 +84,50 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
   typedef PoseT<T> P;
 
   static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
-    rec[(at + 0) * stride] = a.p.x;
-    rec[(at + 1) * stride] = a.p.y;
-    rec[(at + 2) * stride] = a.p.z;
-    rec[(at + 3) * stride] = a.q.x;
-    rec[(at + 4) * stride] = a.q.y;
-    rec[(at + 5) * stride] = a.q.z;
-    rec[(at + 6) * stride] = a.q.w;
+    rec[(at + 0) * STRIDE] = a.p.x;
+    rec[(at + 1) * STRIDE] = a.p.y;
+    rec[(at + 2) * STRIDE] = a.p.z;
+    rec[(at + 3) * STRIDE] = a.q.x;
+    rec[(at + 4) * STRIDE] = a.q.y;
+    rec[(at + 5) * STRIDE] = a.q.z;
+    rec[(at + 6) * STRIDE] = a.q.w;
   }
   static TFK_FN P get_pose(const T *rec, int stride, int at) {
     P a;
-    a.p.x = rec[(at + 0) * stride];
-    a.p.y = rec[(at + 1) * stride];
-    a.p.z = rec[(at + 2) * stride];
-    a.q.x = rec[(at + 3) * stride];
-    a.q.y = rec[(at + 4) * stride];
-    a.q.z = rec[(at + 5) * stride];
-    a.q.w = rec[(at + 6) * stride];
+    a.p.x = rec[(at + 0) * STRIDE];
+    a.p.y = rec[(at + 1) * STRIDE];
+    a.p.z = rec[(at + 2) * STRIDE];
+    a.q.x = rec[(at + 3) * STRIDE];
+    a.q.y = rec[(at + 4) * STRIDE];
+    a.q.z = rec[(at + 5) * STRIDE];
+    a.q.w = rec[(at + 6) * STRIDE];
     return a;
   }
   static TFK_FN V get_vec(const T *rec, int stride, int at) {
     V a;
-    a.x = rec[(at + 0) * stride];
-    a.y = rec[(at + 1) * stride];
-    a.z = rec[(at + 2) * stride];
+    a.x = rec[(at + 0) * STRIDE];
+    a.y = rec[(at + 1) * STRIDE];
+    a.z = rec[(at + 2) * STRIDE];
     return a;
   }
   static TFK_FN void put_vec(T *rec, int stride, int at, const V &a) {
-    rec[(at + 0) * stride] = a.x;
-    rec[(at + 1) * stride] = a.y;
-    rec[(at + 2) * stride] = a.z;
+    rec[(at + 0) * STRIDE] = a.x;
+    rec[(at + 1) * STRIDE] = a.y;
+    rec[(at + 2) * STRIDE] = a.z;
   }
   static TFK_FN Q get_quat(const T *rec, int stride, int at) {
     Q a;
-    a.x = rec[(at + 0) * stride];
-    a.y = rec[(at + 1) * stride];
-    a.z = rec[(at + 2) * stride];
-    a.w = rec[(at + 3) * stride];
+    a.x = rec[(at + 0) * STRIDE];
+    a.y = rec[(at + 1) * STRIDE];
+    a.z = rec[(at + 2) * STRIDE];
+    a.w = rec[(at + 3) * STRIDE];
     return a;
   }
   static TFK_FN void put_quat(T *rec, int stride, int at, const Q &a) {
-    rec[(at + 0) * stride] = a.x;
-    rec[(at + 1) * stride] = a.y;
-    rec[(at + 2) * stride] = a.z;
-    rec[(at + 3) * stride] = a.w;
+    rec[(at + 0) * STRIDE] = a.x;
+    rec[(at + 1) * STRIDE] = a.y;
+    rec[(at + 2) * STRIDE] = a.z;
+    rec[(at + 3) * STRIDE] = a.w;
   }
 
   // ---------------------------------------------------------------------------------------------
@@ -546,6 +549,103 @@ template <class M, bool ANALYTIC_BASE, int ROT> struct FkCore {
     bs.stride = stride;
     bs.at = h.off_base;
     emit_link(pv, e, o, rec, stride, h.off_arec, h.off_prec, bs, out);
+  }
+
+  // ---------------------------------------------------------------------------------------------
+  // compute_inter_link_squared_dists (src/wrapper.cpp:189-237) for one (configuration, link pair), on the
+  // records of phase A (plan built for the union of the pairs' links, RotationType IGNORE):
+  //   sqdist = |p1 - p2|^2,   grad_c = 2 * (J1[:,c] - J2[:,c]) . (p1 - p2)
+  // J1/J2 are the position Jacobians get_jacobian(.., IGNORE, with_base) would return -- their columns
+  // are produced one at a time (same expressions as emit_link) and never stored.  o1, o2: indices into
+  // the plan's elink list.  G points at this pair's row of column 0, columns are ldG apart.
+  static TFK_FN V pos_joint_col(const PlanView &pv, const T *rec, const V &ep, int o, int c) {
+    const PlanHeader &h = *pv.h;
+    V v;
+    v.x = v.y = v.z = T(0);
+    const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
+    if (!((mask[c >> 5] >> (c & 31)) & 1u)) return v;
+    const PlanCol &pc = pv.cols[c];
+    const V aw = get_vec(rec, STRIDE, h.off_arec + 3 * pc.arec);
+    if (pc.prismatic) return aw;
+    const V cp = get_vec(rec, STRIDE, h.off_prec + 3 * pc.prec);
+    V d;
+    d.x = ep.x - cp.x;
+    d.y = ep.y - cp.y;
+    d.z = ep.z - cp.z;
+    return O::cross(aw, d);
+  }
+  static TFK_FN T grad_entry(const V &j1, const V &j2, const V &d) {
+    const T a0 = j1.x - j2.x, a1 = j1.y - j2.y, a2 = j1.z - j2.z;
+    return T(2) * ((a0 * d.x + a1 * d.y) + a2 * d.z);
+  }
+  static TFK_FN void pair_sqdist(const PlanView &pv, const T *rec, int o1, int o2, bool valid, T *sq, T *G, long long ldG) {
+    const PlanHeader &h = *pv.h;
+    const V p1 = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o1] * LREC);
+    const V p2 = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o2] * LREC);
+    V d;
+    d.x = p1.x - p2.x;
+    d.y = p1.y - p2.y;
+    d.z = p1.z - p2.z;
+    if (valid) *sq = (d.x * d.x + d.y * d.y) + d.z * d.z;
+    if (!h.with_jacobian) return;
+    TFK_NOUNROLL
+    for (int c = 0; c < h.n_cols; ++c) {
+      const T g = grad_entry(pos_joint_col(pv, rec, p1, o1, c), pos_joint_col(pv, rec, p2, o2, c), d);
+      if (valid) G[c * ldG] = g;
+    }
+    if (h.base_type == 0) return;
+    // base translation columns are the identity for both links (src/kinematics.cpp:194-196): difference 0
+    const int n_trans = (h.base_type == 1) ? 2 : 3;
+    for (int k = 0; k < n_trans; ++k) {
+      V e1;
+      e1.x = (k == 0) ? T(1) : T(0);
+      e1.y = (k == 1) ? T(1) : T(0);
+      e1.z = (k == 2) ? T(1) : T(0);
+      const T g = grad_entry(e1, e1, d);
+      if (valid) G[(h.n_cols + k) * ldG] = g;
+    }
+    BaseFromRec bs;
+    bs.rec = rec;
+    bs.stride = STRIDE;
+    bs.at = h.off_base;
+    const V base_p = bs.base_p();
+    const int k0 = (h.base_type == 1) ? 2 : 0;
+    if (ANALYTIC_BASE) {
+      V d1, d2;
+      d1.x = p1.x - base_p.x, d1.y = p1.y - base_p.y, d1.z = p1.z - base_p.z;
+      d2.x = p2.x - base_p.x, d2.y = p2.y - base_p.y, d2.z = p2.z - base_p.z;
+      for (int k = k0; k < 3; ++k) {
+        const V w = bs.w(k);
+        const T g = grad_entry(O::cross(w, d1), O::cross(w, d2), d);
+        if (valid) G[(h.n_cols + n_trans + (k - k0)) * ldG] = g;
+      }
+      return;
+    }
+    // forward finite difference columns, src/kinematics.cpp:182-232 (position rows only)
+    const typename M::Den deps = M::den_(T(1e-7));
+    V be1, be2;
+    {
+      const P binv = bs.binv();
+      const Q bi = O::qget_inverse(binv.q);
+      const V r1 = O::qt_xyz(binv.q, O::vq_full(p1, bi)), r2 = O::qt_xyz(binv.q, O::vq_full(p2, bi));
+      be1.x = r1.x + binv.p.x, be1.y = r1.y + binv.p.y, be1.z = r1.z + binv.p.z;
+      be2.x = r2.x + binv.p.x, be2.y = r2.y + binv.p.y, be2.z = r2.z + binv.p.z;
+    }
+    TFK_NOUNROLL
+    for (int k = k0; k < 3; ++k) {
+      const Q bq = bs.bk(k);
+      const Q bi = O::qget_inverse(bq);
+      const V r1 = O::qt_xyz(bq, O::vq_full(be1, bi)), r2 = O::qt_xyz(bq, O::vq_full(be2, bi));
+      T n1[3] = {(r1.x + base_p.x) - p1.x, (r1.y + base_p.y) - p1.y, (r1.z + base_p.z) - p1.z};
+      T n2[3] = {(r2.x + base_p.x) - p2.x, (r2.y + base_p.y) - p2.y, (r2.z + base_p.z) - p2.z};
+      M::divn_(n1, deps);
+      M::divn_(n2, deps);
+      V j1, j2;
+      j1.x = n1[0], j1.y = n1[1], j1.z = n1[2];
+      j2.x = n2[0], j2.y = n2[1], j2.z = n2[2];
+      const T g = grad_entry(j1, j2, d);
+      if (valid) G[(h.n_cols + n_trans + (k - k0)) * ldG] = g;
+    }
   }
 
   // ---------------------------------------------------------------------------------------------

@@ -28,6 +28,8 @@
 
 #include <cuda_runtime.h>
 
+#include <type_traits>
+
 #include "fk_core.h"
 #include "fk_launch.h"
 
@@ -214,6 +216,67 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   }
 }
 
+// compute_inter_link_squared_dists (src/wrapper.cpp:189-237): phase A as in the two-phase kernel (plan over the
+// union of the pairs' links, positions only), then one thread per (configuration, pair): consecutive threads
+// write consecutive entries of sqdists and of every gradient column -- coalesced without staging.
+template <class Core>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_sqdist_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+  typedef typename Core::T T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
+  const PlanHeader &h = pp.h;
+  const int tab = (a.table_bytes + 15) & ~15;
+  int *pairs = reinterpret_cast<int *>(smem + tab);
+  for (int i = threadIdx.x; i < 2 * a.n_pairs; i += TFK_TILE) pairs[i] = a.pairs[i];
+  __syncthreads();
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
+  pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
+  const SmemLayout L = smem_layout(tab + ((2 * a.n_pairs * 4 + 15) & ~15), h.n_in, 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  const T *q = static_cast<const T *>(a.q);
+  T *sq = static_cast<T *>(a.P);
+  T *G = static_cast<T *>(a.J);
+  const long long ldG = a.ld_cfg * a.n_pairs;
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
+    __syncthreads();
+    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+    __syncthreads();
+    const int items = nv * a.n_pairs;
+    const long long hbase = (a.row0 + i0) * a.n_pairs;
+    for (int it = threadIdx.x; it < items; it += TFK_TILE) {
+      const int il = it / a.n_pairs;
+      const int j = it - il * a.n_pairs;
+      Core::pair_sqdist(pv, rec + il, pairs[j], pairs[a.n_pairs + j], true, sq + hbase + it, G ? G + hbase + it : nullptr, ldG);
+    }
+    __syncthreads();
+  }
+}
+
+// the pair kernel exists for RotationType IGNORE only (positions); other instantiations never reach it
+template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
+  fk_sqdist_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+}
+template <class Core> typename std::enable_if<Core::D != 3, void>::type launch_sqdist(const KernelArgs &, const PlanParams &, int, int, cudaStream_t) {}
+template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type occupancy_sqdist(int smem_bytes, int *blocks_per_sm) {
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_sqdist_kernel<Core>, TFK_TILE, smem_bytes);
+}
+template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_sqdist(int, int *blocks_per_sm) {
+  *blocks_per_sm = 0;
+  return cudaSuccess;
+}
+
 template <class Core>
 cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
   if (variant == KV_FUSED_SMEM5)
@@ -222,12 +285,15 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
     fk_fused_kernel<Core, true, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_FUSED_GMEM)
     fk_fused_kernel<Core, false, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+  else if (variant == KV_SQDIST)
+    launch_sqdist<Core>(a, pp, grid, smem_bytes, stream);
   else
     fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
 }
 
 template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
+  if (variant == KV_SQDIST) return occupancy_sqdist<Core>(smem_bytes, blocks_per_sm);
   const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>
                    : variant == KV_FUSED_SMEM ? (const void *)fk_fused_kernel<Core, true, 4>
                    : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false, 4>
@@ -241,14 +307,14 @@ template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes,
 // one instantiation per RotationType (the pose dimension is a compile-time constant of the kernels)
 template <class M, bool ANALYTIC_BASE>
 cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
-  if (pp.h.rot_type == 0) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 0>>(a, pp, variant, grid, smem_bytes, stream);
-  if (pp.h.rot_type == 1) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 1>>(a, pp, variant, grid, smem_bytes, stream);
-  return launch_fk_core<FkCore<M, ANALYTIC_BASE, 2>>(a, pp, variant, grid, smem_bytes, stream);
+  if (pp.h.rot_type == 0) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 0, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
+  if (pp.h.rot_type == 1) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 1, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
+  return launch_fk_core<FkCore<M, ANALYTIC_BASE, 2, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
 }
 template <class M, bool ANALYTIC_BASE> cudaError_t occupancy_fk(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
-  if (rot_type == 0) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 0>>(variant, smem_bytes, blocks_per_sm);
-  if (rot_type == 1) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 1>>(variant, smem_bytes, blocks_per_sm);
-  return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 2>>(variant, smem_bytes, blocks_per_sm);
+  if (rot_type == 0) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 0, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
+  if (rot_type == 1) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 1, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
+  return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 2, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
 }
 
 } // namespace tfk

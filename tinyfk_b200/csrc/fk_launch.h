@@ -19,6 +19,7 @@ enum KernelVariant {
   KV_FUSED_SMEM = 0, // one requested link, joint records in shared memory
   KV_FUSED_GMEM = 1, // one requested link, records too large for shared memory: block-private global scratch
   KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
+  KV_SQDIST = 4,      // inter-link squared distances: phase A -> records -> one thread per (configuration, pair)
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };
@@ -32,6 +33,9 @@ struct KernelArgs {
   long long ld_cfg;  // configurations the destination arrays are dimensioned for (ldP = ld_cfg*n_out)
   void *P, *J;       // column-major outputs (J may be null when the plan has no Jacobian)
   void *scratch;     // grid * TFK_TILE * (rec_size | fz_size) reals (unused by KV_FUSED_SMEM)
+  // KV_SQDIST only: P = sqdists [ld_cfg*n_pairs], J = grads column-major (ld_cfg*n_pairs) x n_dof (or null)
+  const int *pairs;  // device: o1[n_pairs] then o2[n_pairs], indices into the plan's elink list
+  int n_pairs;
 };
 
 // Dynamic shared memory of a block: [per-output tables | q tile (doubles as the warps' staging strips) | records]

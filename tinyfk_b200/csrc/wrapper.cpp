@@ -150,6 +150,28 @@ public:
                        with_jacobian, TFK_F64_STRICT, {}, true);
   }
 
+  // compute_inter_link_squared_dists (src/wrapper.cpp:189-237), batched: returns (sqdists [n*n_check],
+  // grads (n*n_check, n_dof) F-ordered; a 1x1 zero matrix when !with_grads, as the reference)
+  py::tuple sqdists_batch(py::array qs_in, const std::vector<size_t> &link_ids1, const std::vector<size_t> &link_ids2,
+                          const std::vector<size_t> &joint_ids, int base_type, bool with_grads, int precision) {
+    if (base_type < 0 || base_type > 2) throw std::invalid_argument("bad base_type");
+    if (link_ids1.size() != link_ids2.size()) throw std::invalid_argument("link_ids1 and link_ids2 differ in length");
+    const size_t n_in = joint_ids.size() + (base_type == 1 ? 3 : (base_type == 2 ? 6 : 0));
+    std::vector<int> l1 = to_int(link_ids1), l2 = to_int(link_ids2), j = to_int(joint_ids);
+    if (precision == TFK_F32)
+      return run_sq<float>(py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(qs_in), l1, l2, j, base_type,
+                           with_grads, precision, n_in);
+    return run_sq<double>(py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(qs_in), l1, l2, j, base_type,
+                          with_grads, precision, n_in);
+  }
+  // the reference's 7-argument entry: with_base means the 6-D floating base; use_cache has no meaning here
+  py::tuple compute_inter_link_squared_dists(py::array qs, const std::vector<size_t> &link_ids1,
+                                             const std::vector<size_t> &link_ids2, const std::vector<size_t> &joint_ids,
+                                             bool with_base, bool with_grads, bool /*use_cache*/) {
+    return sqdists_batch(qs, link_ids1, link_ids2, joint_ids, with_base ? TFK_BASE_FLOATING : TFK_BASE_FIXED, with_grads,
+                         TFK_F64_STRICT);
+  }
+
   int64_t kernel_launches() const { return tfk_kernel_launch_count(); }
 
 private:
@@ -186,6 +208,31 @@ private:
       return py::make_tuple(P, zeros);
     }
     return py::make_tuple(P, J);
+  }
+
+  template <class T>
+  py::tuple run_sq(py::array_t<T, py::array::c_style | py::array::forcecast> qs, const std::vector<int> &l1,
+                   const std::vector<int> &l2, const std::vector<int> &j, int base_type, bool with_grads, int precision,
+                   size_t n_in) {
+    if (!qs) throw std::invalid_argument("qs must be convertible to a 2-D float array");
+    if (qs.ndim() != 2) throw std::invalid_argument("qs must be 2-D (n_configs, n_dof)");
+    if ((size_t)qs.shape(1) != n_in)
+      throw std::invalid_argument("dof mismatch: expected " + std::to_string(n_in) + " columns, got " +
+                                  std::to_string(qs.shape(1)));
+    const size_t n = (size_t)qs.shape(0), rows = n * l1.size();
+    py::array_t<T> sq((py::ssize_t)rows);
+    py::array_t<T, py::array::f_style> G(with_grads ? std::vector<py::ssize_t>{(py::ssize_t)rows, (py::ssize_t)n_in}
+                                                    : std::vector<py::ssize_t>{1, 1});
+    if (!with_grads) *G.mutable_data() = T(0);
+    int rc;
+    {
+      py::gil_scoped_release nogil;
+      rc = tfk_inter_link_sqdists_host(m_, qs.data(), (int64_t)n, l1.data(), l2.data(), (int)l1.size(), j.data(),
+                                       (int)j.size(), base_type, with_grads ? 1 : 0, precision, sq.mutable_data(),
+                                       with_grads ? G.mutable_data() : nullptr);
+    }
+    check(rc);
+    return py::make_tuple(sq, G);
   }
 
   tfk_model *m_;
@@ -228,7 +275,10 @@ PYBIND11_MODULE(_tinyfk, m) {
       .def("get_link_ids", &RobotModel::get_link_ids)
       .def("get_link_names", &RobotModel::get_link_names)
       .def("add_new_link", &RobotModel::add_new_link)
-      .def("compute_inter_link_squared_dists", [](RobotModel &, py::args, py::kwargs) { not_on_path("compute_inter_link_squared_dists"); })
+      .def("compute_inter_link_squared_dists", &RobotModel::compute_inter_link_squared_dists)
+      .def("compute_inter_link_squared_dists_batch", &RobotModel::sqdists_batch, py::arg("qs"), py::arg("link_ids1"),
+           py::arg("link_ids2"), py::arg("joint_ids"), py::arg("base_type"), py::arg("with_grads"),
+           py::arg("precision") = (int)TFK_F64_STRICT)
       .def("is_relevant", &RobotModel::is_relevant)
       .def("kernel_launches", &RobotModel::kernel_launches)
       .def("clear_cache", &RobotModel::clear_cache);

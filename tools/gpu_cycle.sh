@@ -10,3 +10,4 @@ for l in open("gpurun_out/b.log"):
         d=json.loads(l); print(d["config"]["workload"][:40], d["dtype"], "%.3e"%d["value"], "%.4f ms"%d["ms_per_step"], "frac %.3f"%d["roofline"]["frac"], d["config"]["launch"])
     else: print(l[:300])
 PY
+python tools/time_sqdists.py > gpurun_out/sq.log 2>&1; tail -40 gpurun_out/sq.log
