@@ -135,6 +135,28 @@ TFK_API int tfk_inter_link_sqdists_device(tfk_model *m, int device, void *stream
                                           const int *joint_ids, int n_joint, int base_type, int with_grads,
                                           int precision, void *d_sqdists, void *d_grads, int64_t ld_cfg, int64_t row0);
 
+/* ---- centre of mass ---------------------------------------------- */
+/* KinematicsModelPyWrapper::solve_com_forward_kinematics (src/wrapper.cpp:126-179) over get_com / get_com_jacobian
+ * (src/kinematics.cpp:237-270) + the facade glue of KinematicModel.solve_com_fk (python/tinyfk/__init__.py:160-195),
+ * batched on the GPU.  For every configuration i:
+ *     com[i*3 + k]                           mass-weighted mean of the "<link>_com" link positions, in link-id order;
+ *                                            with action links: (com + sum_j (forces[j]/total_mass) * p_j) / (1 + sum_j ...)
+ *     J[c * (3*N) + 3*i + k]                 its Jacobian, column-major (3N) x n_dof, n_dof = n_joint (+6 with a moving base)
+ * q rows are [joints | base] as for tfk_solve_fk_host; a PLANER row (x, y, yaw) is padded to (x, y, 0, 0, 0, yaw) and
+ * J KEEPS ALL SIX base columns (the reference's facade does not pick columns on this entry).  J may be NULL when
+ * with_jacobian == 0.  Every configuration is evaluated from its own row (the reference skips clear_cache() on this
+ * entry with a FIXED base, src/wrapper.cpp:137-141, and then repeats the first row's result: not reproduced).
+ * Runs on the current device; the model's stored state follows the last configuration. */
+TFK_API int tfk_solve_com_fk_host(tfk_model *m, const void *q, int64_t n, const int *joint_ids, int n_joint,
+                                  const int *action_link_ids, const double *forces, int n_action, int base_type,
+                                  int with_jacobian, int precision, void *com, void *J);
+/* same on device-resident buffers (see tfk_solve_fk_device for stream / ld_cfg / row0); base_type FIXED or FLOATING;
+ *     d_com[k * ld_cfg + row]   (3, ld_cfg) component-major,   d_J[c * (3*ld_cfg) + 3*row + k] */
+TFK_API int tfk_solve_com_fk_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                    const int *joint_ids, int n_joint, const int *action_link_ids,
+                                    const double *forces, int n_action, int base_type, int with_jacobian,
+                                    int precision, void *d_com, void *d_J, int64_t ld_cfg, int64_t row0);
+
 /* ---- helpers ---------------------------------------------------------------------------------- */
 TFK_API int tfk_device_count(int *count);
 /* pinned host memory for the host path (pooled; tfk_host_free returns the block to the pool) */

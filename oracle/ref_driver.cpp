@@ -332,6 +332,86 @@ int tfkref_sqdists(void *p, const double *qs, long n_wp, const int *link_ids1, c
   }
 }
 
+/*
+ * solve_com_fk as the Python user sees it (python/tinyfk/__init__.py:160-195 + src/wrapper.cpp:126-179).  The
+ * reference's own get_com / get_com_jacobian / get_link_pose / get_jacobian do the work; this function restates the
+ * loop of wrapper.cpp:136-178, whose Eigen expressions are element-wise only (block += force * jac, block /= s: no
+ * reductions, so no summation order to pin).
+ * ONE DELIBERATE DIFFERENCE: wrapper.cpp:137-141 calls _set_joint_angles (no cache clear) and only set_base_pose
+ * clears the transform cache, so with a FIXED base the reference answers every row from the cache left by the first
+ * one.  `clear_each` != 0 clears the cache per row (what a caller gets from one call per configuration after
+ * clear_cache()); `clear_each` == 0 reproduces the reference literally.
+ *   q rows [joints | x y yaw (PLANER, padded as __init__.py:98-103) | xyzrpy (FLOATING)]
+ *   com (n_wp, 3) row-major;  J column-major (3*n_wp) x (n_joint + 0|6), may be NULL
+ */
+int tfkref_com(void *p, const double *qs, long n_wp, const int *joint_ids, int n_joint, const int *action_link_ids,
+               const double *forces, int n_action, int base_type, int with_jacobian, int clear_each, double *com,
+               double *J) {
+  try {
+    KinematicModel *kin = static_cast<Handle *>(p)->kin;
+    const bool with_base = base_type != 0;
+    const int n_in = n_joint + (base_type == 1 ? 3 : (base_type == 2 ? 6 : 0));
+    const int n_dof = n_joint + (with_base ? 6 : 0);
+    std::vector<size_t> jids(joint_ids, joint_ids + n_joint);
+    const size_t ldJ = (size_t)3 * n_wp;
+    std::vector<double> q(n_joint), b(6);
+    for (long i = 0; i < n_wp; ++i) {
+      const double *row = qs + (size_t)i * n_in;
+      for (int k = 0; k < n_joint; ++k) q[k] = row[k];
+      kin->_set_joint_angles(jids, q); // wrapper.cpp:137
+      if (with_base) {                 // wrapper.cpp:138-141
+        if (base_type == 1) {
+          b[0] = row[n_joint];
+          b[1] = row[n_joint + 1];
+          b[2] = 0.0;
+          b[3] = 0.0;
+          b[4] = 0.0;
+          b[5] = row[n_joint + 2];
+        } else {
+          for (int k = 0; k < 6; ++k) b[k] = row[n_joint + k];
+        }
+        set_base_xyzrpy(kin, b.data());
+      }
+      if (clear_each) kin->clear_cache();
+      const urdf::Vector3 c0 = kin->get_com(); // wrapper.cpp:143
+      double c[3] = {c0.x, c0.y, c0.z};
+      Eigen::MatrixXd jblock = Eigen::MatrixXd::Zero(3, n_dof);
+      if (with_jacobian) jblock = kin->get_com_jacobian(jids, with_base); // wrapper.cpp:147-150
+      if (n_action > 0) {                                                  // wrapper.cpp:152-177
+        double vertical_force_sum = 1.0;
+        Transform pose;
+        for (int j = 0; j < n_action; ++j) {
+          const double force = forces[j] / kin->total_mass_;
+          vertical_force_sum += force;
+          kin->get_link_pose(action_link_ids[j], pose);
+          c[0] += force * pose.position.x;
+          c[1] += force * pose.position.y;
+          c[2] += force * pose.position.z;
+          if (with_jacobian) {
+            Eigen::MatrixXd jac = kin->get_jacobian(action_link_ids[j], jids, RotationType::IGNORE, with_base);
+            for (int cc = 0; cc < n_dof; ++cc)
+              for (int r = 0; r < 3; ++r) jblock(r, cc) += force * jac(r, cc);
+          }
+        }
+        c[0] /= vertical_force_sum;
+        c[1] /= vertical_force_sum;
+        c[2] /= vertical_force_sum;
+        if (with_jacobian)
+          for (int cc = 0; cc < n_dof; ++cc)
+            for (int r = 0; r < 3; ++r) jblock(r, cc) /= vertical_force_sum;
+      }
+      for (int k = 0; k < 3; ++k) com[(size_t)i * 3 + k] = c[k];
+      if (with_jacobian && J)
+        for (int cc = 0; cc < n_dof; ++cc)
+          for (int r = 0; r < 3; ++r) J[(size_t)cc * ldJ + (size_t)3 * i + r] = jblock(r, cc);
+    }
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
+
 /* which libm is this object bound to?  (tests check the strict build really is pinned) */
 double tfkref_probe_sin(double x) {
   volatile double v = x;

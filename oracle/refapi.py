@@ -97,6 +97,9 @@ def _load_ref(strict):
     lib.tfkref_sqdists.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
                                    ctypes.c_int, ctypes.c_int, _dp, _dp]
     lib.tfkref_sqdists.restype = ctypes.c_int
+    lib.tfkref_com.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int, ctypes.c_int,
+                               ctypes.c_int, ctypes.c_int, _dp, _dp]
+    lib.tfkref_com.restype = ctypes.c_int
     lib.tfkref_probe_sin.argtypes = [ctypes.c_double]
     lib.tfkref_probe_sin.restype = ctypes.c_double
     lib.tfkref_probe_atan2.argtypes = [ctypes.c_double, ctypes.c_double]
@@ -241,6 +244,26 @@ class RefModel:
         if rc:
             raise ValueError(self._lib.tfkref_last_error().decode())
         return sq, G
+
+    def solve_com_fk(self, qs, joint_ids, action_link_ids=(), forces=(), base_type=0, with_jacobian=False, clear_each=True):
+        """solve_com_fk (python/tinyfk/__init__.py:160-195): (com (n, 3), J (3n, n_joint + 0|6) F-order or None).
+        clear_each=False reproduces the reference's stale-cache behaviour with a FIXED base (ref_driver.cpp)."""
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        jids, al = _as_int_array(joint_ids), _as_int_array(action_link_ids)
+        f = np.ascontiguousarray(np.asarray(forces, dtype=np.float64).reshape(-1))
+        assert f.size == al.size
+        n_wp, n_in = qs.shape
+        assert n_in == jids.size + base_dof(base_type), (n_in, jids.size, base_type)
+        n_dof = jids.size + (6 if base_type else 0)
+        com = np.zeros((n_wp, 3))
+        J = np.zeros((3 * n_wp, n_dof), order="F") if with_jacobian else None
+        rc = self._lib.tfkref_com(self._h, qs.ctypes.data_as(_dp), n_wp, jids.ctypes.data_as(_ip), jids.size,
+                                  al.ctypes.data_as(_ip), f.ctypes.data_as(_dp), al.size, int(base_type),
+                                  int(bool(with_jacobian)), int(bool(clear_each)), com.ctypes.data_as(_dp),
+                                  J.ctypes.data_as(_dp) if with_jacobian else None)
+        if rc:
+            raise ValueError(self._lib.tfkref_last_error().decode())
+        return com, J
 
     def probe_sin(self, x):
         return self._lib.tfkref_probe_sin(float(x))

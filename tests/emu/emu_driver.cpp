@@ -80,6 +80,41 @@ static void run_pairs(const std::vector<unsigned char> &blob, const std::vector<
     for (size_t k = 0; k < (size_t)ld * h.n_out_cols; ++k) G[k] = (double)g[k];
 }
 
+// the centre-of-mass kernel's per-thread code (FkCore::phase_a + com_item, item loop of fk_com_kernel) on the CPU
+template <class Core, class T>
+static void run_com(const std::vector<unsigned char> &blob, const ComTables &ct, const double *qs, long n, double *com, double *J) {
+  PlanView pv = plan_view(blob.data());
+  const PlanHeader &h = *pv.h;
+  std::vector<T> rec((size_t)(h.rec_size > 0 ? h.rec_size : 1)), qrow((size_t)(h.n_in > 0 ? h.n_in : 1));
+  std::vector<T> w(ct.w.begin(), ct.w.end());
+  typename Core::ComArgs ca;
+  ca.w = w.data();
+  ca.n_com = ct.n_com;
+  ca.n_act = ct.n_act;
+  ca.mass_total = (T)ct.mass_total;
+  ca.vfs = (T)ct.vfs;
+  const int n_base = h.base_type == 0 ? 0 : 6;
+  const int n_items = 1 + (J ? h.n_cols + (n_base ? 3 : 0) : 0);
+  const size_t ldJ = (size_t)3 * n;
+  for (long i = 0; i < n; ++i) {
+    for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
+    Core::phase_a(pv, qrow.data(), rec.data(), 1);
+    for (int item = 0; item < n_items; ++item) {
+      const typename Core::V v = Core::com_item(pv, rec.data(), item, ca);
+      const double d[3] = {(double)v.x, (double)v.y, (double)v.z};
+      if (item == 0) {
+        for (int k = 0; k < 3; ++k) com[(size_t)i * 3 + k] = d[k];
+      } else {
+        const int col = (item <= h.n_cols) ? item - 1 : item + 2;
+        for (int k = 0; k < 3; ++k) J[(size_t)col * ldJ + 3 * i + k] = d[k];
+      }
+    }
+    if (J && n_base)
+      for (int k = 0; k < 3; ++k)
+        for (int r = 0; r < 3; ++r) J[(size_t)(h.n_cols + k) * ldJ + 3 * i + r] = (r == k) ? (double)(T)ct.diag : 0.0;
+  }
+}
+
 extern "C" {
 int emu_sqdists(void *m, const double *qs, long n, const int *l1, const int *l2, int n_check, const int *joints, int n_joint,
                 int base_type, int with_grads, int mode, double *sq, double *G) {
@@ -105,6 +140,31 @@ int emu_sqdists(void *m, const double *qs, long n, const int *l1, const int *l2,
       run_pairs<FkCore<MathNative32, true, 0, 1>, float>(blob, o12, n_check, qs, n, sq, with_grads ? G : nullptr);
     else
       run_pairs<FkCore<MathPortable, false, 0, 1>, double>(blob, o12, n_check, qs, n, sq, with_grads ? G : nullptr);
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
+// base_type 0 (FIXED) or 2 (FLOATING); com (n, 3) row-major, J column-major (3n) x (n_joint + 0|6)
+int emu_com(void *m, const double *qs, long n, const int *joints, int n_joint, const int *act, const double *forces, int n_act,
+            int base_type, int with_jacobian, int mode, double *com, double *J) {
+  try {
+    const KinematicModel &km = *static_cast<KinematicModel *>(m);
+    const ComTables ct = build_com_tables(km, act, forces, n_act);
+    PlanKey key;
+    key.elink_ids = ct.links;
+    key.joint_ids.assign(joints, joints + n_joint);
+    key.rot_type = 0;
+    key.base_type = base_type;
+    key.with_jacobian = with_jacobian;
+    key.model_version = km.version();
+    std::vector<unsigned char> blob = build_plan(km, key);
+    make_plan_params(blob); // the kernel-parameter limits apply (throws when exceeded)
+    if (mode == 1)
+      run_com<FkCore<MathNative32, true, 0, 1>, float>(blob, ct, qs, n, com, with_jacobian ? J : nullptr);
+    else
+      run_com<FkCore<MathPortable, false, 0, 1>, double>(blob, ct, qs, n, com, with_jacobian ? J : nullptr);
     return 0;
   } catch (const std::exception &e) {
     g_err = e.what();

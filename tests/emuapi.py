@@ -147,3 +147,21 @@ class EmuModel:
         if rc:
             raise ValueError(self._L.emu_last_error().decode())
         return sq, G
+
+    def solve_com_fk(self, qs, joint_ids, action_link_ids=(), forces=(), base_type=0, with_jacobian=False, mode=MODE_STRICT64):
+        """base_type 0 or 2 (the PLANER pad is host glue of the product's com_host, tested on the GPU)"""
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        j, al = _ints(joint_ids), _ints(action_link_ids)
+        f = np.ascontiguousarray(np.asarray(forces, dtype=np.float64).reshape(-1))
+        n, n_in = qs.shape
+        assert n_in == j.size + {0: 0, 2: 6}[int(base_type)]
+        com = np.zeros((n, 3))
+        J = np.zeros((3 * n, n_in), order="F")
+        self._L.emu_com.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int, ctypes.c_int,
+                                    ctypes.c_int, ctypes.c_int, _dp, _dp]
+        rc = self._L.emu_com(self._h, qs.ctypes.data_as(_dp), n, j.ctypes.data_as(_ip), j.size, al.ctypes.data_as(_ip),
+                             f.ctypes.data_as(_dp), al.size, int(base_type), int(bool(with_jacobian)), int(mode),
+                             com.ctypes.data_as(_dp), J.ctypes.data_as(_dp))
+        if rc:
+            raise ValueError(self._L.emu_last_error().decode())
+        return com, (J if with_jacobian else None)

@@ -25,7 +25,7 @@ def test_surface_and_enums():
     with pytest.raises(AssertionError):  # reference python/tinyfk/__init__.py:133-142
         kin.solve_fk(np.zeros((2, 7)), 71, kin.get_joint_ids(W.PR2_RARM), base_type=BaseType.PLANER)
     with pytest.raises(NotImplementedError):
-        kin.solve_com_fk([], [])
+        kin.compute_total_inertia_matrix(np.zeros(7), kin.get_joint_ids(W.PR2_RARM))
 
 
 def test_pickle_and_deepcopy_replay():

@@ -150,8 +150,18 @@ class KinematicModel:
         )
         return P, J
 
-    def solve_com_fk(self, *args, **kwargs):
-        raise NotImplementedError("solve_com_fk is outside the accelerated FK path (DESIGN.md, out of scope)")
+    def solve_com_fk(self, qs, joint_ids, action_link_ids=None, action_forces=None, base_type=BaseType.FIXED,
+                     with_jacobian=False, precision="fp64"):
+        """reference python/tinyfk/__init__.py:160-195 (batched on the GPU).  Returns (coms (n, 3), J (3n, n_dof));
+        n_dof = n_joint (+6 for PLANER and FLOATING: the reference pads a PLANER row and keeps all six base columns
+        on this entry); J is all zeros when with_jacobian is false.  Every row is evaluated from its own
+        configuration (the reference forgets clear_cache() here for a FIXED base and repeats row 0)."""
+        qs = np.atleast_2d(np.asarray(qs))
+        if action_link_ids is None:
+            action_link_ids, action_forces = [], []
+        return self._robot.solve_com_forward_kinematics_batch(
+            qs, list(joint_ids), list(action_link_ids), [float(f) for f in action_forces], base_type.value,
+            bool(with_jacobian), _PRECISION[precision])
 
     def compute_total_inertia_matrix(self, *args, **kwargs):
         raise NotImplementedError("compute_total_inertia_matrix is outside the accelerated FK path")

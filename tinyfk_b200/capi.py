@@ -21,7 +21,7 @@ SYMBOLS = [
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
-    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
+    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
 ]
 
@@ -67,6 +67,10 @@ def lib():
                                               ctypes.c_int, ctypes.c_int, _vp, _vp]
     L.tfk_inter_link_sqdists_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int,
                                                 ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
+    L.tfk_solve_com_fk_host.argtypes = [_vp, _vp, _i64, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                        ctypes.c_int, _vp, _vp]
+    L.tfk_solve_com_fk_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int,
+                                          ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
     L.tfk_device_count.argtypes = [_ip]
     L.tfk_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(_vp)]
     L.tfk_host_free.argtypes = [_vp]
@@ -269,6 +273,34 @@ class Model:
                                                      int(precision), _vp(d_sq), _vp(d_G) if d_G else None,
                                                      int(ld_cfg if ld_cfg is not None else n), int(row0)))
 
+    def solve_com_fk(self, qs, joint_ids, action_link_ids=(), forces=(), base_type=0, with_jacobian=False, precision=0):
+        """Host buffers through tfk_solve_com_fk_host.  Returns (com (n, 3), J (3n, n_joint + 0|6) F-ordered or None)."""
+        dt = np.float32 if precision == 1 else np.float64
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=dt)))
+        j, al = _ints(joint_ids), _ints(action_link_ids)
+        f = np.ascontiguousarray(np.asarray(forces, dtype=np.float64).reshape(-1))
+        if f.size != al.size:
+            raise ValueError("action_link_ids and forces differ in length")
+        n, n_in = qs.shape
+        if n_in != j.size + base_dof(base_type):
+            raise ValueError("dof mismatch")
+        n_dof = j.size + (6 if base_type else 0)
+        com = np.zeros((n, 3), dtype=dt)
+        J = np.zeros((3 * n, n_dof), dtype=dt, order="F") if with_jacobian else None
+        _check(self._L.tfk_solve_com_fk_host(self._h, qs.ctypes.data, n, j.ctypes.data_as(_ip), j.size, al.ctypes.data_as(_ip),
+                                             f.ctypes.data_as(_dp), al.size, int(base_type), int(bool(with_jacobian)),
+                                             int(precision), com.ctypes.data, J.ctypes.data if with_jacobian else None))
+        return com, J
+
+    def solve_com_fk_device(self, device, stream, d_q, n, joint_ids, action_link_ids, forces, base_type, with_jacobian,
+                            precision, d_com, d_J, ld_cfg=None, row0=0):
+        j, al = _ints(joint_ids), _ints(action_link_ids)
+        f = np.ascontiguousarray(np.asarray(forces, dtype=np.float64).reshape(-1))
+        _check(self._L.tfk_solve_com_fk_device(self._h, int(device), _vp(stream), _vp(d_q), int(n), j.ctypes.data_as(_ip), j.size,
+                                               al.ctypes.data_as(_ip), f.ctypes.data_as(_dp), al.size, int(base_type),
+                                               int(bool(with_jacobian)), int(precision), _vp(d_com), _vp(d_J) if d_J else None,
+                                               int(ld_cfg if ld_cfg is not None else n), int(row0)))
+
     def solve_fk_device(self, device, stream, d_q, n, elink_ids, joint_ids, rot_type, base_type, with_jacobian,
                         precision, d_P, d_J, ld_cfg=None, row0=0):
         """Raw device pointers (ints) through tfk_solve_fk_device; asynchronous on `stream`."""
@@ -286,7 +318,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel"}.get(k, "none")
         return d
 
 

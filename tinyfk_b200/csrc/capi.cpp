@@ -273,6 +273,48 @@ int tfk_inter_link_sqdists_device(tfk_model *m, int device, void *stream, const 
   });
 }
 
+static ComSpec make_com_spec(const tfk_model *m, const int *joint_ids, int n_joint, const int *action_link_ids,
+                             const double *forces, int n_action, int base_type, int with_jacobian, int precision) {
+  if (n_joint < 0 || (n_joint > 0 && !joint_ids)) throw std::invalid_argument("bad joint id array");
+  if (n_action < 0 || (n_action > 0 && (!action_link_ids || !forces))) throw std::invalid_argument("bad action link / force arrays");
+  ids_of(joint_ids, n_joint, m->engine.model.n_joints(), "joint");
+  ids_of(action_link_ids, n_action, m->engine.model.n_links(), "link");
+  if (base_type < 0 || base_type > 2) throw std::invalid_argument("base_type must be 0 (FIXED), 1 (PLANER) or 2 (FLOATING)");
+  ComSpec cs;
+  cs.joint_ids = joint_ids;
+  cs.n_joint = n_joint;
+  cs.action_link_ids = action_link_ids;
+  cs.forces = forces;
+  cs.n_action = n_action;
+  cs.base_type = base_type;
+  cs.with_jacobian = with_jacobian ? 1 : 0;
+  cs.precision = precision;
+  return cs;
+}
+
+int tfk_solve_com_fk_host(tfk_model *m, const void *q, int64_t n, const int *joint_ids, int n_joint,
+                          const int *action_link_ids, const double *forces, int n_action, int base_type,
+                          int with_jacobian, int precision, void *com, void *J) {
+  return guarded([&] {
+    need(m, "model");
+    ComSpec cs = make_com_spec(m, joint_ids, n_joint, action_link_ids, forces, n_action, base_type, with_jacobian, precision);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.com_host(q, n, cs, com, J);
+  });
+}
+
+int tfk_solve_com_fk_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n, const int *joint_ids,
+                            int n_joint, const int *action_link_ids, const double *forces, int n_action,
+                            int base_type, int with_jacobian, int precision, void *d_com, void *d_J, int64_t ld_cfg,
+                            int64_t row0) {
+  return guarded([&] {
+    need(m, "model");
+    ComSpec cs = make_com_spec(m, joint_ids, n_joint, action_link_ids, forces, n_action, base_type, with_jacobian, precision);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.com_device(device, static_cast<cudaStream_t>(stream), d_q, n, cs, d_com, d_J, ld_cfg, row0);
+  });
+}
+
 int tfk_device_count(int *count) {
   return guarded([&] {
     need(count, "count");

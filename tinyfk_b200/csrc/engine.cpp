@@ -108,6 +108,11 @@ void Engine::release_device_memory() {
     cudaFree(kv.second.d);
   }
   pair_bufs_.clear();
+  for (auto &kv : weight_bufs_) {
+    cudaSetDevice(kv.first.first);
+    cudaFree(kv.second.d);
+  }
+  weight_bufs_.clear();
   cudaSetDevice(prev);
 }
 
@@ -195,14 +200,15 @@ Engine::Workspace &Engine::workspace(int device, cudaStream_t stream, size_t byt
 }
 
 void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n,
-                    void *d_P, void *d_J, int64_t ld_cfg, int64_t row0, const int *d_pairs, int n_pairs) {
+                    void *d_P, void *d_J, int64_t ld_cfg, int64_t row0, const LaunchExtra *ex) {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (n <= 0 || h->n_out == 0) return;
-  const bool sqdist = d_pairs != nullptr;
+  const bool sqdist = ex && ex->variant == KV_SQDIST, com = ex && ex->variant == KV_COM;
+  const int n_pairs = sqdist ? ex->n_pairs : 0;
   if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
   const int rb = (int)real_size(precision);
   // per-output tables of the two-phase kernel: [lrec_of_out | masks], contiguous inside the blob
-  const int table_bytes = (h->n_out == 1 && !sqdist) ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
+  const int table_bytes = (h->n_out == 1 && !ex) ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
   const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
@@ -212,6 +218,10 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     rec_reals = h->rec_size;
     L = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, 0, rb);
     variant = KV_SQDIST;
+  } else if (com) {
+    rec_reals = h->rec_size;
+    L = smem_layout(table_bytes + (((ex->n_com + ex->n_act) * rb + 15) & ~15), h->n_in, 0, rb);
+    variant = KV_COM;
   } else if (h->n_out == 1) {
     rec_reals = h->fz_size;
     L = smem_layout(plan_bytes, h->n_in, rec_reals, rb);
@@ -259,8 +269,14 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.ld_cfg = ld_cfg;
   a.P = d_P;
   a.J = d_J;
-  a.pairs = d_pairs;
+  a.pairs = sqdist ? ex->d_pairs : nullptr;
   a.n_pairs = n_pairs;
+  a.weights = com ? ex->d_weights : nullptr;
+  a.n_com = com ? ex->n_com : 0;
+  a.n_act = com ? ex->n_act : 0;
+  a.mass_total = com ? ex->mass_total : 0.0;
+  a.vfs = com ? ex->vfs : 0.0;
+  a.com_diag = com ? ex->com_diag : 0.0;
   ck(precision == PREC_F32 ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
                            : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
      "kernel launch");
@@ -363,7 +379,11 @@ void Engine::sqdists_device(int device, cudaStream_t stream, const void *d_q, in
     ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(pairs)"); // o12 is a pageable temporary
     pb.host = o12;
   }
-  launch(device, stream, e, ps.precision, d_q, n, d_sq, ps.with_grads ? d_G : nullptr, ld_cfg, row0, pb.d, ps.n_check);
+  LaunchExtra ex = LaunchExtra();
+  ex.variant = KV_SQDIST;
+  ex.d_pairs = pb.d;
+  ex.n_pairs = ps.n_check;
+  launch(device, stream, e, ps.precision, d_q, n, d_sq, ps.with_grads ? d_G : nullptr, ld_cfg, row0, &ex);
 }
 
 // Host buffers in, host buffers out, current device.  Outputs are small next to the FK arrays
@@ -412,6 +432,141 @@ void Engine::sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq
     model.set_base_pose_xyzrpy(b);
   } else if (h.base_type == BASE_FLOATING) {
     model.set_base_pose_xyzrpy(&last[ps.n_joint]);
+  }
+}
+
+// ---- centre of mass (reference src/wrapper.cpp:126-179) --------------------------------------------------------
+// Plan links = the model's "_com" links in id order, then the action links (RotationType IGNORE).
+void Engine::com_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const ComSpec &cs, void *d_com,
+                        void *d_J, int64_t ld_cfg, int64_t row0) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (row0 < 0 || row0 + n > ld_cfg) throw std::invalid_argument("rows [row0, row0+n) exceed ld_cfg");
+  if (cs.n_action < 0 || cs.n_joint < 0) throw std::invalid_argument("negative id count");
+  if (cs.base_type != BASE_FIXED && cs.base_type != BASE_FLOATING)
+    throw std::invalid_argument("centre of mass on device buffers takes a FIXED or FLOATING base (pad a PLANER row to x y 0 0 0 yaw as "
+                                "python/tinyfk/__init__.py:98-103 does; the host entry does it)");
+  const ComTables ct = build_com_tables(model, cs.action_link_ids, cs.forces, cs.n_action);
+  const std::vector<int> &links = ct.links;
+  SolveSpec s;
+  s.elink_ids = links.data();
+  s.n_link = (int)links.size();
+  s.joint_ids = cs.joint_ids;
+  s.n_joint = cs.n_joint;
+  s.rot_type = ROT_IGNORE;
+  s.base_type = cs.base_type;
+  s.with_jacobian = cs.with_jacobian;
+  s.precision = cs.precision;
+  PlanEntry &e = plan_for(s);
+  if (n == 0) return;
+  if (!d_q && reinterpret_cast<const PlanHeader *>(e.blob.data())->n_in > 0) throw std::invalid_argument("q is null");
+  if (!d_com) throw std::invalid_argument("com is null");
+  if (cs.with_jacobian && !d_J) throw std::invalid_argument("J is null but with_jacobian is set");
+  const std::vector<double> &w = ct.w;
+  DeviceGuard g(device);
+  WeightBuf &wb = weight_bufs_[std::make_pair(device, stream)];
+  const size_t need = w.size() * real_size(cs.precision);
+  if (wb.bytes < need) {
+    if (wb.d) {
+      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
+      cudaFree(wb.d);
+      wb.d = nullptr;
+      wb.bytes = 0;
+    }
+    ck(cudaMalloc(&wb.d, need), "cudaMalloc(weights)");
+    wb.bytes = need;
+    wb.host.clear();
+  }
+  if (wb.host != w || wb.precision != cs.precision) {
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // earlier launches still read the old table
+    std::vector<float> wf(w.begin(), w.end());
+    const void *src = cs.precision == PREC_F32 ? static_cast<const void *>(wf.data()) : static_cast<const void *>(w.data());
+    ck(cudaMemcpyAsync(wb.d, src, need, cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(weights)");
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // pageable temporaries
+    wb.host = w;
+    wb.precision = cs.precision;
+  }
+  LaunchExtra ex = LaunchExtra();
+  ex.variant = KV_COM;
+  ex.d_weights = wb.d;
+  ex.n_com = ct.n_com;
+  ex.n_act = ct.n_act;
+  ex.mass_total = ct.mass_total;
+  ex.vfs = ct.vfs;
+  ex.com_diag = ct.diag;
+  launch(device, stream, e, cs.precision, d_q, n, d_com, cs.with_jacobian ? d_J : nullptr, ld_cfg, row0, &ex);
+}
+
+// Host buffers in, host buffers out, current device.  q rows are [joints | base]; a PLANER row (x, y, yaw) is padded
+// to the FLOATING row the reference's facade builds (python/tinyfk/__init__.py:98-103, 180-182) and the Jacobian keeps
+// all six base columns, exactly as solve_com_fk returns it.
+//   com  (n, 3) row-major;  J  column-major (3n) x (n_joint + 0|6)
+void Engine::com_host(const void *q, int64_t n, const ComSpec &cs_in, void *com, void *J) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (cs_in.base_type < 0 || cs_in.base_type > 2) throw std::invalid_argument("unknown base type");
+  ComSpec cs = cs_in;
+  const int nj = cs.n_joint;
+  const int n_in_user = nj + (cs.base_type == BASE_PLANER ? 3 : (cs.base_type == BASE_FLOATING ? 6 : 0));
+  if (cs.base_type == BASE_PLANER) cs.base_type = BASE_FLOATING;
+  const int n_in = nj + (cs.base_type == BASE_FLOATING ? 6 : 0);
+  const int n_dof = n_in;
+  if (n == 0) {
+    com_device(0, nullptr, nullptr, 0, cs, nullptr, nullptr, 0, 0); // validates ids
+    return;
+  }
+  if (!q && n_in_user > 0) throw std::invalid_argument("q is null");
+  if (!com) throw std::invalid_argument("com is null");
+  if (cs.with_jacobian && !J) throw std::invalid_argument("J is null but with_jacobian is set");
+  int cur = 0;
+  ck(cudaGetDevice(&cur), "cudaGetDevice (is a CUDA device present? there is no CPU fallback)");
+  HostPipe &pp = pipe(cur);
+  cudaStream_t st = pp.stream[0];
+  const size_t sz = real_size(cs.precision);
+  const size_t in_row = (size_t)n_in * sz;
+  const int64_t chunk = std::max<int64_t>(8192, (int64_t)((size_t(64) << 20) / std::max<size_t>(3 * sz * (1 + n_dof), 1)));
+  const int64_t capn = std::min<int64_t>(chunk, n);
+  grow(&pp.dq[0], &pp.cap_q[0], std::max<size_t>((size_t)capn * in_row, 16), st);
+  grow(&pp.dP[0], &pp.cap_P[0], (size_t)capn * 3 * sz, st);
+  if (cs.with_jacobian) grow(&pp.dJ[0], &pp.cap_J[0], std::max<size_t>((size_t)capn * 3 * sz * n_dof, 16), st);
+  const char *qb = static_cast<const char *>(q);
+  std::vector<char> padded, comT;
+  for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+    const int64_t nc = std::min<int64_t>(chunk, n - r0);
+    const char *src = qb + (size_t)r0 * n_in_user * sz;
+    if (cs_in.base_type == BASE_PLANER) {
+      padded.assign((size_t)nc * in_row, 0);
+      for (int64_t i = 0; i < nc; ++i) {
+        const char *r = src + (size_t)i * n_in_user * sz;
+        char *d = padded.data() + (size_t)i * in_row;
+        std::memcpy(d, r, (size_t)(nj + 2) * sz);                          // joints, x, y
+        std::memcpy(d + (size_t)(nj + 5) * sz, r + (size_t)(nj + 2) * sz, sz); // yaw
+      }
+      src = padded.data();
+    }
+    if (in_row) ck(cudaMemcpyAsync(pp.dq[0], src, (size_t)nc * in_row, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(q)");
+    com_device(cur, st, pp.dq[0], nc, cs, pp.dP[0], cs.with_jacobian ? pp.dJ[0] : nullptr, nc, 0);
+    comT.resize((size_t)nc * 3 * sz);
+    ck(cudaMemcpyAsync(comT.data(), pp.dP[0], (size_t)nc * 3 * sz, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(com)");
+    if (cs.with_jacobian)
+      for (int c = 0; c < n_dof; ++c)
+        ck(cudaMemcpyAsync(static_cast<char *>(J) + ((size_t)c * n + r0) * 3 * sz, static_cast<char *>(pp.dJ[0]) + (size_t)c * nc * 3 * sz,
+                           (size_t)nc * 3 * sz, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(J)");
+    ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    for (int64_t i = 0; i < nc; ++i) // (3, nc) component-major -> (n, 3) rows
+      for (int k = 0; k < 3; ++k)
+        std::memcpy(static_cast<char *>(com) + ((size_t)(r0 + i) * 3 + k) * sz, comT.data() + ((size_t)k * nc + i) * sz, sz);
+  }
+  // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:137-141)
+  std::vector<size_t> ids(cs.joint_ids, cs.joint_ids + nj);
+  std::vector<double> last((size_t)n_in_user);
+  for (int c = 0; c < n_in_user; ++c)
+    last[c] = cs.precision == PREC_F32 ? (double)reinterpret_cast<const float *>(qb)[(size_t)(n - 1) * n_in_user + c]
+                                       : reinterpret_cast<const double *>(qb)[(size_t)(n - 1) * n_in_user + c];
+  if (nj > 0) model.set_joint_angles(ids, std::vector<double>(last.begin(), last.begin() + nj));
+  if (cs_in.base_type == BASE_PLANER) {
+    const double b[6] = {last[nj], last[nj + 1], 0.0, 0.0, 0.0, last[nj + 2]};
+    model.set_base_pose_xyzrpy(b);
+  } else if (cs_in.base_type == BASE_FLOATING) {
+    model.set_base_pose_xyzrpy(&last[nj]);
   }
 }
 

@@ -43,6 +43,15 @@ struct PairSpec { // compute_inter_link_squared_dists (reference src/wrapper.cpp
   int base_type, with_grads, precision;
 };
 
+struct ComSpec { // solve_com_forward_kinematics (reference src/wrapper.cpp:126-179)
+  const int *joint_ids;
+  int n_joint;
+  const int *action_link_ids;
+  const double *forces;
+  int n_action;
+  int base_type, with_jacobian, precision; // base_type: FIXED or FLOATING on the device entry (PLANER: host entry pads)
+};
+
 struct LaunchInfo {
   int grid, block, smem_bytes, blocks_per_sm, rec_reals, variant;
 };
@@ -61,6 +70,9 @@ public:
   void sqdists_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const PairSpec &ps, void *d_sq,
                       void *d_G, int64_t ld_cfg, int64_t row0);
   void sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq, void *G);
+  void com_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const ComSpec &cs, void *d_com, void *d_J,
+                  int64_t ld_cfg, int64_t row0);
+  void com_host(const void *q, int64_t n, const ComSpec &cs, void *com, void *J);
   LaunchInfo last_launch;
 
 private:
@@ -81,13 +93,21 @@ private:
     bool ready;
   };
 
+  struct LaunchExtra { // what the pair / centre-of-mass kernels need beyond the plan
+    int variant;
+    const int *d_pairs;
+    int n_pairs;
+    const void *d_weights;
+    int n_com, n_act;
+    double mass_total, vfs, com_diag;
+  };
   PlanEntry &plan_for(const SolveSpec &spec);
   const unsigned char *plan_on_device(PlanEntry &e, int device, cudaStream_t stream);
   Workspace &workspace(int device, cudaStream_t stream, size_t bytes);
   HostPipe &pipe(int device);
   int sm_count(int device);
   void launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n, void *d_P,
-              void *d_J, int64_t ld_cfg, int64_t row0, const int *d_pairs = nullptr, int n_pairs = 0);
+              void *d_J, int64_t ld_cfg, int64_t row0, const LaunchExtra *ex = nullptr);
   PlanEntry &plan_for_pairs(const PairSpec &ps, std::vector<int> &o12);
   struct PairBuf {
     int *d = nullptr;
@@ -95,6 +115,13 @@ private:
     std::vector<int> host;
   };
   std::map<std::pair<int, cudaStream_t>, PairBuf> pair_bufs_;
+  struct WeightBuf {
+    void *d = nullptr;
+    size_t bytes = 0;
+    std::vector<double> host;
+    int precision = -1;
+  };
+  std::map<std::pair<int, cudaStream_t>, WeightBuf> weight_bufs_;
   void release_device_memory();
 
   std::vector<std::unique_ptr<PlanEntry>> plans_;

@@ -649,6 +649,92 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   }
 
   // ---------------------------------------------------------------------------------------------
+  // solve_com_forward_kinematics (src/wrapper.cpp:126-179; get_com / get_com_jacobian,
+  // src/kinematics.cpp:237-270) on the records of phase A.  The plan's links are the model's "<name>_com"
+  // links in id order (weights w[o] = link mass) followed by the caller's action links (w[o] = force /
+  // total mass).  One work item produces one 3-vector of the result for one configuration:
+  //   item 0                    the centre of mass itself
+  //   item 1 + c                column c of the COM Jacobian (joint c)
+  //   item 1 + n_cols + k       base rotation column k (roll, pitch, yaw), finite difference as get_jacobian
+  // and the reference's order of accumulation is kept per element:
+  //   acc = 0; for com links: acc += m * v;  acc /= mass_total;  for action links: acc += f * v;  acc /= vfs
+  // (the base translation columns are the constant `diag` times the identity: evaluated on the host).
+  struct ComArgs {
+    const T *w;     // n_com + n_act weights
+    int n_com, n_act;
+    T mass_total, vfs;
+  };
+  static TFK_FN V com_item(const PlanView &pv, const T *rec, int item, const ComArgs &ca) {
+    const PlanHeader &h = *pv.h;
+    const int kind = (item == 0) ? 0 : ((item <= h.n_cols) ? 1 : 2); // warp-uniform
+    const int c = item - 1;
+    const int k = item - 1 - h.n_cols;
+    BaseFromRec bs;
+    bs.rec = rec;
+    bs.stride = STRIDE;
+    bs.at = h.off_base;
+    V base_p, wk;
+    P binv;
+    Q bi, bq, bqi;
+    base_p.x = base_p.y = base_p.z = T(0);
+    wk = base_p;
+    binv.p = base_p;
+    binv.q = bi = bq = bqi = O::qidentity();
+    if (kind == 2) {
+      base_p = bs.base_p();
+      if (ANALYTIC_BASE) {
+        wk = bs.w(k);
+      } else {
+        binv = bs.binv();
+        bi = O::qget_inverse(binv.q);
+        bq = bs.bk(k);
+        bqi = O::qget_inverse(bq);
+      }
+    }
+    const typename M::Den deps = M::den_(T(1e-7));
+    V acc;
+    acc.x = acc.y = acc.z = T(0);
+    const int n_tot = ca.n_com + ca.n_act;
+    TFK_NOUNROLL
+    for (int o = 0; o < n_tot; ++o) {
+      if (o == ca.n_com) {
+        T a[3] = {acc.x, acc.y, acc.z};
+        M::divn_(a, M::den_(ca.mass_total));
+        acc.x = a[0], acc.y = a[1], acc.z = a[2];
+      }
+      const V p = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o] * LREC);
+      V v = p;
+      if (kind == 1) {
+        v = pos_joint_col(pv, rec, p, o, c);
+      } else if (kind == 2) {
+        if (ANALYTIC_BASE) {
+          V d;
+          d.x = p.x - base_p.x, d.y = p.y - base_p.y, d.z = p.z - base_p.z;
+          v = O::cross(wk, d);
+        } else { // src/kinematics.cpp:182-232, position rows
+          const V r0 = O::qt_xyz(binv.q, O::vq_full(p, bi));
+          V be;
+          be.x = r0.x + binv.p.x, be.y = r0.y + binv.p.y, be.z = r0.z + binv.p.z;
+          const V r1 = O::qt_xyz(bq, O::vq_full(be, bqi));
+          T nn[3] = {(r1.x + base_p.x) - p.x, (r1.y + base_p.y) - p.y, (r1.z + base_p.z) - p.z};
+          M::divn_(nn, deps);
+          v.x = nn[0], v.y = nn[1], v.z = nn[2];
+        }
+      }
+      const T wo = ca.w[o];
+      acc.x = acc.x + wo * v.x;
+      acc.y = acc.y + wo * v.y;
+      acc.z = acc.z + wo * v.z;
+    }
+    {
+      T a[3] = {acc.x, acc.y, acc.z};
+      M::divn_(a, M::den_(ca.n_act > 0 ? ca.vfs : ca.mass_total));
+      acc.x = a[0], acc.y = a[1], acc.z = a[2];
+    }
+    return acc;
+  }
+
+  // ---------------------------------------------------------------------------------------------
   // fused driver (n_out == 1): the requested link is the last slot of the pruned chain (or the root),
   // so walk() returns its pose and the same thread emits the outputs; records use the fz_* layout.
   // OutFactory::make() builds the output sink only once the walk is done (nothing of it stays live

@@ -264,6 +264,88 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_sqdist_kernel(const KernelArgs
   }
 }
 
+// ---- centre of mass (src/wrapper.cpp:126-179) ----------------------------------------------------------------
+// Phase A as above over the model's "_com" links (+ action links).  Phase B: the same thread walks the work
+// items of its configuration (Core::com_item: COM, then one Jacobian column at a time), so a warp works on ONE
+// column for 32 consecutive configurations: the relevance test and the column's plan entries are warp-uniform,
+// record reads are coalesced (element k of configuration i at rec[k*TILE + i]) and the three stores of a warp
+// cover 768 contiguous bytes.
+//   com  (3, ld_cfg) component-major: com[k*ld + row]
+//   J    column-major (3*ld_cfg) x n_dof: J[c*3*ld + 3*row + k]   (Eigen's layout of wrapper.cpp:134)
+template <class Core>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_com_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+  typedef typename Core::T T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
+  const PlanHeader &h = pp.h;
+  const int tab = (a.table_bytes + 15) & ~15;
+  const int n_w = a.n_com + a.n_act;
+  T *w = reinterpret_cast<T *>(smem + tab);
+  for (int i = threadIdx.x; i < n_w; i += TFK_TILE) w[i] = static_cast<const T *>(a.weights)[i];
+  __syncthreads();
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
+  pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
+  const SmemLayout L = smem_layout(tab + ((n_w * (int)sizeof(T) + 15) & ~15), h.n_in, 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  const T *q = static_cast<const T *>(a.q);
+  T *com = static_cast<T *>(a.P);
+  T *J = static_cast<T *>(a.J);
+  typename Core::ComArgs ca;
+  ca.w = w;
+  ca.n_com = a.n_com;
+  ca.n_act = a.n_act;
+  ca.mass_total = (T)a.mass_total;
+  ca.vfs = (T)a.vfs;
+  const int n_base = (h.base_type == 0) ? 0 : 6;
+  // work items per configuration: COM, joint columns, three base rotation columns (translation columns are constant)
+  const int n_items = 1 + (J ? h.n_cols + (n_base ? 3 : 0) : 0);
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
+    __syncthreads();
+    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+    __syncthreads();
+    const long long row = a.row0 + i0 + threadIdx.x;
+    if ((int)threadIdx.x < nv) {
+      TFK_NOUNROLL
+      for (int item = 0; item < n_items; ++item) {
+        const typename Core::V v = Core::com_item(pv, rec + threadIdx.x, item, ca);
+        if (item == 0) {
+          __stcs(com + row, v.x);
+          __stcs(com + a.ld_cfg + row, v.y);
+          __stcs(com + 2 * a.ld_cfg + row, v.z);
+        } else {
+          const int col = (item <= h.n_cols) ? item - 1 : item + 2; // rotation columns follow the three translation columns
+          T *o = J + (size_t)col * 3 * a.ld_cfg + 3 * row;
+          __stcs(o, v.x);
+          __stcs(o + 1, v.y);
+          __stcs(o + 2, v.z);
+        }
+      }
+      if (J && n_base) { // d com / d base translation = diag * I (host-evaluated constant, engine.cpp)
+        const T dg = (T)a.com_diag;
+        for (int k = 0; k < 3; ++k) {
+          T *o = J + (size_t)(h.n_cols + k) * 3 * a.ld_cfg + 3 * row;
+          __stcs(o, k == 0 ? dg : T(0));
+          __stcs(o + 1, k == 1 ? dg : T(0));
+          __stcs(o + 2, k == 2 ? dg : T(0));
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // the pair kernel exists for RotationType IGNORE only (positions); other instantiations never reach it
 template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
   fk_sqdist_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
@@ -273,6 +355,17 @@ template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type o
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_sqdist_kernel<Core>, TFK_TILE, smem_bytes);
 }
 template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_sqdist(int, int *blocks_per_sm) {
+  *blocks_per_sm = 0;
+  return cudaSuccess;
+}
+template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_com(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
+  fk_com_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+}
+template <class Core> typename std::enable_if<Core::D != 3, void>::type launch_com(const KernelArgs &, const PlanParams &, int, int, cudaStream_t) {}
+template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type occupancy_com(int smem_bytes, int *blocks_per_sm) {
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_com_kernel<Core>, TFK_TILE, smem_bytes);
+}
+template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_com(int, int *blocks_per_sm) {
   *blocks_per_sm = 0;
   return cudaSuccess;
 }
@@ -287,6 +380,8 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
     fk_fused_kernel<Core, false, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_SQDIST)
     launch_sqdist<Core>(a, pp, grid, smem_bytes, stream);
+  else if (variant == KV_COM)
+    launch_com<Core>(a, pp, grid, smem_bytes, stream);
   else
     fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
@@ -294,6 +389,7 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
 
 template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
   if (variant == KV_SQDIST) return occupancy_sqdist<Core>(smem_bytes, blocks_per_sm);
+  if (variant == KV_COM) return occupancy_com<Core>(smem_bytes, blocks_per_sm);
   const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>
                    : variant == KV_FUSED_SMEM ? (const void *)fk_fused_kernel<Core, true, 4>
                    : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false, 4>

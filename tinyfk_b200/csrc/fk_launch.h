@@ -20,6 +20,7 @@ enum KernelVariant {
   KV_FUSED_GMEM = 1, // one requested link, records too large for shared memory: block-private global scratch
   KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
   KV_SQDIST = 4,      // inter-link squared distances: phase A -> records -> one thread per (configuration, pair)
+  KV_COM = 5,         // centre of mass (+ Jacobian): phase A -> records -> mass-weighted sums in link-id order
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };
@@ -36,6 +37,10 @@ struct KernelArgs {
   // KV_SQDIST only: P = sqdists [ld_cfg*n_pairs], J = grads column-major (ld_cfg*n_pairs) x n_dof (or null)
   const int *pairs;  // device: o1[n_pairs] then o2[n_pairs], indices into the plan's elink list
   int n_pairs;
+  // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
+  const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
+  int n_com, n_act;
+  double mass_total, vfs, com_diag;
 };
 
 // Dynamic shared memory of a block: [per-output tables | q tile (doubles as the warps' staging strips) | records]

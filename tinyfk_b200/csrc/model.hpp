@@ -70,6 +70,8 @@ public:
   size_t n_links() const { return links_.size(); }
   size_t n_joints() const { return joints_.size(); }
   double total_mass() const { return total_mass_; }
+  // ids of the "<name>_com" links in creation (= id) order: com_dummy_links_ of src/tinyfk.cpp:89-111
+  const std::vector<int> &com_links() const { return com_links_; }
 
   // ---- limits (src/tinyfk.cpp:164-201): continuous joints -> (-inf, +inf)
   std::vector<std::pair<double, double>> get_joint_position_limits(const std::vector<size_t> &ids) const;

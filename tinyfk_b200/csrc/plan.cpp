@@ -304,4 +304,33 @@ std::unique_ptr<PlanParams> make_plan_params(const std::vector<unsigned char> &b
   return p;
 }
 
+ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action) {
+  ComTables t;
+  const std::vector<int> &cl = model.com_links();
+  if (cl.empty()) throw std::invalid_argument("the model has no link with an <inertial>: centre of mass undefined");
+  if (n_action < 0 || (n_action > 0 && (!action_link_ids || !forces))) throw std::invalid_argument("bad action link / force arrays");
+  t.links.assign(cl.begin(), cl.end());
+  t.n_com = (int)cl.size();
+  t.n_act = n_action;
+  t.mass_total = 0.0;
+  t.diag = 0.0;
+  for (int id : cl) {
+    const double m = model.links()[id].mass;
+    t.w.push_back(m);
+    t.mass_total += m;
+    t.diag = t.diag + m * 1.0; // jac_average(k, n_joint + k) += mass * 1.0 (kinematics.cpp:194-196, 263)
+  }
+  t.diag = t.diag / t.mass_total;
+  t.vfs = 1.0;
+  for (int j = 0; j < n_action; ++j) {
+    const double f = forces[j] / model.total_mass(); // wrapper.cpp:156
+    t.links.push_back(action_link_ids[j]);
+    t.w.push_back(f);
+    t.vfs += f;
+    t.diag = t.diag + f * 1.0;
+  }
+  if (n_action > 0) t.diag = t.diag / t.vfs;
+  return t;
+}
+
 } // namespace tfk

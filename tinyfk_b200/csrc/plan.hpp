@@ -28,6 +28,18 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
 // list exceeds what the parameter block holds (TFK_PSLOTS links, TFK_PCOLS joints).
 std::unique_ptr<PlanParams> make_plan_params(const std::vector<unsigned char> &blob);
 
+// Constants of solve_com_forward_kinematics (src/wrapper.cpp:126-179, src/kinematics.cpp:237-270), evaluated in the
+// reference's own order: links = "_com" links in id order then the action links; w = masses then forces/total_mass.
+struct ComTables {
+  std::vector<int> links;
+  std::vector<double> w;
+  int n_com, n_act;
+  double mass_total; // sum of the com links' masses (kinematics.cpp:242, 260)
+  double vfs;        // 1 + sum of forces/total_mass (wrapper.cpp:153-157)
+  double diag;       // d com / d base translation: ((sum m*1)/mass_total [+ sum f*1] [/ vfs])
+};
+ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action);
+
 inline int pose_dim_of(int rot_type) { return 3 + (rot_type == ROT_RPY) * 3 + (rot_type == ROT_XYZW) * 4; }
 inline int base_dof_of(int base_type) { return base_type == BASE_PLANER ? 3 : (base_type == BASE_FLOATING ? 6 : 0); }
 

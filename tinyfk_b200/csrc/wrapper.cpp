@@ -3,8 +3,8 @@
 // numpy in / numpy out, no PyTorch.  Method names, argument order and error types follow the
 // reference; everything numerical happens behind tfk_solve_fk_host (CUDA, no CPU fallback).
 //
-// Out of scope here ("next"): solve_com_forward_kinematics,
-// compute_total_inertia_matrix, compute_inter_link_squared_dists -- they raise NotImplementedError.
+// SURVEY.md section 8(f) rows built on the same path: compute_inter_link_squared_dists (rank 1),
+// solve_com_forward_kinematics (rank 2).  compute_total_inertia_matrix raises NotImplementedError.
 #include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
@@ -172,6 +172,29 @@ public:
                          TFK_F64_STRICT);
   }
 
+  // solve_com_forward_kinematics (src/wrapper.cpp:126-179), batched: returns (coms (n, 3), J (3n, n_dof) F-ordered,
+  // all zeros when !with_jacobian as the reference).  base_type PLANER takes (x, y, yaw) rows and returns the six
+  // base columns of the padded row, as KinematicModel.solve_com_fk does (python/tinyfk/__init__.py:180-195).
+  py::tuple com_batch(py::array qs_in, const std::vector<size_t> &joint_ids, const std::vector<size_t> &action_link_ids,
+                      const std::vector<double> &forces, int base_type, bool with_jacobian, int precision) {
+    if (base_type < 0 || base_type > 2) throw std::invalid_argument("bad base_type");
+    if (action_link_ids.size() != forces.size()) throw std::invalid_argument("action_link_ids and forces differ in length");
+    const size_t n_in = joint_ids.size() + (base_type == 1 ? 3 : (base_type == 2 ? 6 : 0));
+    std::vector<int> j = to_int(joint_ids), al = to_int(action_link_ids);
+    if (precision == TFK_F32)
+      return run_com<float>(py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(qs_in), j, al, forces, base_type,
+                            with_jacobian, precision, n_in);
+    return run_com<double>(py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(qs_in), j, al, forces, base_type,
+                           with_jacobian, precision, n_in);
+  }
+  // the reference's 6-argument entry: with_base means the 6-D floating base
+  py::tuple solve_com_forward_kinematics(py::array qs, const std::vector<size_t> &joint_ids,
+                                         const std::vector<size_t> &action_link_ids, const std::vector<double> &forces,
+                                         bool with_base, bool with_jacobian) {
+    return com_batch(qs, joint_ids, action_link_ids, forces, with_base ? TFK_BASE_FLOATING : TFK_BASE_FIXED, with_jacobian,
+                     TFK_F64_STRICT);
+  }
+
   int64_t kernel_launches() const { return tfk_kernel_launch_count(); }
 
 private:
@@ -235,6 +258,40 @@ private:
     return py::make_tuple(sq, G);
   }
 
+  template <class T>
+  py::tuple run_com(py::array_t<T, py::array::c_style | py::array::forcecast> qs, const std::vector<int> &j,
+                    const std::vector<int> &al, const std::vector<double> &forces, int base_type, bool with_jacobian,
+                    int precision, size_t n_in) {
+    if (!qs) throw std::invalid_argument("qs must be convertible to a 2-D float array");
+    if (qs.ndim() != 2) throw std::invalid_argument("qs must be 2-D (n_configs, n_dof)");
+    if ((size_t)qs.shape(1) != n_in)
+      throw std::invalid_argument("dof mismatch: expected " + std::to_string(n_in) + " columns, got " +
+                                  std::to_string(qs.shape(1)));
+    const size_t n = (size_t)qs.shape(0), n_dof = j.size() + (base_type == 0 ? 0 : 6);
+    py::array_t<T> com(std::vector<py::ssize_t>{(py::ssize_t)n, 3});
+    if (!with_jacobian) {
+      int rc;
+      {
+        py::gil_scoped_release nogil;
+        rc = tfk_solve_com_fk_host(m_, qs.data(), (int64_t)n, j.data(), (int)j.size(), al.data(), forces.data(), (int)al.size(),
+                                   base_type, 0, precision, com.mutable_data(), nullptr);
+      }
+      check(rc);
+      py::object zeros = py::module_::import("numpy").attr("zeros")(
+          py::make_tuple(3 * n, n_dof), py::arg("dtype") = py::dtype::of<T>(), py::arg("order") = "F");
+      return py::make_tuple(com, zeros);
+    }
+    py::array_t<T, py::array::f_style> J(std::vector<py::ssize_t>{(py::ssize_t)(3 * n), (py::ssize_t)n_dof});
+    int rc;
+    {
+      py::gil_scoped_release nogil;
+      rc = tfk_solve_com_fk_host(m_, qs.data(), (int64_t)n, j.data(), (int)j.size(), al.data(), forces.data(), (int)al.size(),
+                                 base_type, 1, precision, com.mutable_data(), J.mutable_data());
+    }
+    check(rc);
+    return py::make_tuple(com, J);
+  }
+
   tfk_model *m_;
 };
 
@@ -265,7 +322,10 @@ PYBIND11_MODULE(_tinyfk, m) {
            py::arg("pinned_output") = true)
       .def("get_joint_angles", &RobotModel::get_joint_angles)
       .def("set_joint_angles", &RobotModel::set_joint_angles)
-      .def("solve_com_forward_kinematics", [](RobotModel &, py::args, py::kwargs) { not_on_path("solve_com_forward_kinematics"); })
+      .def("solve_com_forward_kinematics", &RobotModel::solve_com_forward_kinematics)
+      .def("solve_com_forward_kinematics_batch", &RobotModel::com_batch, py::arg("qs"), py::arg("joint_ids"),
+           py::arg("action_link_ids"), py::arg("forces"), py::arg("base_type"), py::arg("with_jacobian"),
+           py::arg("precision") = (int)TFK_F64_STRICT)
       .def("compute_total_inertia_matrix", [](RobotModel &, py::args, py::kwargs) { not_on_path("compute_total_inertia_matrix"); })
       .def("get_joint_names", &RobotModel::get_joint_names)
       .def("get_joint_ids", &RobotModel::get_joint_ids)
