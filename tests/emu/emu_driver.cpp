@@ -13,6 +13,8 @@
 #include "../../tinyfk_b200/csrc/model.hpp"
 #include "../../tinyfk_b200/csrc/plan.hpp"
 
+#include <stdexcept>
+
 using namespace tfk;
 
 static thread_local std::string g_err;
@@ -169,6 +171,26 @@ int emu_com(void *m, const double *qs, long n, const int *joints, int n_joint, c
   } catch (const std::exception &e) {
     g_err = e.what();
     return 1;
+  }
+}
+// plan.cpp:plan_to_source for a single-link query; returns the length written (0 on error)
+long emu_plan_source(void *m, const int *elinks, int n_link, const int *joints, int n_joint, int rot_type, int base_type,
+                     int with_jacobian, char *buf, long cap) {
+  try {
+    PlanKey key;
+    key.elink_ids.assign(elinks, elinks + n_link);
+    key.joint_ids.assign(joints, joints + n_joint);
+    key.rot_type = rot_type;
+    key.base_type = base_type;
+    key.with_jacobian = with_jacobian;
+    key.model_version = static_cast<KinematicModel *>(m)->version();
+    const std::string src = plan_to_source(build_plan(*static_cast<KinematicModel *>(m), key));
+    if ((long)src.size() + 1 > cap) throw std::invalid_argument("buffer too small");
+    std::memcpy(buf, src.c_str(), src.size() + 1);
+    return (long)src.size();
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 0;
   }
 }
 // MathPortable::div_ (shared-reciprocal IEEE division, fk_math.h) on arrays: must equal a[i] / b[i]

@@ -27,9 +27,17 @@
 #if defined(__CUDACC__)
 #define TFK_UNROLL _Pragma("unroll")
 #define TFK_NOUNROLL _Pragma("unroll 1")
+// loops over the plan (slots, Jacobian columns, base columns): one copy of the body in the generic kernels; fully
+// unrolled in a plan-specialised build, where the plan is a compile-time constant and every test on it folds away
+#if defined(TFK_SPEC_PLAN)
+#define TFK_PLAN_LOOP _Pragma("unroll")
+#else
+#define TFK_PLAN_LOOP _Pragma("unroll 1")
+#endif
 #else
 #define TFK_UNROLL
 #define TFK_NOUNROLL
+#define TFK_PLAN_LOOP
 #endif
 
 namespace tfk {
@@ -154,20 +162,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       // setFromRPY(0, 0, yaw), pose.h:202-216: sin(0) = 0, cos(0) = 1 exactly, so the products with
       // them are exact and x = y = 0, z = sin(yaw/2), w = cos(yaw/2) before normalize
       base.p.z = T(0);
-      T s, c;
-      M::sincos_(b[2] / T(2), &s, &c);
-      base.q.x = T(0);
-      base.q.y = T(0);
-      base.q.z = s;
-      base.q.w = c;
-      const T n = M::sqrt_(s * s + c * c); // x*x + y*y + z*z + w*w with x = y = 0 (pose.h:232)
-      if (n == T(0)) {
-        base.q = O::qidentity();
-      } else {
-        const typename M::Den d = M::den_(n);
-        base.q.z = M::div_(s, d);
-        base.q.w = M::div_(c, d);
-      }
+      base.q = O::qz_dense(O::qz_from_yaw(b[2]));
     } else {
       base.p.z = b[2];
       base.q = O::from_rpy(b[3], b[4], b[5]);
@@ -206,7 +201,33 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   }
 
   // two-phase: phase A stores the context once per configuration, phase B reads what it needs, late
+  // PLANER: everything is yaw-only (fk_math.h "yaw-only rotations"); same record layout, x = y = 0
+  struct PlanerCtx {
+    V base_p;
+    typename O::PZ binv;
+    typename O::QZ bk; // setFromRPY(0, 0, yaw_b + eps), the only tweaked rotation PLANER keeps
+  };
+  static TFK_FN PlanerCtx planer_ctx(const P &base) {
+    PlanerCtx c;
+    c.base_p = base.p;
+    typename O::PZ b;
+    b.p = base.p;
+    b.q.z = base.q.z;
+    b.q.w = base.q.w;
+    c.binv = O::inverse_z(b);
+    c.bk = O::qz_from_yaw(O::qz_yaw(b.q) + T(1e-7)); // src/kinematics.cpp:187, 201-210
+    return c;
+  }
   static TFK_FN void store_base_ctx(const PlanHeader &h, const P &base, T *rec, int stride) {
+    if (!ANALYTIC_BASE && h.base_type == 1) {
+      const PlanerCtx c = planer_ctx(base);
+      P bi;
+      bi.p = c.binv.p;
+      bi.q = O::qz_dense(c.binv.q);
+      put_pose(rec, stride, h.off_base + 7, bi);
+      put_quat(rec, stride, h.off_base + 14 + 4 * 2, O::qz_dense(c.bk));
+      return;
+    }
     const V rpy_b = O::to_rpy(base.q);
     if (ANALYTIC_BASE) {
       V w[3];
@@ -228,6 +249,16 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     TFK_FN P binv() const { return get_pose(rec, stride, at + 7); }
     TFK_FN Q bk(int k) const { return get_quat(rec, stride, at + 14 + 4 * k); }
     TFK_FN V w(int k) const { return get_vec(rec, stride, at + 7 + 3 * k); }
+    TFK_FN PlanerCtx planer() const {
+      PlanerCtx c;
+      c.base_p = get_vec(rec, stride, at);
+      c.binv.p = get_vec(rec, stride, at + 7);
+      c.binv.q.z = rec[(at + 12) * STRIDE];
+      c.binv.q.w = rec[(at + 13) * STRIDE];
+      c.bk.z = rec[(at + 24) * STRIDE];
+      c.bk.w = rec[(at + 25) * STRIDE];
+      return c;
+    }
   };
   // fused: one link per configuration, so everything is computed where it is used; only the base pose
   // itself is re-read from the record (it exists only for a Jacobian with a moving base)
@@ -246,6 +277,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     TFK_FN P binv() const { return O::inverse(b); }
     TFK_FN Q bk(int k) const { return tweaked_rotation(rpy_b, k); }
     TFK_FN V w(int k) const { return (k == 0) ? wk[0] : ((k == 1) ? wk[1] : wk[2]); }
+    TFK_FN PlanerCtx planer() const { return planer_ctx(get_pose(rec, stride, 0)); }
   };
 
   // ---------------------------------------------------------------------------------------------
@@ -260,7 +292,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
                        int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
-    TFK_NOUNROLL
+    TFK_PLAN_LOOP
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
       if (sl.frame_ld != FRAME_RUNNING && (BASE_REC || sl.frame_ld != FRAME_BASE)) // a child of the root, or the
@@ -365,7 +397,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
 
     // joint columns, src/kinematics.cpp:131-180
     const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
-    TFK_NOUNROLL
+    TFK_PLAN_LOOP
     for (int c = 0; c < h.n_cols; ++c) {
       T v[7];
       v[0] = v[1] = v[2] = v[3] = v[4] = v[5] = v[6] = T(0);
@@ -407,7 +439,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     if (h.base_type == 0) return;
     // base translation columns, src/kinematics.cpp:194-196
     const int n_trans = (h.base_type == 1) ? 2 : 3;
-    TFK_NOUNROLL
+    TFK_PLAN_LOOP
     for (int k = 0; k < n_trans; ++k) {
       T v[7];
       v[0] = (k == 0) ? T(1) : T(0);
@@ -417,6 +449,10 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       out.put_J(h.n_cols + k, v);
     }
     // base rotation columns: FLOATING keeps roll, pitch, yaw; PLANER keeps yaw only
+    if (!ANALYTIC_BASE && h.base_type == 1) {
+      emit_planer_yaw(h, e, erpy, bs, out);
+      return;
+    }
     bs.prepare();
     const V base_p = bs.base_p();
     const int k0 = (h.base_type == 1) ? 2 : 0;
@@ -425,7 +461,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       d.x = e.p.x - base_p.x;
       d.y = e.p.y - base_p.y;
       d.z = e.p.z - base_p.z;
-      TFK_NOUNROLL
+      TFK_PLAN_LOOP
       for (int k = k0; k < 3; ++k) {
         T v[7];
         v[6] = T(0);
@@ -466,7 +502,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
         be.q = O::qidentity();
       }
     }
-    TFK_NOUNROLL
+    TFK_PLAN_LOOP
     for (int k = k0; k < 3; ++k) { // one copy of the code
       P bk;
       bk.p = base_p;
@@ -509,6 +545,56 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       }
       out.put_J(h.n_cols + n_trans + (k - k0), v);
     }
+  }
+
+  // The yaw column of a PLANER base: the forward finite difference of src/kinematics.cpp:182-232 with every base
+  // quantity yaw-only (fk_math.h), i.e. half of the products of the two pose_transforms, one atan2 instead of
+  // getRPY(base) and one sincos instead of three in setFromRPY(rpy_b + eps*e_z).
+  template <class BaseSrc, class OutSink>
+  static TFK_FN void emit_planer_yaw(const PlanHeader &h, const P &e, const V &erpy, BaseSrc &bs, OutSink &out) {
+    const PlanerCtx c = bs.planer();
+    V bep; // tf_blink_to_elink = pose_transform(tf_blink_to_rlink, tf_rlink_to_elink)
+    {
+      const V r = O::rotate_z(c.binv.q, e.p);
+      bep.x = r.x + c.binv.p.x;
+      bep.y = r.y + c.binv.p.y;
+      bep.z = r.z + c.binv.p.z;
+    }
+    V pk; // pose_out = pose_transform(tf_rlink_to_blink_tweaked, tf_blink_to_elink)
+    {
+      const V r = O::rotate_z(c.bk, bep);
+      pk.x = r.x + c.base_p.x;
+      pk.y = r.y + c.base_p.y;
+      pk.z = r.z + c.base_p.z;
+    }
+    T v[7];
+    v[0] = pk.x - e.p.x;
+    v[1] = pk.y - e.p.y;
+    v[2] = pk.z - e.p.z;
+    v[3] = v[4] = v[5] = v[6] = T(0);
+    if (LREC == 7) {
+      const Q qk = O::qmul_zb(c.bk, O::qmul_zb(c.binv.q, e.q));
+      if (ROT == 1) {
+        const V rk = O::to_rpy(qk);
+        v[3] = rk.x - erpy.x;
+        v[4] = rk.y - erpy.y;
+        v[5] = rk.z - erpy.z;
+      } else {
+        v[3] = qk.x - e.q.x;
+        v[4] = qk.y - e.q.y;
+        v[5] = qk.z - e.q.z;
+        v[6] = qk.w - e.q.w;
+      }
+    }
+    {
+      T num[D];
+      TFK_UNROLL
+      for (int r = 0; r < D; ++r) num[r] = v[r];
+      M::divn_(num, M::den_(T(1e-7)));
+      TFK_UNROLL
+      for (int r = 0; r < D; ++r) v[r] = num[r];
+    }
+    out.put_J(h.n_cols + 2, v);
   }
 
   // ---------------------------------------------------------------------------------------------

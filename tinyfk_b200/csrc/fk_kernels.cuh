@@ -164,6 +164,56 @@ __global__ void __launch_bounds__(TFK_TILE, BPS) fk_fused_kernel(const KernelArg
   }
 }
 
+#if defined(TFK_SPEC_PLAN)
+// Plan-specialised build of the fused kernel: the plan is the compile-time constant tfk::spec::k_* (generated by
+// plan.cpp:plan_to_source and compiled at run time, jit.cpp), the plan loops are fully unrolled and every test on a
+// plan field is folded, so what is left is the straight-line arithmetic of THIS robot/query.  Same source, same
+// compiler flags, same bits as the generic kernel.
+template <class Core, bool SMEM_REC, int BPS>
+__device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
+  typedef typename Core::T T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  PlanView pv;
+  pv.h = &spec::k_h;
+  pv.slots = spec::k_slots;
+  pv.cols = spec::k_cols;
+  pv.masks = spec::k_mask0;
+  pv.lrec_of_out = nullptr;
+  const PlanHeader &h = spec::k_h;
+  const SmemLayout L = smem_layout(0, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
+                    : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.fz_size;
+  rec += threadIdx.x;
+  const T *q = static_cast<const T *>(a.q);
+  const int warp = threadIdx.x >> 5;
+
+  StagedFactory<T, Core::D> fac;
+  fac.P = static_cast<T *>(a.P);
+  fac.J = static_cast<T *>(a.J);
+  fac.ldP = a.ld_cfg;
+  fac.stg = qs + warp * 32 * L.q_pitch;
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
+    __syncthreads();
+    int nvalid = nv - warp * 32;
+    nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
+    if (nvalid > 0) {
+      const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1;
+      fac.nvalid = nvalid;
+      fac.head0 = a.row0 + i0 + warp * 32;
+      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, fac);
+    }
+    __syncthreads();
+  }
+}
+#endif
+
 template <class Core>
 __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;

@@ -22,10 +22,16 @@
 #define TFK_FN __host__ __device__ __forceinline__
 // out-of-line on the device: called from several sites, each holding two or three independent libm
 // evaluations that the compiler interleaves (ILP) -- one copy keeps the instruction cache footprint small
+#if defined(TFK_SPEC_INLINE)
+#define TFK_FN_CALL __host__ __device__ __forceinline__
+#else
 #define TFK_FN_CALL __host__ __device__ __noinline__
+#endif
+#define TFK_FN_RARE __host__ __device__ __noinline__
 #else
 #define TFK_FN inline
 #define TFK_FN_CALL inline
+#define TFK_FN_RARE inline
 #endif
 #if defined(__CUDACC__)
 #define TFK_MATH_UNROLL _Pragma("unroll")
@@ -53,11 +59,20 @@ struct MathPortable {
   static TFK_FN double sin_(double x) { return tfk_sin(x); }
   static TFK_FN double cos_(double x) { return tfk_cos(x); }
   // fkmath_simt.h: bit-identical to fkmath.h's functions, restructured for warps
+#if defined(TFK_SPEC_SINCOS_CALL)
+  static __host__ __device__ __noinline__ TfkSinCos sincos_call_(double x) { return tfk_sincos_simt(x); }
+  static TFK_FN void sincos_(double x, double *s, double *c) {
+    const TfkSinCos r = sincos_call_(x);
+    *s = r.s;
+    *c = r.c;
+  }
+#else
   static TFK_FN void sincos_(double x, double *s, double *c) {
     const TfkSinCos r = tfk_sincos_simt(x);
     *s = r.s;
     *c = r.c;
   }
+#endif
   static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
   static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
   static TFK_FN double atan2_rare_(double y, double x) { return tfk_atan2(y, x); } // same bits, out of line
@@ -92,11 +107,13 @@ struct MathPortable {
 #endif
     return d;
   }
+  // the compiler's full IEEE division (its slow path is ~100 instructions): one copy, out of line
+  static TFK_FN_RARE double div_rare_(double a, double b) { return a / b; }
   static TFK_FN double div_(double a, const Den &d) {
     const uint32_t t = (uint32_t)tfk_hi32(a) & 0x7fffffffu;
-    if (!d.ok || (t - 0x27000000u) >= 0x32000000u) { // |a| outside [2^-399, 2^401): rare, or an exact zero
+    if (TFK_UNLIKELY(!d.ok || (t - 0x27000000u) >= 0x32000000u)) { // |a| outside [2^-399, 2^401): rare, or an exact zero
       if (d.ok && (t | (uint32_t)tfk_lo32(a)) == 0u) return a * d.y;
-      return a / d.b;
+      return div_rare_(a, d.b);
     }
 #if defined(__CUDA_ARCH__)
     double q = __dmul_rn(a, d.y);
@@ -118,7 +135,7 @@ struct MathPortable {
     uint32_t bad = d.ok ? 0u : 1u;
     TFK_MATH_UNROLL
     for (int i = 0; i < N; ++i) bad |= (((uint32_t)tfk_hi32(a[i]) & 0x7fffffffu) - 0x27000000u) >= 0x32000000u ? 1u : 0u;
-    if (bad) {
+    if (TFK_UNLIKELY(bad != 0u)) {
       TFK_MATH_UNROLL
       for (int i = 0; i < N; ++i) a[i] = div_(a[i], d);
       return;
@@ -230,7 +247,7 @@ template <class M> struct Ops {
   static TFK_FN Q qget_inverse(const Q &q) {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r = qidentity();
-    if (norm > T(0)) {
+    if (TFK_LIKELY(norm > T(0))) {
       T a[4] = {q.w, -q.x, -q.y, -q.z};
       M::divn_(a, M::den_(norm));
       r.w = a[0];
@@ -377,7 +394,7 @@ template <class M> struct Ops {
   // Rotation::normalize, pose.h:230-250
   static TFK_FN void qnormalize(Q &q) {
     T s = M::sqrt_(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-    if (s == T(0)) {
+    if (TFK_UNLIKELY(s == T(0))) {
       q = qidentity();
     } else {
       T a[4] = {q.x, q.y, q.z, q.w};
@@ -411,11 +428,11 @@ template <class M> struct Ops {
     T sarg = T(-2) * (q.x * q.z - q.w * q.y);
     const T pi_2 = T(1.57079632679489661923);
     V r;
-    if (sarg <= T(-0.99999)) {
+    if (TFK_UNLIKELY(sarg <= T(-0.99999))) {
       r.y = -pi_2;
       r.x = T(0);
       r.z = T(2) * M::atan2_rare_(q.x, -q.y);
-    } else if (sarg >= T(0.99999)) {
+    } else if (TFK_UNLIKELY(sarg >= T(0.99999))) {
       r.y = pi_2;
       r.x = T(0);
       r.z = T(2) * M::atan2_rare_(-q.x, q.y);
@@ -474,6 +491,100 @@ template <class M> struct Ops {
     n.y = a.p.y * T(-1);
     n.z = a.p.z * T(-1);
     o.p = rotate(o.q, n);
+    return o;
+  }
+
+  // ---- yaw-only rotations (PLANER base) ------------------------------------------------------------
+  // With base_type PLANER every base quantity is built from q = (+-0, +-0, z, w): setFromRPY(0, 0, yaw)
+  // (sin(0) = 0, cos(0) = 1 exactly), its inverse, and the yaw-tweaked rotation of the finite-difference
+  // column.  These are the reference's dense expressions (pose.h) with the products by those two exact
+  // zeros dropped -- the sparsity policy of fk_plan.h: only the sign of an exact zero can differ.
+  struct QZ {
+    T z, w;
+  };
+  struct PZ {
+    V p;
+    QZ q;
+  };
+  static TFK_FN Q qz_dense(const QZ &q) {
+    Q r;
+    r.x = T(0);
+    r.y = T(0);
+    r.z = q.z;
+    r.w = q.w;
+    return r;
+  }
+  // setFromRPY(0, 0, yaw) incl. normalize (pose.h:202-216, 230-250)
+  static TFK_FN QZ qz_from_yaw(T yaw) {
+    T s, c;
+    M::sincos_(yaw / T(2), &s, &c);
+    QZ q;
+    q.z = s;
+    q.w = c;
+    const T n = M::sqrt_(s * s + c * c); // x*x + y*y + z*z + w*w with x = y = 0
+    if (TFK_UNLIKELY(n == T(0))) {
+      q.z = T(0);
+      q.w = T(1);
+    } else {
+      T a[2] = {s, c};
+      M::divn_(a, M::den_(n));
+      q.z = a[0];
+      q.w = a[1];
+    }
+    return q;
+  }
+  // getRPY (pose.h:161-192) of a yaw-only rotation: roll = atan2(+-0, w^2 + z^2) = +-0, pitch = asin(+-0) = +-0
+  static TFK_FN T qz_yaw(const QZ &q) { return M::atan2_(T(2) * (q.w * q.z), q.w * q.w - q.z * q.z); }
+  // GetInverse (pose.h:284-299)
+  static TFK_FN QZ qz_get_inverse(const QZ &q) {
+    const T norm = q.w * q.w + q.z * q.z;
+    QZ r;
+    r.z = T(0);
+    r.w = T(1);
+    if (TFK_LIKELY(norm > T(0))) {
+      T a[2] = {q.w, -q.z};
+      M::divn_(a, M::den_(norm));
+      r.w = a[0];
+      r.z = a[1];
+    }
+    return r;
+  }
+  // a * b, a yaw-only (pose.h:253-263)
+  static TFK_FN Q qmul_zb(const QZ &a, const Q &b) {
+    Q c;
+    c.x = a.w * b.x - a.z * b.y;
+    c.y = a.w * b.y + a.z * b.x;
+    c.z = a.w * b.z + a.z * b.w;
+    c.w = a.w * b.w - a.z * b.z;
+    return c;
+  }
+  // Rotation * Vector3 (pose.h:265-282), q yaw-only
+  static TFK_FN V rotate_z(const QZ &q, const V &v) {
+    const QZ i = qz_get_inverse(q);
+    Q t;
+    t.x = v.x * i.w + v.y * i.z;
+    t.y = -(v.x * i.z) + v.y * i.w;
+    t.z = v.z * i.w;
+    t.w = -(v.z * i.z);
+    V r;
+    r.x = q.w * t.x - q.z * t.y;
+    r.y = q.w * t.y + q.z * t.x;
+    r.z = q.w * t.z + q.z * t.w;
+    return r;
+  }
+  // Pose::inverse (pose.h:329-339) of a yaw-only pose
+  static TFK_FN PZ inverse_z(const PZ &a) {
+    PZ o;
+    const T norm = a.q.w * a.q.w + a.q.z * a.q.z;
+    T qa[2] = {a.q.w, -a.q.z};
+    M::divn_(qa, M::den_(norm));
+    o.q.w = qa[0];
+    o.q.z = qa[1];
+    V n;
+    n.x = a.p.x * T(-1);
+    n.y = a.p.y * T(-1);
+    n.z = a.p.z * T(-1);
+    o.p = rotate_z(o.q, n);
     return o;
   }
 

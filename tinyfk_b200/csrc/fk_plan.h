@@ -30,7 +30,10 @@ namespace tfk {
 enum { SLOT_FIXED = 0, SLOT_REVOLUTE = 1, SLOT_PRISMATIC = 2 };
 enum { FRAME_RUNNING = -1, FRAME_BASE = -2 };
 enum { TFK_MAX_FRAMES = 64 };     // live branch-point frames per config, kept in the per-config records
-enum { TFK_TILE = 128 };          // configs per block tile == threads per block
+#ifndef TFK_TILE_CFG
+#define TFK_TILE_CFG 128
+#endif
+enum { TFK_TILE = TFK_TILE_CFG }; // configs per block tile == threads per block
 enum { TFK_BASE_REC = 26 };       // base pose 7 + inverse 7 + three tweaked rotations 3*4
 
 // how the slot's local rotation (parent link -> this link) arises

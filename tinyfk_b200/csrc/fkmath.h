@@ -30,6 +30,15 @@
 #include <stdint.h>
 #include <string.h>
 
+/* rare branches: keep the common path the fall-through one (taken branches cost instruction-fetch bubbles) */
+#if defined(__GNUC__) || defined(__CUDACC__)
+#define TFK_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#define TFK_LIKELY(x) __builtin_expect(!!(x), 1)
+#else
+#define TFK_UNLIKELY(x) (x)
+#define TFK_LIKELY(x) (x)
+#endif
+
 #if defined(__CUDACC__)
 #define TFK_HD __host__ __device__ inline
 /* out-of-line on the device: the kernels call these from a dozen sites and the instruction cache is

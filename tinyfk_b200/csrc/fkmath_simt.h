@@ -122,7 +122,7 @@ typedef struct {
 TFK_HD TfkSinCos tfk_sincos_simt(double x) {
   TfkSinCos out;
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
-  if (hx >= 0x41392000) { /* |x| >= ~1.64e6 (1647099.0 = 0x413921fb_00000000), inf, nan: rare */
+  if (TFK_UNLIKELY(hx >= 0x41392000)) { /* |x| >= ~1.64e6 (1647099.0 = 0x413921fb_00000000), inf, nan: rare */
     tfk_sincos(x, &out.s, &out.c);
     return out;
   }
@@ -137,7 +137,7 @@ TFK_HD TfkSinCos tfk_sincos_simt(double x) {
   if (!small) {
     const int j = (hx >> 20) & 0x7ff;
     int i = j - ((tfk_hi32(a0) >> 20) & 0x7ff);
-    if (i > 16) { /* cancellation near a multiple of pi/2: rare */
+    if (TFK_UNLIKELY(i > 16)) { /* cancellation near a multiple of pi/2: rare */
       double t2 = r;
       w = fn * TFK_PIO2_2;
       r = t2 - w;
@@ -185,8 +185,8 @@ TFK_HD double tfk_asin_pq_simt(double z, double *q) {
 /* bit-identical to tfk_asin (fkmath.h): one rational kernel + one division for both ranges */
 TFK_HD double tfk_asin_simt(double x) {
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
-  if (hx >= 0x3ff00000) return tfk_asin(x); /* |x| >= 1, nan: rare */
-  if (hx < 0x3e400000) return x;            /* |x| < 2^-27 */
+  if (TFK_UNLIKELY(hx >= 0x3ff00000)) return tfk_asin(x); /* |x| >= 1, nan: rare */
+  if (TFK_UNLIKELY(hx < 0x3e400000)) return x; /* |x| < 2^-27 */
   const double ax = fabs(x);
   const int big = hx >= 0x3fe00000; /* |x| >= 0.5 */
   const double t = (1.0 - ax) * 0.5;
@@ -257,7 +257,7 @@ TFK_HD double tfk_atan2_simt(double y, double x) {
      plain range -- the fkmath.h function handles them */
   const int special = (hx >= 0x7ff00000) | (hy >= 0x7ff00000) | ((hy | tfk_lo32(y)) == 0) | ((hx | tfk_lo32(x)) == 0) |
                       ((hxs == 0x3ff00000) & (tfk_lo32(x) == 0)) | (k > 60) | (k < -60);
-  if (special) return tfk_atan2(y, x);
+  if (TFK_UNLIKELY(special)) return tfk_atan2(y, x);
   const double a = fabs(y / x);
   const int32_t ha = tfk_hi32(a);
   double z = (ha < 0x3e200000) ? a : tfk_atan_pos_simt(a); /* |a| < 2^-29: atan(a) = a */

@@ -1,6 +1,9 @@
 // plan.cpp -- see plan.hpp / fk_plan.h.
 #include "plan.hpp"
 
+#include <cstdio>
+#include <initializer_list>
+
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -302,6 +305,71 @@ std::unique_ptr<PlanParams> make_plan_params(const std::vector<unsigned char> &b
   if (h->n_cols) std::memcpy(p->cols, blob.data() + h->off_cols, sizeof(PlanCol) * h->n_cols);
   if (h->n_out >= 1) std::memcpy(p->mask0, blob.data() + h->off_masks, sizeof(uint32_t) * (h->mask_words < 2 ? h->mask_words : 2));
   return p;
+}
+
+namespace {
+void put_real(std::string &o, double v) {
+  char b[64];
+  std::snprintf(b, sizeof b, "%a", v);
+  o += b;
+}
+template <int N> void put_reals(std::string &o, const double (&v)[N]) {
+  o += "{";
+  for (int i = 0; i < N; ++i) {
+    if (i) o += ", ";
+    put_real(o, v[i]);
+  }
+  o += "}";
+}
+void put_ints(std::string &o, std::initializer_list<int> v) {
+  for (int x : v) {
+    o += ", ";
+    o += std::to_string(x);
+  }
+}
+} // namespace
+
+std::string plan_to_source(const std::vector<unsigned char> &blob) {
+  const PlanHeader &h = *reinterpret_cast<const PlanHeader *>(blob.data());
+  const PlanSlot *slots = reinterpret_cast<const PlanSlot *>(blob.data() + h.off_slots);
+  const PlanCol *cols = reinterpret_cast<const PlanCol *>(blob.data() + h.off_cols);
+  const uint32_t *masks = reinterpret_cast<const uint32_t *>(blob.data() + h.off_masks);
+  if (h.n_out != 1 || h.mask_words > 2) throw std::invalid_argument("plan specialisation exists for one requested link only");
+  std::string o = "namespace tfk { namespace spec {\n";
+  // PlanHeader, in declaration order (fk_plan.h)
+  o += "static __device__ constexpr PlanHeader k_h = {" + std::to_string(h.n_slots);
+  put_ints(o, {h.n_out, h.n_cols, h.n_arec, h.n_prec, h.n_lrec, h.rot_type, h.base_type, h.pose_dim, h.with_jacobian, h.n_in,
+               h.n_out_cols, h.lrec_size, h.off_base, h.off_arec, h.off_prec, h.off_lrec, h.off_frame, h.rec_size, h.fz_arec,
+               h.fz_prec, h.fz_frame, h.fz_size, h.root_lrec, h.mask_words, h.off_slots, h.off_outs, h.off_masks, h.off_cols,
+               h.total_bytes, h.n_frames, h.pad_});
+  o += ", ";
+  put_reals(o, h.base_pose);
+  o += "};\n";
+  o += "static __device__ constexpr PlanSlot k_slots[" + std::to_string(std::max(h.n_slots, 1)) + "] = {\n";
+  for (int s = 0; s < h.n_slots; ++s) {
+    const PlanSlot &sl = slots[s];
+    o += "  {";
+    put_reals(o, sl.opos);
+    o += ", ";
+    put_reals(o, sl.oquat);
+    o += ", ";
+    put_reals(o, sl.axis);
+    o += ", ";
+    put_reals(o, sl.oinv);
+    put_ints(o, {sl.kind, sl.qcol, sl.frame_ld, sl.frame_st, sl.arec, sl.prec, sl.lrec, sl.rot, sl.trn, sl.axc, sl.flags, sl.pad_});
+    o += "},\n";
+  }
+  if (h.n_slots == 0) o += "  {}\n";
+  o += "};\n";
+  o += "static __device__ constexpr PlanCol k_cols[" + std::to_string(std::max(h.n_cols, 1)) + "] = {\n";
+  for (int c = 0; c < h.n_cols; ++c)
+    o += "  {" + std::to_string(cols[c].arec) + ", " + std::to_string(cols[c].prec) + ", " + std::to_string(cols[c].prismatic) + ", 0},\n";
+  if (h.n_cols == 0) o += "  {}\n";
+  o += "};\n";
+  o += "static __device__ constexpr uint32_t k_mask0[2] = {" + std::to_string(h.mask_words > 0 ? masks[0] : 0u) + "u, " +
+       std::to_string(h.mask_words > 1 ? masks[1] : 0u) + "u};\n";
+  o += "}} // namespace tfk::spec\n";
+  return o;
 }
 
 ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action) {

@@ -4,6 +4,7 @@
 
 #include <cstdint>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "fk_plan.h"
@@ -39,6 +40,11 @@ struct ComTables {
   double diag;       // d com / d base translation: ((sum m*1)/mass_total [+ sum f*1] [/ vfs])
 };
 ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action);
+
+// CUDA source of a plan as compile-time constants (namespace tfk::spec: k_h, k_slots[], k_cols[], k_mask0[]):
+// what the plan-specialised build of the fused kernel is compiled against (fk_kernels.cuh, TFK_SPEC_PLAN).
+// Reals are printed as hexadecimal floating literals: the constants are the blob's, bit for bit.
+std::string plan_to_source(const std::vector<unsigned char> &blob);
 
 inline int pose_dim_of(int rot_type) { return 3 + (rot_type == ROT_RPY) * 3 + (rot_type == ROT_XYZW) * 4; }
 inline int base_dof_of(int base_type) { return base_type == BASE_PLANER ? 3 : (base_type == BASE_FLOATING ? 6 : 0); }

@@ -30,6 +30,7 @@ src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-so
                      text=True).stdout
 cur_file = None
 agg = collections.Counter()
+smp = collections.Counter()
 opagg = collections.defaultdict(collections.Counter)
 ops = collections.Counter()
 text = {}
@@ -49,6 +50,10 @@ for r in csv.reader(io.StringIO(src)):
     except ValueError:
         continue
     agg[line] += e
+    try:
+        smp[line] += int(r[6])
+    except ValueError:
+        pass
     s = r[3].strip()
     if s.startswith("@"):
         s = s.split(None, 1)[1]
@@ -64,3 +69,13 @@ for (f, l), c in agg.items():
 print({k: round(v / W) for k, v in byfile.most_common()})
 for (f, l), c in agg.most_common(top):
     print("%-16s %4d %6.0f  %-64s %s" % (f, l, c / W, text[(f, l)][:64], dict((k, round(v / W)) for k, v in opagg[(f, l)].most_common(4))))
+
+# warp-stall samples per source line: where the warps' TIME goes (samples ~ warp-cycles), next to the instruction share
+ts = float(sum(smp.values())) or 1.0
+print("\nstall samples: %d; share of samples vs share of executed instructions, per file" % ts)
+sf = collections.Counter()
+for (f, l), c in smp.items():
+    sf[f] += c
+print({k: "%.1f%% / %.1f%%" % (100 * v / ts, 100.0 * byfile[k] / tot) for k, v in sf.most_common()})
+for (f, l), c in smp.most_common(top):
+    print("%-16s %4d %5.1f%% (instr %4.1f%%)  %-64s" % (f, l, 100 * c / ts, 100.0 * agg[(f, l)] / tot, text[(f, l)][:64]))
