@@ -157,6 +157,21 @@ TFK_API int tfk_solve_com_fk_device(tfk_model *m, int device, void *stream, cons
                                     const double *forces, int n_action, int base_type, int with_jacobian,
                                     int precision, void *d_com, void *d_J, int64_t ld_cfg, int64_t row0);
 
+/* ---- total inertia matrix ----------------------------------------- */
+/* KinematicsModelPyWrapper::compute_total_inertia_matrix (src/wrapper.cpp:181-187) over get_total_inertia_matrix
+ * (src/kinematics.cpp:272-317), batched: q is [n][n_joint] (the stored base pose applies), out is [n][3][3]:
+ *     sum over the links with an <inertial> of  R I R^T + m (|v|^2 Id - v v^T),   v = p_link - centre of mass.
+ * The reference evaluates the 3x3 products with Eigen, whose summation order is not pinned in this repository
+ * (no Eigen here): the contract for this entry is 1e-12 relative, not bit equality.  Every row is evaluated from its
+ * own configuration (the reference skips clear_cache() on this entry).  Current device; stored angles follow the
+ * last configuration. */
+TFK_API int tfk_total_inertia_matrix_host(tfk_model *m, const void *q, int64_t n, const int *joint_ids, int n_joint,
+                                          int precision, void *out);
+/* device-resident buffers: d_out[(3*i + j) * ld_cfg + row] (9, ld_cfg) component-major */
+TFK_API int tfk_total_inertia_matrix_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                            const int *joint_ids, int n_joint, int precision, void *d_out,
+                                            int64_t ld_cfg, int64_t row0);
+
 /* ---- helpers ---------------------------------------------------------------------------------- */
 TFK_API int tfk_device_count(int *count);
 /* pinned host memory for the host path (pooled; tfk_host_free returns the block to the pool) */

@@ -412,6 +412,32 @@ int tfkref_com(void *p, const double *qs, long n_wp, const int *joint_ids, int n
   }
 }
 
+/*
+ * compute_total_inertia_matrix (src/wrapper.cpp:181-187): _set_joint_angles + the reference's own
+ * get_total_inertia_matrix (src/kinematics.cpp:272-317), whose Eigen expressions run on oracle/eigen_stub (3x3 products
+ * summed k = 0, 1, 2 from 0.0; Eigen's own order is NOT pinned).  clear != 0 clears the transform cache first (the
+ * reference does not: see tfkref_com).  out: 9 doubles row-major per configuration.
+ */
+int tfkref_inertia(void *p, const double *qs, long n_wp, const int *joint_ids, int n_joint, int clear, double *out) {
+  try {
+    KinematicModel *kin = static_cast<Handle *>(p)->kin;
+    std::vector<size_t> jids(joint_ids, joint_ids + n_joint);
+    std::vector<double> q(n_joint);
+    for (long i = 0; i < n_wp; ++i) {
+      for (int k = 0; k < n_joint; ++k) q[k] = qs[(size_t)i * n_joint + k];
+      kin->_set_joint_angles(jids, q);
+      if (clear) kin->clear_cache();
+      const Eigen::Matrix3d m = kin->get_total_inertia_matrix();
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) out[(size_t)i * 9 + 3 * r + c] = m(r, c);
+    }
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
+  }
+}
+
 /* which libm is this object bound to?  (tests check the strict build really is pinned) */
 double tfkref_probe_sin(double x) {
   volatile double v = x;

@@ -100,6 +100,8 @@ def _load_ref(strict):
     lib.tfkref_com.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int, ctypes.c_int,
                                ctypes.c_int, ctypes.c_int, _dp, _dp]
     lib.tfkref_com.restype = ctypes.c_int
+    lib.tfkref_inertia.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, ctypes.c_int, _dp]
+    lib.tfkref_inertia.restype = ctypes.c_int
     lib.tfkref_probe_sin.argtypes = [ctypes.c_double]
     lib.tfkref_probe_sin.restype = ctypes.c_double
     lib.tfkref_probe_atan2.argtypes = [ctypes.c_double, ctypes.c_double]
@@ -264,6 +266,18 @@ class RefModel:
         if rc:
             raise ValueError(self._lib.tfkref_last_error().decode())
         return com, J
+
+    def total_inertia_matrix(self, qs, joint_ids, clear_each=True):
+        """compute_total_inertia_matrix (src/wrapper.cpp:181-187) per row of qs: (n, 3, 3)"""
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        jids = _as_int_array(joint_ids)
+        assert qs.shape[1] == jids.size
+        out = np.zeros((qs.shape[0], 3, 3))
+        rc = self._lib.tfkref_inertia(self._h, qs.ctypes.data_as(_dp), qs.shape[0], jids.ctypes.data_as(_ip), jids.size,
+                                      int(bool(clear_each)), out.ctypes.data_as(_dp))
+        if rc:
+            raise ValueError(self._lib.tfkref_last_error().decode())
+        return out
 
     def probe_sin(self, x):
         return self._lib.tfkref_probe_sin(float(x))

@@ -117,6 +117,22 @@ static void run_com(const std::vector<unsigned char> &blob, const ComTables &ct,
   }
 }
 
+// the inertia kernel's per-thread code on the CPU: out 9 doubles row-major per configuration
+template <class Core, class T>
+static void run_inertia(const std::vector<unsigned char> &blob, const InertiaTables &it, const double *qs, long n, double *out) {
+  PlanView pv = plan_view(blob.data());
+  const PlanHeader &h = *pv.h;
+  std::vector<T> rec((size_t)(h.rec_size > 0 ? h.rec_size : 1)), qrow((size_t)(h.n_in > 0 ? h.n_in : 1));
+  std::vector<T> w(it.w.begin(), it.w.end());
+  for (long i = 0; i < n; ++i) {
+    for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
+    Core::phase_a(pv, qrow.data(), rec.data(), 1);
+    T m[9];
+    Core::inertia_total(pv, rec.data(), w.data(), (int)it.links.size(), (T)it.mass_total, m);
+    for (int k = 0; k < 9; ++k) out[(size_t)i * 9 + k] = (double)m[k];
+  }
+}
+
 extern "C" {
 int emu_sqdists(void *m, const double *qs, long n, const int *l1, const int *l2, int n_check, const int *joints, int n_joint,
                 int base_type, int with_grads, int mode, double *sq, double *G) {
@@ -191,6 +207,29 @@ long emu_plan_source(void *m, const int *elinks, int n_link, const int *joints, 
   } catch (const std::exception &e) {
     g_err = e.what();
     return 0;
+  }
+}
+int emu_inertia(void *m, const double *qs, long n, const int *joints, int n_joint, int mode, double *out) {
+  try {
+    const KinematicModel &km = *static_cast<KinematicModel *>(m);
+    const InertiaTables it = build_inertia_tables(km);
+    PlanKey key;
+    key.elink_ids = it.links;
+    key.joint_ids.assign(joints, joints + n_joint);
+    key.rot_type = 2;
+    key.base_type = 0;
+    key.with_jacobian = 0;
+    key.model_version = km.version();
+    std::vector<unsigned char> blob = build_plan(km, key);
+    make_plan_params(blob);
+    if (mode == 1)
+      run_inertia<FkCore<MathNative32, true, 2, 1>, float>(blob, it, qs, n, out);
+    else
+      run_inertia<FkCore<MathPortable, false, 2, 1>, double>(blob, it, qs, n, out);
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return 1;
   }
 }
 // MathPortable::div_ (shared-reciprocal IEEE division, fk_math.h) on arrays: must equal a[i] / b[i]

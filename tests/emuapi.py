@@ -165,3 +165,15 @@ class EmuModel:
         if rc:
             raise ValueError(self._L.emu_last_error().decode())
         return com, (J if with_jacobian else None)
+
+    def total_inertia_matrix(self, qs, joint_ids, mode=MODE_STRICT64):
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))
+        j = _ints(joint_ids)
+        assert qs.shape[1] == j.size
+        out = np.zeros((qs.shape[0], 3, 3))
+        self._L.emu_inertia.argtypes = [ctypes.c_void_p, _dp, ctypes.c_long, _ip, ctypes.c_int, ctypes.c_int, _dp]
+        rc = self._L.emu_inertia(self._h, qs.ctypes.data_as(_dp), qs.shape[0], j.ctypes.data_as(_ip), j.size, int(mode),
+                                 out.ctypes.data_as(_dp))
+        if rc:
+            raise ValueError(self._L.emu_last_error().decode())
+        return out

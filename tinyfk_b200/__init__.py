@@ -163,8 +163,12 @@ class KinematicModel:
             qs, list(joint_ids), list(action_link_ids), [float(f) for f in action_forces], base_type.value,
             bool(with_jacobian), _PRECISION[precision])
 
-    def compute_total_inertia_matrix(self, *args, **kwargs):
-        raise NotImplementedError("compute_total_inertia_matrix is outside the accelerated FK path")
+    def compute_total_inertia_matrix(self, q, joint_ids, precision="fp64"):
+        """reference python/tinyfk/__init__.py:197-198: total inertia matrix about the centre of mass for one
+        configuration (3, 3); a 2-D `q` of several configurations returns (n, 3, 3).  The stored base pose applies."""
+        q = np.asarray(q)
+        out = self._robot.compute_total_inertia_matrix_batch(np.atleast_2d(q), list(joint_ids), _PRECISION[precision])
+        return out[0] if q.ndim == 1 else out
 
     def compute_inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=BaseType.FIXED, with_jacobian=False,
                                    use_cache=False, precision="fp64"):

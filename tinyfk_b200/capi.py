@@ -21,7 +21,7 @@ SYMBOLS = [
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
-    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
+    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
 ]
 
@@ -71,6 +71,8 @@ def lib():
                                         ctypes.c_int, _vp, _vp]
     L.tfk_solve_com_fk_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, _ip, _dp, ctypes.c_int,
                                           ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
+    L.tfk_total_inertia_matrix_host.argtypes = [_vp, _vp, _i64, _ip, ctypes.c_int, ctypes.c_int, _vp]
+    L.tfk_total_inertia_matrix_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, ctypes.c_int, _vp, _i64, _i64]
     L.tfk_device_count.argtypes = [_ip]
     L.tfk_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(_vp)]
     L.tfk_host_free.argtypes = [_vp]
@@ -292,6 +294,19 @@ class Model:
                                              int(precision), com.ctypes.data, J.ctypes.data if with_jacobian else None))
         return com, J
 
+    def total_inertia_matrix(self, qs, joint_ids, precision=0):
+        """Host buffers through tfk_total_inertia_matrix_host.  Returns (n, 3, 3)."""
+        dt = np.float32 if precision == 1 else np.float64
+        qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=dt)))
+        j = _ints(joint_ids)
+        n, n_in = qs.shape
+        if n_in != j.size:
+            raise ValueError("dof mismatch")
+        out = np.zeros((n, 3, 3), dtype=dt)
+        _check(self._L.tfk_total_inertia_matrix_host(self._h, qs.ctypes.data, n, j.ctypes.data_as(_ip), j.size, int(precision),
+                                                     out.ctypes.data))
+        return out
+
     def solve_com_fk_device(self, device, stream, d_q, n, joint_ids, action_link_ids, forces, base_type, with_jacobian,
                             precision, d_com, d_J, ld_cfg=None, row0=0):
         j, al = _ints(joint_ids), _ints(action_link_ids)
@@ -318,7 +333,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel"}.get(k, "none")
         return d
 
 

@@ -315,6 +315,28 @@ int tfk_solve_com_fk_device(tfk_model *m, int device, void *stream, const void *
   });
 }
 
+int tfk_total_inertia_matrix_host(tfk_model *m, const void *q, int64_t n, const int *joint_ids, int n_joint, int precision,
+                                  void *out) {
+  return guarded([&] {
+    need(m, "model");
+    if (n_joint < 0 || (n_joint > 0 && !joint_ids)) throw std::invalid_argument("bad joint id array");
+    ids_of(joint_ids, n_joint, m->engine.model.n_joints(), "joint");
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.inertia_host(q, n, joint_ids, n_joint, precision, out);
+  });
+}
+
+int tfk_total_inertia_matrix_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n, const int *joint_ids,
+                                    int n_joint, int precision, void *d_out, int64_t ld_cfg, int64_t row0) {
+  return guarded([&] {
+    need(m, "model");
+    if (n_joint < 0 || (n_joint > 0 && !joint_ids)) throw std::invalid_argument("bad joint id array");
+    ids_of(joint_ids, n_joint, m->engine.model.n_joints(), "joint");
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.inertia_device(device, static_cast<cudaStream_t>(stream), d_q, n, joint_ids, n_joint, precision, d_out, ld_cfg, row0);
+  });
+}
+
 int tfk_device_count(int *count) {
   return guarded([&] {
     need(count, "count");

@@ -203,7 +203,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
                     void *d_P, void *d_J, int64_t ld_cfg, int64_t row0, const LaunchExtra *ex) {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (n <= 0 || h->n_out == 0) return;
-  const bool sqdist = ex && ex->variant == KV_SQDIST, com = ex && ex->variant == KV_COM;
+  const bool sqdist = ex && ex->variant == KV_SQDIST, com = ex && (ex->variant == KV_COM || ex->variant == KV_INERTIA);
   const int n_pairs = sqdist ? ex->n_pairs : 0;
   if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
   const int rb = (int)real_size(precision);
@@ -220,8 +220,9 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     variant = KV_SQDIST;
   } else if (com) {
     rec_reals = h->rec_size;
-    L = smem_layout(table_bytes + (((ex->n_com + ex->n_act) * rb + 15) & ~15), h->n_in, 0, rb);
-    variant = KV_COM;
+    const int n_w = ex->variant == KV_INERTIA ? 7 * ex->n_com : ex->n_com + ex->n_act;
+    L = smem_layout(table_bytes + ((n_w * rb + 15) & ~15), h->n_in, 0, rb);
+    variant = ex->variant;
   } else if (h->n_out == 1) {
     rec_reals = h->fz_size;
     L = smem_layout(plan_bytes, h->n_in, rec_reals, rb);
@@ -494,6 +495,99 @@ void Engine::com_device(int device, cudaStream_t stream, const void *d_q, int64_
   ex.vfs = ct.vfs;
   ex.com_diag = ct.diag;
   launch(device, stream, e, cs.precision, d_q, n, d_com, cs.with_jacobian ? d_J : nullptr, ld_cfg, row0, &ex);
+}
+
+// ---- total inertia matrix (reference src/wrapper.cpp:181-187, src/kinematics.cpp:272-317) ---------------------
+void Engine::inertia_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const int *joint_ids, int n_joint,
+                            int precision, void *d_out, int64_t ld_cfg, int64_t row0) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (row0 < 0 || row0 + n > ld_cfg) throw std::invalid_argument("rows [row0, row0+n) exceed ld_cfg");
+  if (n_joint < 0) throw std::invalid_argument("negative id count");
+  const InertiaTables it = build_inertia_tables(model);
+  SolveSpec s;
+  s.elink_ids = it.links.data();
+  s.n_link = (int)it.links.size();
+  s.joint_ids = joint_ids;
+  s.n_joint = n_joint;
+  s.rot_type = ROT_XYZW; // the link rotations are needed (R I R^T)
+  s.base_type = BASE_FIXED;
+  s.with_jacobian = 0;
+  s.precision = precision;
+  PlanEntry &e = plan_for(s);
+  if (n == 0) return;
+  if (!d_q && n_joint > 0) throw std::invalid_argument("q is null");
+  if (!d_out) throw std::invalid_argument("out is null");
+  DeviceGuard g(device);
+  WeightBuf &wb = weight_bufs_[std::make_pair(device, stream)];
+  const std::vector<double> &w = it.w;
+  const size_t need = w.size() * real_size(precision);
+  if (wb.bytes < need) {
+    if (wb.d) {
+      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
+      cudaFree(wb.d);
+      wb.d = nullptr;
+      wb.bytes = 0;
+    }
+    ck(cudaMalloc(&wb.d, need), "cudaMalloc(weights)");
+    wb.bytes = need;
+    wb.host.clear();
+  }
+  if (wb.host != w || wb.precision != precision) {
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
+    std::vector<float> wf(w.begin(), w.end());
+    const void *src = precision == PREC_F32 ? static_cast<const void *>(wf.data()) : static_cast<const void *>(w.data());
+    ck(cudaMemcpyAsync(wb.d, src, need, cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(weights)");
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
+    wb.host = w;
+    wb.precision = precision;
+  }
+  LaunchExtra ex = LaunchExtra();
+  ex.variant = KV_INERTIA;
+  ex.d_weights = wb.d;
+  ex.n_com = (int)it.links.size();
+  ex.mass_total = it.mass_total;
+  launch(device, stream, e, precision, d_q, n, d_out, nullptr, ld_cfg, row0, &ex);
+}
+
+void Engine::inertia_host(const void *q, int64_t n, const int *joint_ids, int n_joint, int precision, void *out) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (n == 0) {
+    inertia_device(0, nullptr, nullptr, 0, joint_ids, n_joint, precision, nullptr, 0, 0);
+    return;
+  }
+  if (!q && n_joint > 0) throw std::invalid_argument("q is null");
+  if (!out) throw std::invalid_argument("out is null");
+  int cur = 0;
+  ck(cudaGetDevice(&cur), "cudaGetDevice (is a CUDA device present? there is no CPU fallback)");
+  HostPipe &pp = pipe(cur);
+  cudaStream_t st = pp.stream[0];
+  const size_t sz = real_size(precision), in_row = (size_t)n_joint * sz;
+  const int64_t chunk = 1 << 16;
+  const int64_t capn = std::min<int64_t>(chunk, n);
+  grow(&pp.dq[0], &pp.cap_q[0], std::max<size_t>((size_t)capn * in_row, 16), st);
+  grow(&pp.dP[0], &pp.cap_P[0], (size_t)capn * 9 * sz, st);
+  const char *qb = static_cast<const char *>(q);
+  std::vector<char> tmp;
+  for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+    const int64_t nc = std::min<int64_t>(chunk, n - r0);
+    if (in_row) ck(cudaMemcpyAsync(pp.dq[0], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(q)");
+    inertia_device(cur, st, pp.dq[0], nc, joint_ids, n_joint, precision, pp.dP[0], nc, 0);
+    tmp.resize((size_t)nc * 9 * sz);
+    ck(cudaMemcpyAsync(tmp.data(), pp.dP[0], tmp.size(), cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(inertia)");
+    ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    for (int64_t i = 0; i < nc; ++i)
+      for (int k = 0; k < 9; ++k)
+        std::memcpy(static_cast<char *>(out) + ((size_t)(r0 + i) * 9 + k) * sz, tmp.data() + ((size_t)k * nc + i) * sz, sz);
+  }
+  // the model is left at the LAST configuration (src/wrapper.cpp:185)
+  if (n_joint > 0) {
+    std::vector<size_t> ids(joint_ids, joint_ids + n_joint);
+    std::vector<double> last((size_t)n_joint);
+    for (int c = 0; c < n_joint; ++c)
+      last[c] = precision == PREC_F32 ? (double)reinterpret_cast<const float *>(qb)[(size_t)(n - 1) * n_joint + c]
+                                      : reinterpret_cast<const double *>(qb)[(size_t)(n - 1) * n_joint + c];
+    model.set_joint_angles(ids, last);
+  }
 }
 
 // Host buffers in, host buffers out, current device.  q rows are [joints | base]; a PLANER row (x, y, yaw) is padded

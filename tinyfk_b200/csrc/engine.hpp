@@ -73,6 +73,11 @@ public:
   void com_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const ComSpec &cs, void *d_com, void *d_J,
                   int64_t ld_cfg, int64_t row0);
   void com_host(const void *q, int64_t n, const ComSpec &cs, void *com, void *J);
+  // total inertia matrix about the centre of mass (reference src/wrapper.cpp:181-187, src/kinematics.cpp:272-317);
+  // q rows are the selected joints (stored base pose); device out (9, ld_cfg) component-major, host out (n, 3, 3)
+  void inertia_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const int *joint_ids, int n_joint,
+                      int precision, void *d_out, int64_t ld_cfg, int64_t row0);
+  void inertia_host(const void *q, int64_t n, const int *joint_ids, int n_joint, int precision, void *out);
   LaunchInfo last_launch;
 
 private:

@@ -821,6 +821,67 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   }
 
   // ---------------------------------------------------------------------------------------------
+  // get_total_inertia_matrix (src/kinematics.cpp:272-317) on the records of phase A (plan: the "_com" links in id
+  // order, RotationType XYZW so that the link rotations are recorded).  w: 7 reals per link (mass, ixx, ixy, ixz,
+  // iyy, iyz, izz).  out[3*i + j] = sum over links of (R I R^T + m (|v|^2 Id - v v^T))_ij, v = p_link - com.
+  // The Eigen 3x3 products of the reference are evaluated as (a0*b0 + a1*b1) + a2*b2 (Eigen's order is not
+  // pinned in this repo: oracle/eigen_stub).
+  static TFK_FN T dot3_(T a0, T b0, T a1, T b1, T a2, T b2) { return (a0 * b0 + a1 * b1) + a2 * b2; }
+  static TFK_FN void inertia_total(const PlanView &pv, const T *rec, const T *w, int n_com, T mass_total, T (&out)[9]) {
+    const PlanHeader &h = *pv.h;
+    V com; // get_com, src/kinematics.cpp:237-253
+    com.x = com.y = com.z = T(0);
+    TFK_NOUNROLL
+    for (int o = 0; o < n_com; ++o) {
+      const V p = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o] * LREC);
+      const T m = w[7 * o];
+      com.x = com.x + m * p.x;
+      com.y = com.y + m * p.y;
+      com.z = com.z + m * p.z;
+    }
+    {
+      T a[3] = {com.x, com.y, com.z};
+      M::divn_(a, M::den_(mass_total));
+      com.x = a[0], com.y = a[1], com.z = a[2];
+    }
+    TFK_UNROLL
+    for (int k = 0; k < 9; ++k) out[k] = T(0);
+    TFK_NOUNROLL
+    for (int o = 0; o < n_com; ++o) {
+      const int at = h.off_lrec + pv.lrec_of_out[o] * LREC;
+      const V p = get_vec(rec, STRIDE, at);
+      Q q = O::qidentity();
+      if (LREC == 7) q = get_quat(rec, STRIDE, at + 3);
+      const T *wl = w + 7 * o;
+      const T mass = wl[0];
+      const T I[3][3] = {{wl[1], wl[2], wl[3]}, {wl[2], wl[4], wl[5]}, {wl[3], wl[5], wl[6]}};
+      const T vx = p.x - com.x, vy = p.y - com.y, vz = p.z - com.z;
+      const T xy2 = T(2) * (q.x * q.y), xz2 = T(2) * (q.x * q.z), xw2 = T(2) * (q.x * q.w);
+      const T yz2 = T(2) * (q.y * q.z), yw2 = T(2) * (q.y * q.w), zw2 = T(2) * (q.z * q.w);
+      const T xx2 = T(2) * (q.x * q.x), yy2 = T(2) * (q.y * q.y), zz2 = T(2) * (q.z * q.z);
+      const T R[3][3] = {{T(1) - yy2 - zz2, xy2 - zw2, xz2 + yw2},
+                         {xy2 + zw2, T(1) - xx2 - zz2, yz2 - xw2},
+                         {xz2 - yw2, yz2 + xw2, T(1) - xx2 - yy2}};
+      T RI[3][3];
+      TFK_UNROLL
+      for (int i = 0; i < 3; ++i)
+        TFK_UNROLL
+        for (int j = 0; j < 3; ++j) RI[i][j] = dot3_(R[i][0], I[0][j], R[i][1], I[1][j], R[i][2], I[2][j]);
+      const T nrm = M::sqrt_((vx * vx + vy * vy) + vz * vz);
+      const T n2 = nrm * nrm;
+      const T v[3] = {vx, vy, vz};
+      TFK_UNROLL
+      for (int i = 0; i < 3; ++i)
+        TFK_UNROLL
+        for (int j = 0; j < 3; ++j) {
+          const T rirt = dot3_(RI[i][0], R[j][0], RI[i][1], R[j][1], RI[i][2], R[j][2]);
+          const T tt = mass * ((i == j ? n2 : T(0)) - v[i] * v[j]);
+          out[3 * i + j] = out[3 * i + j] + (rirt + tt);
+        }
+    }
+  }
+
+  // ---------------------------------------------------------------------------------------------
   // fused driver (n_out == 1): the requested link is the last slot of the pruned chain (or the root),
   // so walk() returns its pose and the same thread emits the outputs; records use the fz_* layout.
   // OutFactory::make() builds the output sink only once the walk is done (nothing of it stays live

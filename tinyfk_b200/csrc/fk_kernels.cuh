@@ -396,6 +396,50 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_com_kernel(const KernelArgs a,
   }
 }
 
+// ---- total inertia matrix (src/kinematics.cpp:272-317) ---------------------------------------------------------
+// Phase A over the "_com" links with their rotations recorded (RotationType XYZW plan), then the same thread
+// reduces its configuration: out (9, ld_cfg) component-major, out[(3*i + j)*ld + row].
+template <class Core>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_inertia_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+  typedef typename Core::T T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
+    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
+  const PlanHeader &h = pp.h;
+  const int tab = (a.table_bytes + 15) & ~15;
+  const int n_w = 7 * a.n_com;
+  T *w = reinterpret_cast<T *>(smem + tab);
+  for (int i = threadIdx.x; i < n_w; i += TFK_TILE) w[i] = static_cast<const T *>(a.weights)[i];
+  __syncthreads();
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
+  pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
+  const SmemLayout L = smem_layout(tab + ((n_w * (int)sizeof(T) + 15) & ~15), h.n_in, 0, (int)sizeof(T));
+  T *qs = reinterpret_cast<T *>(smem + L.q_off);
+  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  const T *q = static_cast<const T *>(a.q);
+  T *out = static_cast<T *>(a.P);
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
+    __syncthreads();
+    if ((int)threadIdx.x < nv) {
+      Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+      T m[9];
+      Core::inertia_total(pv, rec + threadIdx.x, w, a.n_com, (T)a.mass_total, m);
+      const long long row = a.row0 + i0 + threadIdx.x;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) __stcs(out + k * a.ld_cfg + row, m[k]);
+    }
+    __syncthreads();
+  }
+}
+
 // the pair kernel exists for RotationType IGNORE only (positions); other instantiations never reach it
 template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
   fk_sqdist_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
@@ -405,6 +449,17 @@ template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type o
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_sqdist_kernel<Core>, TFK_TILE, smem_bytes);
 }
 template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_sqdist(int, int *blocks_per_sm) {
+  *blocks_per_sm = 0;
+  return cudaSuccess;
+}
+template <class Core> typename std::enable_if<Core::D == 7, void>::type launch_inertia(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
+  fk_inertia_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+}
+template <class Core> typename std::enable_if<Core::D != 7, void>::type launch_inertia(const KernelArgs &, const PlanParams &, int, int, cudaStream_t) {}
+template <class Core> typename std::enable_if<Core::D == 7, cudaError_t>::type occupancy_inertia(int smem_bytes, int *blocks_per_sm) {
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_inertia_kernel<Core>, TFK_TILE, smem_bytes);
+}
+template <class Core> typename std::enable_if<Core::D != 7, cudaError_t>::type occupancy_inertia(int, int *blocks_per_sm) {
   *blocks_per_sm = 0;
   return cudaSuccess;
 }
@@ -432,6 +487,8 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
     launch_sqdist<Core>(a, pp, grid, smem_bytes, stream);
   else if (variant == KV_COM)
     launch_com<Core>(a, pp, grid, smem_bytes, stream);
+  else if (variant == KV_INERTIA)
+    launch_inertia<Core>(a, pp, grid, smem_bytes, stream);
   else
     fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
@@ -440,6 +497,7 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
 template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
   if (variant == KV_SQDIST) return occupancy_sqdist<Core>(smem_bytes, blocks_per_sm);
   if (variant == KV_COM) return occupancy_com<Core>(smem_bytes, blocks_per_sm);
+  if (variant == KV_INERTIA) return occupancy_inertia<Core>(smem_bytes, blocks_per_sm);
   const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>
                    : variant == KV_FUSED_SMEM ? (const void *)fk_fused_kernel<Core, true, 4>
                    : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false, 4>

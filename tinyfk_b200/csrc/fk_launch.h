@@ -21,6 +21,7 @@ enum KernelVariant {
   KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
   KV_SQDIST = 4,      // inter-link squared distances: phase A -> records -> one thread per (configuration, pair)
   KV_COM = 5,         // centre of mass (+ Jacobian): phase A -> records -> mass-weighted sums in link-id order
+  KV_INERTIA = 6,     // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };
@@ -37,6 +38,7 @@ struct KernelArgs {
   // KV_SQDIST only: P = sqdists [ld_cfg*n_pairs], J = grads column-major (ld_cfg*n_pairs) x n_dof (or null)
   const int *pairs;  // device: o1[n_pairs] then o2[n_pairs], indices into the plan's elink list
   int n_pairs;
+  // KV_INERTIA: P = out (9, ld_cfg); weights = 7 reals per com link (mass, ixx, ixy, ixz, iyy, iyz, izz); n_com, mass_total
   // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
   const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
   int n_com, n_act;

@@ -68,6 +68,7 @@ struct RawLink {
   bool has_inertial;
   Vec3<double> com;
   double mass;
+  double inertia[6]; // ixx ixy ixz iyy iyz izz
 };
 
 // urdf::parsePose (urdf_parser/src/pose.cpp:96-128): missing attributes leave zeros
@@ -88,6 +89,7 @@ RawLink parse_link(const xml::Element &e) {
   l.has_inertial = false;
   l.com.x = l.com.y = l.com.z = 0.0;
   l.mass = 0.0;
+  for (int i = 0; i < 6; ++i) l.inertia[i] = 0.0;
   if (const xml::Element *in = e.child("inertial")) {
     Vec3<double> rpy;
     parse_origin(in->child("origin"), l.com, rpy, "inertial origin");
@@ -100,7 +102,7 @@ RawLink parse_link(const xml::Element &e) {
     for (int i = 0; i < 6; ++i) {
       const std::string *a = it->attr(k[i]);
       if (!a) throw std::invalid_argument("urdf: inertia of link [" + l.name + "] misses " + k[i]);
-      (void)parse_double(*a, "inertia");
+      l.inertia[i] = parse_double(*a, "inertia");
     }
     l.has_inertial = true;
   }
@@ -218,6 +220,7 @@ KinematicModel::KinematicModel(const std::string &xml_text, HostLibm libm)
     l.origin.q = OpsP::qidentity();
     l.has_inertial = kv.second.has_inertial;
     l.mass = kv.second.mass;
+    for (int i = 0; i < 6; ++i) l.inertia[i] = kv.second.inertia[i];
     link_ids_[l.name] = (int)links_.size();
     links_.push_back(l);
     if (l.has_inertial) total_mass_ += l.mass; // src/tinyfk.cpp:38-44 (id order)
@@ -295,6 +298,7 @@ KinematicModel::KinematicModel(const std::string &xml_text, HostLibm libm)
     int id = add_link_pose(links_[i].name + "_com", i, p);
     links_[id].has_inertial = true;
     links_[id].mass = links_[i].mass;
+    for (int k = 0; k < 6; ++k) links_[id].inertia[k] = links_[i].inertia[k]; // the dummy link shares the parent's inertial
     com_links_.push_back(id);
   }
 }
@@ -427,6 +431,7 @@ int KinematicModel::add_link_pose(const std::string &name, size_t parent_id, con
   l.origin = pose;
   l.has_inertial = false;
   l.mass = 0.0;
+  for (int k = 0; k < 6; ++k) l.inertia[k] = 0.0;
   int id = (int)links_.size();
   link_ids_[name] = id;
   links_.push_back(l);

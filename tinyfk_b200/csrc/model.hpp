@@ -46,6 +46,7 @@ struct LinkRec {
   std::vector<int> children;
   bool has_inertial;
   double mass;
+  double inertia[6]; // ixx ixy ixz iyy iyz izz (urdf::Inertial, link.h:60-75)
 };
 
 struct JointRec {

@@ -372,6 +372,21 @@ std::string plan_to_source(const std::vector<unsigned char> &blob) {
   return o;
 }
 
+InertiaTables build_inertia_tables(const KinematicModel &model) {
+  InertiaTables t;
+  const std::vector<int> &cl = model.com_links();
+  if (cl.empty()) throw std::invalid_argument("the model has no link with an <inertial>: inertia matrix undefined");
+  t.links.assign(cl.begin(), cl.end());
+  t.mass_total = 0.0;
+  for (int id : cl) {
+    const LinkRec &l = model.links()[id];
+    t.w.push_back(l.mass);
+    for (int k = 0; k < 6; ++k) t.w.push_back(l.inertia[k]);
+    t.mass_total += l.mass;
+  }
+  return t;
+}
+
 ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action) {
   ComTables t;
   const std::vector<int> &cl = model.com_links();

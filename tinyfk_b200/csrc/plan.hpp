@@ -39,6 +39,13 @@ struct ComTables {
   double vfs;        // 1 + sum of forces/total_mass (wrapper.cpp:153-157)
   double diag;       // d com / d base translation: ((sum m*1)/mass_total [+ sum f*1] [/ vfs])
 };
+// get_total_inertia_matrix (src/kinematics.cpp:272-317): per "_com" link (mass, ixx, ixy, ixz, iyy, iyz, izz)
+struct InertiaTables {
+  std::vector<int> links;
+  std::vector<double> w; // 7 per link
+  double mass_total;
+};
+InertiaTables build_inertia_tables(const KinematicModel &model);
 ComTables build_com_tables(const KinematicModel &model, const int *action_link_ids, const double *forces, int n_action);
 
 // CUDA source of a plan as compile-time constants (namespace tfk::spec: k_h, k_slots[], k_cols[], k_mask0[]):

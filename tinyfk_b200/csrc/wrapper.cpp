@@ -4,7 +4,7 @@
 // reference; everything numerical happens behind tfk_solve_fk_host (CUDA, no CPU fallback).
 //
 // SURVEY.md section 8(f) rows built on the same path: compute_inter_link_squared_dists (rank 1),
-// solve_com_forward_kinematics (rank 2).  compute_total_inertia_matrix raises NotImplementedError.
+// solve_com_forward_kinematics (rank 2), compute_total_inertia_matrix (rank 4).
 #include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
@@ -195,6 +195,21 @@ public:
                      TFK_F64_STRICT);
   }
 
+  // compute_total_inertia_matrix (src/wrapper.cpp:181-187): one configuration -> 3x3; the batched form returns (n, 3, 3)
+  py::array inertia_batch(py::array qs_in, const std::vector<size_t> &joint_ids, int precision) {
+    std::vector<int> j = to_int(joint_ids);
+    if (precision == TFK_F32)
+      return run_inertia<float>(py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(qs_in), j, precision);
+    return run_inertia<double>(py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(qs_in), j, precision);
+  }
+  py::array compute_total_inertia_matrix(const std::vector<double> &q, const std::vector<size_t> &joint_ids) {
+    if (q.size() != joint_ids.size()) throw std::invalid_argument("q and joint_ids differ in length");
+    py::array_t<double> qa(std::vector<py::ssize_t>{1, (py::ssize_t)q.size()});
+    std::memcpy(qa.mutable_data(), q.data(), q.size() * sizeof(double));
+    py::array r = inertia_batch(qa, joint_ids, TFK_F64_STRICT);
+    return r.attr("reshape")(3, 3).cast<py::array>();
+  }
+
   int64_t kernel_launches() const { return tfk_kernel_launch_count(); }
 
 private:
@@ -292,6 +307,22 @@ private:
     return py::make_tuple(com, J);
   }
 
+  template <class T> py::array run_inertia(py::array_t<T, py::array::c_style | py::array::forcecast> qs, const std::vector<int> &j, int precision) {
+    if (!qs) throw std::invalid_argument("qs must be convertible to a 2-D float array");
+    if (qs.ndim() != 2) throw std::invalid_argument("qs must be 2-D (n_configs, n_joint)");
+    if ((size_t)qs.shape(1) != j.size())
+      throw std::invalid_argument("dof mismatch: expected " + std::to_string(j.size()) + " columns, got " + std::to_string(qs.shape(1)));
+    const size_t n = (size_t)qs.shape(0);
+    py::array_t<T> out(std::vector<py::ssize_t>{(py::ssize_t)n, 3, 3});
+    int rc;
+    {
+      py::gil_scoped_release nogil;
+      rc = tfk_total_inertia_matrix_host(m_, qs.data(), (int64_t)n, j.data(), (int)j.size(), precision, out.mutable_data());
+    }
+    check(rc);
+    return out;
+  }
+
   tfk_model *m_;
 };
 
@@ -326,7 +357,9 @@ PYBIND11_MODULE(_tinyfk, m) {
       .def("solve_com_forward_kinematics_batch", &RobotModel::com_batch, py::arg("qs"), py::arg("joint_ids"),
            py::arg("action_link_ids"), py::arg("forces"), py::arg("base_type"), py::arg("with_jacobian"),
            py::arg("precision") = (int)TFK_F64_STRICT)
-      .def("compute_total_inertia_matrix", [](RobotModel &, py::args, py::kwargs) { not_on_path("compute_total_inertia_matrix"); })
+      .def("compute_total_inertia_matrix", &RobotModel::compute_total_inertia_matrix)
+      .def("compute_total_inertia_matrix_batch", &RobotModel::inertia_batch, py::arg("qs"), py::arg("joint_ids"),
+           py::arg("precision") = (int)TFK_F64_STRICT)
       .def("get_joint_names", &RobotModel::get_joint_names)
       .def("get_joint_ids", &RobotModel::get_joint_ids)
       .def("get_joint_limits", &RobotModel::get_joint_limits)
