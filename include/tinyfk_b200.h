@@ -172,6 +172,27 @@ TFK_API int tfk_total_inertia_matrix_device(tfk_model *m, int device, void *stre
                                             const int *joint_ids, int n_joint, int precision, void *d_out,
                                             int64_t ld_cfg, int64_t row0);
 
+/* ---- plan specialisation ------------------------------------------------------------------------ */
+/* No reference equivalent.  A query signature (links, joints, rot_type, base_type, with_jacobian) that is evaluated
+ * over and over is a constant of the application: the single-link kernel can be compiled once more against THAT plan
+ * (NVRTC at run time, same source, same flags, same bits; cubins cached under TFK_CACHE_DIR, default
+ * ~/.cache/tinyfk_b200) and then runs ~1.25x faster.  Policy (tfk_set_jit_mode; env TFK_JIT=off|auto|on):
+ *   TFK_JIT_OFF   generic kernels only
+ *   TFK_JIT_AUTO  (default) a plan that has served TFK_JIT_THRESHOLD (default 2^22) configurations is compiled in a
+ *                 background thread; calls keep using the generic kernel until it is ready
+ *   TFK_JIT_ON    compile synchronously on a plan's first use
+ * tfk_specialize does it explicitly: flags TFK_SPEC_WAIT blocks until the kernel is compiled (and, unless
+ * TFK_SPEC_COMPILE_ONLY, loaded on the current device); TFK_SPEC_COMPILE_ONLY needs no GPU.  info (may be NULL)
+ * receives {state, threads per block, blocks per SM, shared memory bytes, cubin bytes, came from the disk cache};
+ * state: 1 compiling, 2 compiled, 3 ready.  TFK_ERR_INVALID: the plan is not eligible (several links, very long
+ * chain); TFK_ERR_RUNTIME: NVRTC not found or the compile failed (the generic kernel keeps serving the plan). */
+enum { TFK_JIT_OFF = 0, TFK_JIT_AUTO = 1, TFK_JIT_ON = 2 };
+enum { TFK_SPEC_WAIT = 1, TFK_SPEC_COMPILE_ONLY = 2 };
+TFK_API int tfk_specialize(tfk_model *m, const int *elink_ids, int n_link, const int *joint_ids, int n_joint,
+                           int rot_type, int base_type, int with_jacobian, int precision, int flags, int64_t *info);
+TFK_API int tfk_set_jit_mode(tfk_model *m, int mode);
+TFK_API int tfk_get_jit_mode(const tfk_model *m);
+
 /* ---- helpers ---------------------------------------------------------------------------------- */
 TFK_API int tfk_device_count(int *count);
 /* pinned host memory for the host path (pooled; tfk_host_free returns the block to the pool) */

@@ -1,0 +1,102 @@
+"""Plan specialisation (tinyfk_b200/csrc/jit.cpp): the fused kernel compiled at run time against one plan must be the
+generic kernel bit for bit.  The compile itself needs no GPU (NVRTC), so it is checked on the CPU too."""
+import os
+
+import numpy as np
+import pytest
+
+from tinyfk_b200 import capi
+from tinyfk_b200 import workloads as W
+
+CASES = [  # urdf, joints, link, rot, base, jac, precision
+    ("pr2.urdf", W.PR2_RARM, "r_gripper_tool_frame", 1, 1, True, 0),   # cfg2
+    ("kuka.urdf", W.KUKA_JOINTS, "lbr_iiwa_link_7", 2, 0, True, 0),    # cfg3
+    ("pr2.urdf", W.PR2_RARM, "r_gripper_tool_frame", 1, 2, True, 0),   # FLOATING: three finite-difference columns
+    ("fetch.urdf", W.FETCH_JOINTS, "gripper_link", 0, 1, True, 0),     # prismatic torso, IGNORE
+    ("pr2.urdf", W.PR2_RARM, "r_gripper_tool_frame", 2, 0, False, 0),  # pose only
+    ("pr2.urdf", W.PR2_RARM, "r_gripper_tool_frame", 1, 1, True, 1),   # FP32 mode
+]
+
+
+@pytest.fixture(autouse=True)
+def _cache(tmp_path, monkeypatch):
+    monkeypatch.setenv("TFK_CACHE_DIR", str(tmp_path / "cache"))
+
+
+def _have_nvrtc():
+    m = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0)
+    j, l = list(m.get_joint_ids(W.KUKA_JOINTS)), list(m.get_link_ids(["lbr_iiwa_link_7"]))
+    try:
+        m.specialize(l, j, 0, 0, False, 0, wait=True, compile_only=True)
+        return True
+    except RuntimeError:
+        return False
+
+
+needs_nvrtc = pytest.mark.skipif(not _have_nvrtc(), reason="NVRTC (libnvrtc.so.12) not found")
+
+
+@needs_nvrtc
+def test_specialisation_compiles_without_a_gpu_and_is_cached(tmp_path):
+    m = capi.Model(W.urdf_text("pr2.urdf"), host_libm=0)
+    j, l = list(m.get_joint_ids(W.PR2_RARM)), list(m.get_link_ids(["r_gripper_tool_frame"]))
+    a = m.specialize(l, j, 1, 1, True, 0, wait=True, compile_only=True)
+    assert a["state"] == 2 and a["block"] == 256 and a["blocks_per_sm"] == 2 and a["cubin_bytes"] > 10000 and a["from_cache"] == 0
+    assert any(f.endswith(".cubin") for f in os.listdir(os.environ["TFK_CACHE_DIR"]))
+    m2 = capi.Model(W.urdf_text("pr2.urdf"), host_libm=0)
+    b = m2.specialize(l, j, 1, 1, True, 0, wait=True, compile_only=True)
+    assert b["from_cache"] == 1 and b["cubin_bytes"] == a["cubin_bytes"]
+    # several links: not a plan the fused kernel serves
+    l2 = list(m.get_link_ids(["r_gripper_tool_frame", "r_elbow_flex_link"]))
+    with pytest.raises(ValueError):
+        m.specialize(l2, j, 1, 1, True, 0, wait=True, compile_only=True)
+
+
+@pytest.mark.gpu
+@needs_nvrtc
+@pytest.mark.parametrize("urdf,joints,link,rot,base,jac,prec", CASES)
+def test_gpu_specialised_kernel_is_the_generic_kernel_bit_for_bit(urdf, joints, link, rot, base, jac, prec):
+    m = capi.Model(W.urdf_text(urdf), host_libm=0)
+    j, l = list(m.get_joint_ids(joints)), list(m.get_link_ids([link]))
+    q = W.sample_q(m.get_joint_limits(j), base, 1000, seed=5, wide_pitch=True)  # ragged tail tile
+    m.set_jit_mode(0)
+    P0, J0 = m.solve_fk(q, l, j, rot, base, jac, precision=prec)
+    assert "spec" not in m.last_launch_info()["kernel"]
+    m.set_jit_mode(1)
+    info = m.specialize(l, j, rot, base, jac, prec, wait=True)
+    assert info["state"] == 3
+    P1, J1 = m.solve_fk(q, l, j, rot, base, jac, precision=prec)
+    li = m.last_launch_info()
+    assert li["kernel"].startswith("tfk_spec_kernel") and li["block"] == info["block"]
+    if prec == 0:  # strict FP64: no contraction, so constant folding cannot change a bit
+        assert np.array_equal(P0, P1)
+        if jac:
+            assert np.array_equal(J0, J1)
+    else:  # FP32 mode contracts multiply-adds; folding constants changes which ones -> the mode's own tolerance
+        assert np.abs(P0 - P1).max() < 1e-5
+        if jac:
+            assert np.abs(J0 - J1).max() < 1e-4
+
+
+@pytest.mark.gpu
+@needs_nvrtc
+def test_gpu_auto_mode_compiles_in_the_background_and_switches_over():
+    import time
+    m = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0)
+    j, l = list(m.get_joint_ids(W.KUKA_JOINTS)), list(m.get_link_ids(["lbr_iiwa_link_7"]))
+    assert m.get_jit_mode() == 1
+    q = W.sample_q(m.get_joint_limits(j), 0, 1 << 16, seed=1)
+    ref = None
+    kernels = []
+    t0 = time.time()
+    for it in range(4000):  # 2^22 configurations start the compile; it finishes within seconds
+        P, J = m.solve_fk(q, l, j, 2, 0, True)
+        k = m.last_launch_info()["kernel"]
+        if ref is None:
+            ref = (P.copy(), J.copy())
+        if not kernels or kernels[-1] != k:
+            kernels.append(k)
+            assert np.array_equal(P, ref[0]) and np.array_equal(J, ref[1])
+        if k.startswith("tfk_spec_kernel") or time.time() - t0 > 120:
+            break
+    assert len(kernels) == 2 and kernels[0].startswith("fk_fused_kernel") and kernels[1].startswith("tfk_spec_kernel"), kernels

@@ -21,7 +21,7 @@ SYMBOLS = [
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
-    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
+    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
 ]
 
@@ -73,6 +73,10 @@ def lib():
                                           ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
     L.tfk_total_inertia_matrix_host.argtypes = [_vp, _vp, _i64, _ip, ctypes.c_int, ctypes.c_int, _vp]
     L.tfk_total_inertia_matrix_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, ctypes.c_int, _vp, _i64, _i64]
+    L.tfk_specialize.argtypes = [_vp, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                 ctypes.c_int, ctypes.POINTER(ctypes.c_int64)]
+    L.tfk_set_jit_mode.argtypes = [_vp, ctypes.c_int]
+    L.tfk_get_jit_mode.argtypes = [_vp]
     L.tfk_device_count.argtypes = [_ip]
     L.tfk_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(_vp)]
     L.tfk_host_free.argtypes = [_vp]
@@ -275,6 +279,21 @@ class Model:
                                                      int(precision), _vp(d_sq), _vp(d_G) if d_G else None,
                                                      int(ld_cfg if ld_cfg is not None else n), int(row0)))
 
+    def specialize(self, elink_ids, joint_ids, rot_type, base_type, with_jacobian, precision=0, wait=True, compile_only=False):
+        """tfk_specialize: compile the single-link kernel against this query's plan.  Returns the info dict."""
+        l, j = _ints(elink_ids), _ints(joint_ids)
+        info = (ctypes.c_int64 * 6)()
+        _check(self._L.tfk_specialize(self._h, l.ctypes.data_as(_ip), l.size, j.ctypes.data_as(_ip), j.size, int(rot_type),
+                                      int(base_type), int(bool(with_jacobian)), int(precision),
+                                      (1 if wait else 0) | (2 if compile_only else 0), info))
+        return dict(zip(("state", "block", "blocks_per_sm", "smem_bytes", "cubin_bytes", "from_cache"), [int(x) for x in info]))
+
+    def set_jit_mode(self, mode):
+        _check(self._L.tfk_set_jit_mode(self._h, int(mode)))
+
+    def get_jit_mode(self):
+        return int(self._L.tfk_get_jit_mode(self._h))
+
     def solve_com_fk(self, qs, joint_ids, action_link_ids=(), forces=(), base_type=0, with_jacobian=False, precision=0):
         """Host buffers through tfk_solve_com_fk_host.  Returns (com (n, 3), J (3n, n_joint + 0|6) F-ordered or None)."""
         dt = np.float32 if precision == 1 else np.float64
@@ -333,7 +352,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)"}.get(k, "none")
         return d
 
 

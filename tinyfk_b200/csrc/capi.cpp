@@ -372,4 +372,32 @@ int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int *smem_by
 
 int tfk_last_launch_variant(const tfk_model *m) { return m ? m->engine.last_launch.variant : -1; }
 
+int tfk_specialize(tfk_model *m, const int *elink_ids, int n_link, const int *joint_ids, int n_joint, int rot_type,
+                   int base_type, int with_jacobian, int precision, int flags, int64_t *info) {
+  return guarded([&] {
+    need(m, "model");
+    SolveSpec s = make_spec(elink_ids, n_link, joint_ids, n_joint, rot_type, base_type, with_jacobian, precision);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    const SpecInfo si = m->engine.specialize(s, (flags & TFK_SPEC_WAIT) != 0, (flags & TFK_SPEC_COMPILE_ONLY) != 0);
+    if (info) {
+      info[0] = si.state;
+      info[1] = si.tile;
+      info[2] = si.blocks_per_sm;
+      info[3] = si.smem_bytes;
+      info[4] = si.cubin_bytes;
+      info[5] = si.from_cache;
+    }
+  });
+}
+
+int tfk_set_jit_mode(tfk_model *m, int mode) {
+  return guarded([&] {
+    need(m, "model");
+    if (mode < 0 || mode > 2) throw std::invalid_argument("jit mode must be 0 (off), 1 (auto) or 2 (on)");
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.jit_mode = mode;
+  });
+}
+int tfk_get_jit_mode(const tfk_model *m) { return m ? m->engine.jit_mode : -1; }
+
 } // extern "C"

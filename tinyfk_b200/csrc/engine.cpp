@@ -1,5 +1,6 @@
 // engine.cpp -- see engine.hpp.
 #include "engine.hpp"
+#include "jit.hpp"
 
 #include <algorithm>
 #include <atomic>
@@ -74,7 +75,200 @@ void pinned_free(void *p) {
 }
 
 // ---- engine -------------------------------------------------------------------------------------
-Engine::Engine(const std::string &xml, HostLibm libm) : model(xml, libm) { std::memset(&last_launch, 0, sizeof last_launch); }
+Engine::Engine(const std::string &xml, HostLibm libm) : model(xml, libm) {
+  std::memset(&last_launch, 0, sizeof last_launch);
+  jit_mode = JIT_AUTO;
+  jit_threshold = int64_t(1) << 22;
+  if (const char *m = std::getenv("TFK_JIT")) {
+    const std::string v(m);
+    if (v == "off" || v == "0") jit_mode = JIT_OFF;
+    if (v == "on" || v == "2") jit_mode = JIT_ON;
+  }
+  if (const char *t = std::getenv("TFK_JIT_THRESHOLD")) jit_threshold = std::atoll(t);
+}
+
+Engine::SpecKernel::~SpecKernel() {
+  if (worker.joinable()) worker.join();
+  if (lib) cudaLibraryUnload(lib);
+}
+
+// ---- plan specialisation (jit.hpp) -------------------------------------------------------------------------------
+bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const {
+  const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
+  if (h->n_out != 1) {
+    if (why) *why = "plan specialisation exists for one requested link (the fused kernel) only";
+    return false;
+  }
+  if (h->n_slots > 48 || h->n_cols > 32) {
+    if (why) *why = "chain too long to unroll (more than 48 links or 32 joints)";
+    return false;
+  }
+  const int rb = (int)real_size(precision);
+  // 256-thread blocks: the blocks of an SM walk the (long, straight-line) code closer together, which the
+  // instruction cache rewards; registers allow 512 (FP64) / 768 (FP32) resident threads
+  const int limit = 227 * 1024;
+  {
+    const SmemLayout L = smem_layout_tile(256, 0, h->n_in, h->fz_size, rb);
+    int b = precision == PREC_F32 ? 3 : 2;
+    while (b > 2 && b * (L.total + 1024) > limit) --b;
+    if (b * (L.total + 1024) <= limit) {
+      *tile = 256;
+      *bps = b;
+      *smem = L.total;
+      return true;
+    }
+  }
+  // larger records: 128-thread blocks, as many as fit (at least two)
+  const SmemLayout L = smem_layout_tile(128, 0, h->n_in, h->fz_size, rb);
+  int b = precision == PREC_F32 ? 6 : 4;
+  while (b > 2 && b * (L.total + 1024) > limit) --b;
+  if (b * (L.total + 1024) > limit) {
+    if (why) *why = "joint records do not fit in shared memory twice";
+    return false;
+  }
+  *tile = 128;
+  *bps = b;
+  *smem = L.total;
+  return true;
+}
+
+void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
+  SpecKernel &sk = e.spec[precision];
+  {
+    std::lock_guard<std::mutex> lk(sk.mu);
+    if (sk.state != SPEC_NONE) {
+      if (!(wait && sk.state == SPEC_COMPILING)) return;
+    } else {
+      std::string why;
+      if (!spec_eligible(e, precision, &sk.tile, &sk.bps, &sk.smem, &why)) throw std::invalid_argument(why);
+      if (!nvrtc_available(&why)) {
+        sk.state = SPEC_FAILED;
+        sk.error = why;
+        throw std::runtime_error(why);
+      }
+      sk.state = SPEC_COMPILING;
+      const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
+      SpecOptions o;
+      o.precision = precision;
+      o.rot_type = h->rot_type;
+      o.tile = sk.tile;
+      o.blocks_per_sm = sk.bps;
+      const std::string src = plan_to_source(e.blob);
+      SpecKernel *p = &sk; // heap-allocated with the plan entry; its destructor joins this thread
+      sk.worker = std::thread([p, src, o] {
+        std::vector<char> cubin;
+        std::string err;
+        bool cached = false;
+        try {
+          cubin = spec_compile(src, o, &cached);
+        } catch (const std::exception &ex) {
+          err = ex.what();
+        }
+        std::lock_guard<std::mutex> lk2(p->mu);
+        if (err.empty()) {
+          p->cubin.swap(cubin);
+          p->from_cache = cached;
+          p->state = SPEC_COMPILED;
+        } else {
+          p->error = err;
+          p->state = SPEC_FAILED;
+        }
+      });
+    }
+  }
+  if (wait && sk.worker.joinable()) sk.worker.join();
+}
+
+SpecInfo Engine::specialize(const SolveSpec &spec, bool wait, bool compile_only) {
+  if (spec.precision != PREC_F64_STRICT && spec.precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
+  PlanEntry &e = plan_for(spec);
+  SpecKernel &sk = e.spec[spec.precision];
+  spec_start(e, spec.precision, wait);
+  SpecInfo info;
+  {
+    std::lock_guard<std::mutex> lk(sk.mu);
+    if (sk.state == SPEC_FAILED) throw std::runtime_error(sk.error);
+    info.state = sk.state;
+    info.tile = sk.tile;
+    info.blocks_per_sm = sk.bps;
+    info.smem_bytes = sk.smem;
+    info.cubin_bytes = (int64_t)sk.cubin.size();
+    info.from_cache = sk.from_cache ? 1 : 0;
+  }
+  if (!compile_only && info.state == SPEC_COMPILED) { // load now so that the first launch does not pay for it
+    int cur = 0;
+    ck(cudaGetDevice(&cur), "cudaGetDevice (is a CUDA device present?)");
+    std::lock_guard<std::mutex> lk(sk.mu);
+    if (sk.state == SPEC_COMPILED) {
+      ck(cudaLibraryLoadData(&sk.lib, sk.cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0), "cudaLibraryLoadData(specialised kernel)");
+      ck(cudaLibraryGetKernel(&sk.kernel, sk.lib, "tfk_spec_kernel"), "cudaLibraryGetKernel");
+      sk.state = SPEC_READY;
+    }
+    info.state = sk.state;
+  }
+  return info;
+}
+
+// Launches the specialised kernel if there is one; otherwise advances the JIT policy and returns false (the caller
+// launches the generic kernel).
+bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const KernelArgs &a) {
+  SpecKernel &sk = e.spec[precision];
+  int state;
+  {
+    std::lock_guard<std::mutex> lk(sk.mu);
+    state = sk.state;
+  }
+  if (state == SPEC_NONE) {
+    if (jit_mode == JIT_AUTO) {
+      e.configs_served += a.n;
+      if (e.configs_served < jit_threshold) return false;
+    }
+    try {
+      spec_start(e, precision, jit_mode == JIT_ON);
+    } catch (const std::exception &ex) { // not eligible / no NVRTC: remember, keep serving with the generic kernel
+      std::lock_guard<std::mutex> lk(sk.mu);
+      sk.state = SPEC_FAILED;
+      sk.error = ex.what();
+      return false;
+    }
+    std::lock_guard<std::mutex> lk(sk.mu);
+    state = sk.state;
+  }
+  if (state == SPEC_COMPILED) {
+    std::lock_guard<std::mutex> lk(sk.mu);
+    if (cudaLibraryLoadData(&sk.lib, sk.cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0) != cudaSuccess ||
+        cudaLibraryGetKernel(&sk.kernel, sk.lib, "tfk_spec_kernel") != cudaSuccess) {
+      cudaGetLastError();
+      sk.state = SPEC_FAILED;
+      sk.error = "loading the specialised kernel failed";
+      return false;
+    }
+    sk.state = state = SPEC_READY;
+  }
+  if (state != SPEC_READY) return false;
+  auto it = sk.blocks_per_sm.find(device);
+  if (it == sk.blocks_per_sm.end()) {
+    const void *fn = reinterpret_cast<const void *>(sk.kernel);
+    if (sk.smem > 48 * 1024) ck(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, sk.smem), "cudaFuncSetAttribute(specialised kernel)");
+    int b = 0;
+    ck(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, fn, sk.tile, sk.smem), "occupancy query (specialised kernel)");
+    if (b < 1) throw CudaError("specialised kernel does not fit on an SM");
+    it = sk.blocks_per_sm.insert(std::make_pair(device, b)).first;
+  }
+  const int64_t n_tiles = (a.n + sk.tile - 1) / sk.tile;
+  const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
+  KernelArgs args = a;
+  void *params[] = {&args};
+  ck(cudaLaunchKernel(reinterpret_cast<const void *>(sk.kernel), dim3(grid), dim3(sk.tile), params, (size_t)sk.smem, stream), "launch (specialised kernel)");
+  g_launches.fetch_add(1);
+  last_launch.grid = grid;
+  last_launch.block = sk.tile;
+  last_launch.smem_bytes = sk.smem;
+  last_launch.blocks_per_sm = it->second;
+  last_launch.rec_reals = reinterpret_cast<const PlanHeader *>(e.blob.data())->fz_size;
+  last_launch.variant = KV_FUSED_SPEC;
+  return true;
+}
 
 Engine::~Engine() { release_device_memory(); }
 
@@ -237,6 +431,16 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     rec_reals = h->rec_size;
     L = smem_layout(plan_bytes, h->n_in, 0, rb);
     variant = KV_TWOPHASE;
+  }
+  if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5) && jit_mode != JIT_OFF) {
+    KernelArgs sa = KernelArgs();
+    sa.q = d_q;
+    sa.n = n;
+    sa.row0 = row0;
+    sa.ld_cfg = ld_cfg;
+    sa.P = d_P;
+    sa.J = d_J;
+    if (spec_launch(device, stream, e, precision, sa)) return;
   }
   const int smem = L.total;
   if (smem > 200 * 1024) throw std::invalid_argument("plan too large for shared memory");

@@ -12,6 +12,7 @@
 #include <memory>
 #include <mutex>
 #include <stdexcept>
+#include <thread>
 #include <string>
 #include <tuple>
 #include <utility>
@@ -52,6 +53,20 @@ struct ComSpec { // solve_com_forward_kinematics (reference src/wrapper.cpp:126-
   int base_type, with_jacobian, precision; // base_type: FIXED or FLOATING on the device entry (PLANER: host entry pads)
 };
 
+enum JitMode {
+  JIT_OFF = 0,  // generic kernels only
+  JIT_AUTO = 1, // a single-link plan that has served TFK_JIT_THRESHOLD configurations is specialised in the background
+  JIT_ON = 2,   // specialise synchronously on first use (first call pays the compile, a few seconds)
+};
+
+struct SpecInfo { // what Engine::specialize reports
+  int state;      // SPEC_*
+  int tile, blocks_per_sm, smem_bytes;
+  int64_t cubin_bytes;
+  int from_cache;
+};
+enum { SPEC_NONE = 0, SPEC_COMPILING = 1, SPEC_COMPILED = 2, SPEC_READY = 3, SPEC_FAILED = 4 };
+
 struct LaunchInfo {
   int grid, block, smem_bytes, blocks_per_sm, rec_reals, variant;
 };
@@ -77,16 +92,40 @@ public:
   // q rows are the selected joints (stored base pose); device out (9, ld_cfg) component-major, host out (n, 3, 3)
   void inertia_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const int *joint_ids, int n_joint,
                       int precision, void *d_out, int64_t ld_cfg, int64_t row0);
+  // Plan specialisation (jit.hpp).  wait: block until the kernel is compiled; compile_only: never touch a device.
+  // Throws std::invalid_argument when the plan is not eligible (several links, records beyond shared memory, very
+  // long chains) and std::runtime_error when NVRTC is missing or the compile fails.
+  SpecInfo specialize(const SolveSpec &spec, bool wait, bool compile_only);
+  int jit_mode;
+  int64_t jit_threshold;
   void inertia_host(const void *q, int64_t n, const int *joint_ids, int n_joint, int precision, void *out);
   LaunchInfo last_launch;
 
 private:
+  struct SpecKernel { // one per (plan, precision)
+    std::mutex mu;     // guards state / cubin / error against the compile thread
+    int state = SPEC_NONE;
+    std::string error;
+    std::vector<char> cubin;
+    bool from_cache = false;
+    std::thread worker;
+    int tile = 0, bps = 0, smem = 0;
+    cudaLibrary_t lib = nullptr;
+    cudaKernel_t kernel = nullptr;
+    std::map<int, int> blocks_per_sm; // device -> occupancy (also marks the shared-memory attribute as set there)
+    ~SpecKernel();
+  };
   struct PlanEntry {
     PlanKey key;
     std::vector<unsigned char> blob;
     std::unique_ptr<PlanParams> params; // the kernel-parameter form of the blob (fk_plan.h)
     std::map<int, unsigned char *> on_device; // device ordinal -> uploaded copy
+    SpecKernel spec[2];                       // by precision
+    int64_t configs_served = 0;
   };
+  bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const;
+  void spec_start(PlanEntry &e, int precision, bool wait);
+  bool spec_launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const KernelArgs &a);
   struct Workspace { // one per (device, stream): concurrent launches never share records
     void *scratch;
     size_t scratch_bytes;

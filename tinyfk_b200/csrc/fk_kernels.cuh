@@ -26,9 +26,11 @@
 #ifndef TFK_FK_KERNELS_CUH
 #define TFK_FK_KERNELS_CUH
 
+#if !defined(__CUDACC_RTC__)
 #include <cuda_runtime.h>
 
 #include <type_traits>
+#endif
 
 #include "fk_core.h"
 #include "fk_launch.h"
@@ -440,6 +442,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_inertia_kernel(const KernelArg
   }
 }
 
+#if !defined(__CUDACC_RTC__) // host-side launch helpers (not part of a run-time compiled translation unit)
 // the pair kernel exists for RotationType IGNORE only (positions); other instantiations never reach it
 template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
   fk_sqdist_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
@@ -520,6 +523,8 @@ template <class M, bool ANALYTIC_BASE> cudaError_t occupancy_fk(int rot_type, in
   if (rot_type == 1) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 1, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
   return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 2, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
 }
+
+#endif // !__CUDACC_RTC__
 
 } // namespace tfk
 #endif

@@ -4,7 +4,9 @@
 #ifndef TFK_FK_LAUNCH_H
 #define TFK_FK_LAUNCH_H
 
+#if !defined(__CUDACC_RTC__)
 #include <cuda_runtime.h>
+#endif
 
 #include "fk_plan.h"
 
@@ -21,7 +23,9 @@ enum KernelVariant {
   KV_TWOPHASE = 2,   // several links: phase A -> records in global scratch -> phase B
   KV_SQDIST = 4,      // inter-link squared distances: phase A -> records -> one thread per (configuration, pair)
   KV_COM = 5,         // centre of mass (+ Jacobian): phase A -> records -> mass-weighted sums in link-id order
-  KV_INERTIA = 6,     // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
+  KV_INERTIA = 6,
+  KV_FUSED_SPEC = 7,  // plan-specialised build of the fused kernel, compiled at run time (jit.cpp)
+     // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };
@@ -57,22 +61,27 @@ struct SmemLayout {
 // q tile pitch: odd (conflict-free 64-bit reads at one row per thread) and >= 7 so that a warp's own 32
 // rows can double as its staging strip (32 x pose_dim reals) once the angles have been consumed
 TFK_HDI int q_pitch_of(int n_in) { return (n_in < 7 ? 7 : n_in) | 1; }
-TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
+TFK_HDI SmemLayout smem_layout_tile(int tile, int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
   SmemLayout L;
   L.plan_bytes = (table_bytes + 15) & ~15;
   L.q_pitch = q_pitch_of(n_in);
   L.q_off = L.plan_bytes;
-  L.rec_off = L.q_off + ((TFK_TILE * L.q_pitch * real_bytes + 15) & ~15);
-  L.total = L.rec_off + rec_reals_in_smem * TFK_TILE * real_bytes;
+  L.rec_off = L.q_off + ((tile * L.q_pitch * real_bytes + 15) & ~15);
+  L.total = L.rec_off + rec_reals_in_smem * tile * real_bytes;
   return L;
 }
+TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
+  return smem_layout_tile(TFK_TILE, table_bytes, n_in, rec_reals_in_smem, real_bytes);
+}
 
+#if !defined(__CUDACC_RTC__)
 cudaError_t launch_fk_f64_strict(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
                                  cudaStream_t stream);
 cudaError_t occupancy_fk_f64_strict(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
 cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
                           cudaStream_t stream);
 cudaError_t occupancy_fk_f32(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
+#endif
 
 } // namespace tfk
 #endif

@@ -23,7 +23,14 @@
 #ifndef TFK_FK_PLAN_H
 #define TFK_FK_PLAN_H
 
+#if defined(__CUDACC_RTC__)
+typedef signed int int32_t;
+typedef unsigned int uint32_t;
+typedef long long int64_t;
+typedef unsigned long long uint64_t;
+#else
 #include <stdint.h>
+#endif
 
 namespace tfk {
 

@@ -26,9 +26,16 @@
 #ifndef TFK_FKMATH_H
 #define TFK_FKMATH_H
 
+#if defined(__CUDACC_RTC__) /* run-time compilation (jit.cpp): no libc headers, the CUDA built-ins are implicit */
+typedef signed int int32_t;
+typedef unsigned int uint32_t;
+typedef long long int64_t;
+typedef unsigned long long uint64_t;
+#else
 #include <math.h>
 #include <stdint.h>
 #include <string.h>
+#endif
 
 /* rare branches: keep the common path the fall-through one (taken branches cost instruction-fetch bubbles) */
 #if defined(__GNUC__) || defined(__CUDACC__)

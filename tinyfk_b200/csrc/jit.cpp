@@ -1,0 +1,189 @@
+// jit.cpp -- see jit.hpp
+#include "jit.hpp"
+
+#include <dlfcn.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <mutex>
+#include <stdexcept>
+
+#include "fk_launch.h"
+#include "jit_headers.inc" // build/: k_jit_header_names / k_jit_header_sources / k_jit_n_headers
+
+namespace tfk {
+namespace {
+
+// ---- NVRTC through dlopen -----------------------------------------------------------------------------------
+typedef struct _nvrtcProgram *nvrtcProgram;
+struct Nvrtc {
+  void *so = nullptr;
+  std::string error;
+  int (*Version)(int *, int *) = nullptr;
+  int (*CreateProgram)(nvrtcProgram *, const char *, const char *, int, const char *const *, const char *const *) = nullptr;
+  int (*DestroyProgram)(nvrtcProgram *) = nullptr;
+  int (*CompileProgram)(nvrtcProgram, int, const char *const *) = nullptr;
+  int (*GetCUBINSize)(nvrtcProgram, size_t *) = nullptr;
+  int (*GetCUBIN)(nvrtcProgram, char *) = nullptr;
+  int (*GetProgramLogSize)(nvrtcProgram, size_t *) = nullptr;
+  int (*GetProgramLog)(nvrtcProgram, char *) = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+  int major = 0, minor = 0;
+};
+
+template <class F> bool sym(void *so, const char *name, F &f) {
+  f = reinterpret_cast<F>(dlsym(so, name));
+  return f != nullptr;
+}
+
+Nvrtc &nvrtc() {
+  static Nvrtc n;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    std::vector<std::string> names;
+    if (const char *p = std::getenv("TFK_NVRTC")) names.push_back(p);
+    names.push_back("libnvrtc.so.12");
+    names.push_back("/usr/local/cuda/lib64/libnvrtc.so.12");
+    if (const char *h = std::getenv("CUDA_HOME")) names.push_back(std::string(h) + "/lib64/libnvrtc.so.12");
+    names.push_back("libnvrtc.so");
+    names.push_back("libnvrtc.so.13");
+    for (const std::string &s : names) {
+      n.so = dlopen(s.c_str(), RTLD_NOW | RTLD_LOCAL);
+      if (n.so) break;
+    }
+    if (!n.so) {
+      n.error = "NVRTC not found (libnvrtc.so.12; set TFK_NVRTC to its path)";
+      return;
+    }
+    const bool ok = sym(n.so, "nvrtcVersion", n.Version) && sym(n.so, "nvrtcCreateProgram", n.CreateProgram) &&
+                    sym(n.so, "nvrtcDestroyProgram", n.DestroyProgram) && sym(n.so, "nvrtcCompileProgram", n.CompileProgram) &&
+                    sym(n.so, "nvrtcGetCUBINSize", n.GetCUBINSize) && sym(n.so, "nvrtcGetCUBIN", n.GetCUBIN) &&
+                    sym(n.so, "nvrtcGetProgramLogSize", n.GetProgramLogSize) && sym(n.so, "nvrtcGetProgramLog", n.GetProgramLog) &&
+                    sym(n.so, "nvrtcGetErrorString", n.GetErrorString);
+    if (!ok) {
+      n.error = "NVRTC library lacks a required entry point";
+      dlclose(n.so);
+      n.so = nullptr;
+      return;
+    }
+    n.Version(&n.major, &n.minor);
+  });
+  return n;
+}
+
+// ---- disk cache ------------------------------------------------------------------------------------------------
+uint64_t fnv1a(const std::string &s, uint64_t h = 1469598103934665603ull) {
+  for (unsigned char c : s) {
+    h ^= c;
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+std::string cache_dir() {
+  if (const char *d = std::getenv("TFK_CACHE_DIR")) return *d ? std::string(d) : std::string();
+  if (const char *h = std::getenv("HOME")) return std::string(h) + "/.cache/tinyfk_b200";
+  return std::string();
+}
+
+void mkdirs(const std::string &p) {
+  for (size_t i = 1; i <= p.size(); ++i)
+    if (i == p.size() || p[i] == '/') mkdir(p.substr(0, i).c_str(), 0755);
+}
+
+std::vector<std::string> compile_options(const SpecOptions &o) {
+  std::vector<std::string> v;
+  v.push_back("--gpu-architecture=sm_100a");
+  v.push_back("--std=c++17");
+  v.push_back("--generate-line-info");
+  if (o.precision == PREC_F64_STRICT) v.push_back("--fmad=false"); // as fk_kernels_strict.cu: no FMA contraction
+  return v;
+}
+
+} // namespace
+
+bool nvrtc_available(std::string *why) {
+  Nvrtc &n = nvrtc();
+  if (!n.so && why) *why = n.error;
+  return n.so != nullptr;
+}
+
+std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
+  if (o.tile != 128 && o.tile != 256) throw std::invalid_argument("tile must be 128 or 256");
+  if (o.rot_type < 0 || o.rot_type > 2) throw std::invalid_argument("bad rot_type");
+  const bool f32 = o.precision == PREC_F32;
+  std::string s;
+  s += "#define TFK_SPEC_PLAN 1\n#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n";
+  s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
+  s += "#include \"fk_plan.h\"\n";
+  s += plan_source;
+  s += "#include \"fk_kernels.cuh\"\n";
+  s += "extern \"C\" __global__ void __launch_bounds__(tfk::TFK_TILE, " + std::to_string(o.blocks_per_sm) +
+       ") tfk_spec_kernel(const tfk::KernelArgs a) {\n";
+  s += std::string("  tfk::fk_fused_spec_body<tfk::FkCore<") + (f32 ? "tfk::MathNative32, true, " : "tfk::MathPortable, false, ") +
+       std::to_string(o.rot_type) + ", tfk::TFK_TILE>, true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
+  return s;
+}
+
+std::vector<char> spec_compile(const std::string &plan_source, const SpecOptions &o, bool *from_cache) {
+  if (from_cache) *from_cache = false;
+  Nvrtc &n = nvrtc();
+  if (!n.so) throw std::runtime_error(n.error);
+  const std::string src = spec_source(plan_source, o);
+  const std::vector<std::string> opts = compile_options(o);
+  // cache key: everything that determines the cubin
+  uint64_t key = fnv1a(src);
+  for (const std::string &x : opts) key = fnv1a(x, key);
+  for (int i = 0; i < k_jit_n_headers; ++i) key = fnv1a(k_jit_header_sources[i], key);
+  key = fnv1a("nvrtc " + std::to_string(n.major) + "." + std::to_string(n.minor), key);
+  char name[64];
+  std::snprintf(name, sizeof name, "/spec_%016llx.cubin", (unsigned long long)key);
+  const std::string dir = cache_dir();
+  if (!dir.empty()) {
+    std::ifstream f(dir + name, std::ios::binary);
+    if (f) {
+      std::vector<char> cubin((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+      if (cubin.size() > 64) {
+        if (from_cache) *from_cache = true;
+        return cubin;
+      }
+    }
+  }
+  nvrtcProgram prog = nullptr;
+  int rc = n.CreateProgram(&prog, src.c_str(), "tfk_spec.cu", k_jit_n_headers, k_jit_header_sources, k_jit_header_names);
+  if (rc != 0) throw std::runtime_error(std::string("nvrtcCreateProgram: ") + n.GetErrorString(rc));
+  std::vector<const char *> copts;
+  for (const std::string &x : opts) copts.push_back(x.c_str());
+  rc = n.CompileProgram(prog, (int)copts.size(), copts.data());
+  if (rc != 0) {
+    size_t ls = 0;
+    n.GetProgramLogSize(prog, &ls);
+    std::string log(ls, '\0');
+    if (ls) n.GetProgramLog(prog, &log[0]);
+    n.DestroyProgram(&prog);
+    throw std::runtime_error(std::string("plan specialisation failed to compile (") + n.GetErrorString(rc) + "):\n" + log);
+  }
+  size_t cs = 0;
+  rc = n.GetCUBINSize(prog, &cs);
+  std::vector<char> cubin(cs);
+  if (rc == 0 && cs) rc = n.GetCUBIN(prog, cubin.data());
+  n.DestroyProgram(&prog);
+  if (rc != 0 || cs == 0) throw std::runtime_error("NVRTC produced no cubin");
+  if (!dir.empty()) { // best effort; written through a temporary so that concurrent processes never see a partial file
+    mkdirs(dir);
+    const std::string tmp = dir + name + "." + std::to_string((long)getpid()) + ".tmp";
+    std::ofstream f(tmp, std::ios::binary);
+    if (f) {
+      f.write(cubin.data(), (std::streamsize)cubin.size());
+      f.close();
+      if (!f || std::rename(tmp.c_str(), (dir + name).c_str()) != 0) std::remove(tmp.c_str());
+    }
+  }
+  return cubin;
+}
+
+} // namespace tfk

@@ -210,6 +210,30 @@ public:
     return r.attr("reshape")(3, 3).cast<py::array>();
   }
 
+  // tfk_specialize: compile the single-link kernel against this query's plan (include/tinyfk_b200.h)
+  py::dict specialize(const std::vector<size_t> &elink_ids, const std::vector<size_t> &joint_ids, int rot_type, int base_type,
+                      bool with_jacobian, int precision, bool wait, bool compile_only) {
+    std::vector<int> l = to_int(elink_ids), j = to_int(joint_ids);
+    int64_t info[6] = {0, 0, 0, 0, 0, 0};
+    int rc;
+    {
+      py::gil_scoped_release nogil;
+      rc = tfk_specialize(m_, l.data(), (int)l.size(), j.data(), (int)j.size(), rot_type, base_type, with_jacobian ? 1 : 0, precision,
+                          (wait ? TFK_SPEC_WAIT : 0) | (compile_only ? TFK_SPEC_COMPILE_ONLY : 0), info);
+    }
+    check(rc);
+    py::dict d;
+    d["state"] = info[0];
+    d["block"] = info[1];
+    d["blocks_per_sm"] = info[2];
+    d["smem_bytes"] = info[3];
+    d["cubin_bytes"] = info[4];
+    d["from_cache"] = info[5];
+    return d;
+  }
+  void set_jit_mode(int mode) { check(tfk_set_jit_mode(m_, mode)); }
+  int get_jit_mode() const { return tfk_get_jit_mode(m_); }
+
   int64_t kernel_launches() const { return tfk_kernel_launch_count(); }
 
 private:
@@ -326,12 +350,6 @@ private:
   tfk_model *m_;
 };
 
-[[noreturn]] void not_on_path(const char *what) {
-  PyErr_SetString(PyExc_NotImplementedError,
-                  (std::string(what) + " is outside the accelerated FK path (see DESIGN.md, 'out of scope')").c_str());
-  throw py::error_already_set();
-}
-
 } // namespace
 
 PYBIND11_MODULE(_tinyfk, m) {
@@ -372,6 +390,11 @@ PYBIND11_MODULE(_tinyfk, m) {
       .def("compute_inter_link_squared_dists_batch", &RobotModel::sqdists_batch, py::arg("qs"), py::arg("link_ids1"),
            py::arg("link_ids2"), py::arg("joint_ids"), py::arg("base_type"), py::arg("with_grads"),
            py::arg("precision") = (int)TFK_F64_STRICT)
+      .def("specialize", &RobotModel::specialize, py::arg("elink_ids"), py::arg("joint_ids"), py::arg("rot_type"),
+           py::arg("base_type"), py::arg("with_jacobian"), py::arg("precision") = (int)TFK_F64_STRICT, py::arg("wait") = true,
+           py::arg("compile_only") = false)
+      .def("set_jit_mode", &RobotModel::set_jit_mode)
+      .def("get_jit_mode", &RobotModel::get_jit_mode)
       .def("is_relevant", &RobotModel::is_relevant)
       .def("kernel_launches", &RobotModel::kernel_launches)
       .def("clear_cache", &RobotModel::clear_cache);
