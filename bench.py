@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--precision", default="fp64", choices=["fp64", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--jit", default="on", choices=["on", "off"],
+                    help="on: specialise the single-link kernel on the workload's plan before the warm-up "
+                         "(tfk_specialize, part of model set-up); off: generic kernel")
     return ap.parse_args()
 
 
@@ -246,6 +249,21 @@ def run_ours(args):
     d_J = torch.empty((n_in, n * L * pd), dtype=t_dt, device=dev)
     stream = torch.cuda.current_stream()
 
+    # plan specialisation (include/tinyfk_b200.h, tfk_specialize): set-up work like creating the model, outside
+    # every timed region; the same call is made on the e2e arm's model below
+    jit_note = "off"
+    model.set_jit_mode(0)
+    if args.jit == "on":
+        try:
+            t0 = time.perf_counter()
+            si = model.specialize(lids, jids, rot, base, True, prec, wait=True)
+            model.set_jit_mode(1)
+            jit_note = "specialised on the plan in %.1f s%s" % (time.perf_counter() - t0, " (disk cache)" if si["from_cache"] else "")
+        except ValueError as e:  # several links: served by the two-phase kernel
+            jit_note = "not applicable: %s" % e
+        except RuntimeError as e:  # NVRTC missing: the generic kernel serves the plan
+            jit_note = "unavailable: %s" % str(e).splitlines()[0]
+
     def step(i):
         model.solve_fk_device(local_rank, stream.cuda_stream, d_q[i % n_rot].data_ptr(), n, lids, jids, rot, base,
                               True, prec, d_P.data_ptr(), d_J.data_ptr(), n, 0)
@@ -283,6 +301,10 @@ def run_ours(args):
 
         robot = _tinyfk.RobotModel(W.urdf_text(W.CONFIGS[cfg][0]))
         W.setup(_FacadeShim(robot), cfg)
+        robot.set_jit_mode(0)
+        if args.jit == "on" and jit_note.startswith("specialised"):
+            robot.specialize(lids, jids, rot, base, True, prec, True, False)
+            robot.set_jit_mode(1)
         ne = min(n, max(4096, int(3e9 // max(bytes_per_cfg, 1))))  # bound host memory: <= ~3 GB of output
         pin_q = capi.PinnedArray((ne, n_in), dtype=np_dt, order="C")
         pin_q.array[...] = host_q[0][:ne]
@@ -321,7 +343,7 @@ def run_ours(args):
                              % (n_rot, n_rot * n * n_in * rb / 1e6, n * L * pd * rb * (1 + n_in) / 1e6),
                        "mode": "strict FP64: reference operation order, portable libm, no FMA contraction" if not prec
                                else "FP32 opt-in mode",
-                       "launch": info},
+                       "jit": jit_note, "launch": info},
             "clocks": clk, "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES.get((cfg, args.precision)),
