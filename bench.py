@@ -153,45 +153,67 @@ def run_reference_arm(args):
 
 # ---- clocks ----------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi sampled every 200 ms DURING the timed region (B200_PROFILING.md recipe)."""
-
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region (the quantities of the B200_PROFILING.md
+    `nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.*` line, read through NVML)."""
 
     def __init__(self, gpu_index):
-        self.p = None
+        """NVML from a host thread, one sample per millisecond while the timed region runs (the region is a few
+        milliseconds long: an `nvidia-smi -lms` child would miss it), plus one forced sample while the GPU is busy."""
+        self.samples, self.h, self.nv, self.t, self.on = [], None, None, None, False
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms",
-                                       "200", "-i", str(gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
-                                      text=True)
-        except OSError:
-            self.p = None
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        except Exception:
+            self.h = None
+
+    def sample(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        try:
+            sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            smax = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            try:
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            self.samples.append((float(sm), float(smax), int(r)))
+        except Exception:
+            pass
+
+    def start(self):
+        import threading
+        self.on = True
+
+        def loop():
+            while self.on:
+                self.sample()
+                time.sleep(0.001)
+        self.t = threading.Thread(target=loop, daemon=True)
+        self.t.start()
 
     def stop(self):
-        if self.p is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.p.terminate()
-        try:
-            out, _ = self.p.communicate(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.p.kill()
-            out, _ = self.p.communicate()
-        sm, smax, reasons = [], [], set()
-        for line in out.strip().splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1]))
-                smax.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+        self.on = False
+        if self.t is not None:
+            self.t.join()
+        if self.h is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["NVML unavailable"], "samples": 0}
+        sm = [x[0] for x in self.samples]
+        smax = [x[1] for x in self.samples]
+        bits = 0
+        for x in self.samples:
+            bits |= x[2]
+        # nvml.h: SwPowerCap 0x4, HwSlowdown 0x8, SwThermalSlowdown 0x20, HwThermalSlowdown 0x40
+        names = [("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(n for n, b in names if bits & b), "samples": len(sm)}
 
 
 def measured_peaks():
@@ -208,7 +230,7 @@ def measured_peaks():
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from the committed
 # `ncu --set full` capture (profiles/), keyed by workload; None until a capture exists
 NCU_TRAFFIC_BYTES = {
-    ("cfg2", "fp64"): 577.5e6,  # profiles/r1_full_cfg2_strict_v5.txt: 84.0 MB read + 493.5 MB written (algorithmic 637.5 MB)
+    ("cfg2", "fp64"): 577.6e6,  # profiles/r1_full_cfg2_strict_v8.txt: 84.0 MB read + 493.7 MB written (algorithmic 637.5 MB)
 }
 
 
@@ -279,11 +301,16 @@ def run_ours(args):
     barrier()
     launches0 = capi.kernel_launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    if clocks is not None:
+        clocks.start()
     ev[0].record(stream)
     for i in range(args.steps):
         step(i)
         ev[i + 1].record(stream)
+    if clocks is not None:
+        clocks.sample()  # the launches above are asynchronous: the GPU is inside the timed region now
     barrier()
+    clk = clocks.stop() if clocks is not None else None
     launches = capi.kernel_launch_count() - launches0
     total_ms = ev[0].elapsed_time(ev[-1])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
@@ -327,7 +354,6 @@ def run_ours(args):
                "configs_per_step_per_gpu": int(ne), "steps": k_e2e,
                "api": "_tinyfk.RobotModel.solve_forward_kinematics_batch (numpy in, pinned numpy out)"}
         del P, J
-    clk = clocks.stop() if clocks is not None else None
 
     if rank == 0:
         peak, peak_src = measured_peaks()

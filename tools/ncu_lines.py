@@ -60,6 +60,20 @@ for r in csv.reader(io.StringIO(src)):
     op = s.split()[0].split(".")[0]
     opagg[line][op] += e
     ops[op] += e
+# kernels compiled at run time carry only file names (embedded headers): take the text from the source tree
+import os
+_src_cache = {}
+def _text(f, l):
+    t = text.get((f, l), "")
+    if t and "Unable to open" not in t:
+        return t
+    if f not in _src_cache:
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tinyfk_b200", "csrc", f)
+        _src_cache[f] = open(path).read().splitlines() if os.path.exists(path) else []
+    lines = _src_cache[f]
+    return lines[l - 1].strip() if 0 < l <= len(lines) else t
+for k in list(text):
+    text[k] = _text(*k)
 tot = sum(agg.values())
 print("\nexecuted warp instructions per 32 configs: %.0f" % (tot / W))
 print(" ".join("%s=%.0f" % (k, v / W) for k, v in ops.most_common(24)))
