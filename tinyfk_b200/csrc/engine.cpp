@@ -431,6 +431,13 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     rec_reals = h->rec_size;
     L = smem_layout(plan_bytes, h->n_in, 0, rb);
     variant = KV_TWOPHASE;
+    // the records every (configuration, link) item re-reads go to shared memory when three blocks still fit on an SM
+    const SmemLayout Lh = smem_layout(plan_bytes, h->n_in, h->off_frame, rb);
+    if (3 * (Lh.total + 1024) <= 227 * 1024) {
+      L = Lh;
+      variant = KV_TWOPHASE_SMEM;
+      rec_reals = h->rec_size - h->off_frame;
+    }
   }
   if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5) && jit_mode != JIT_OFF) {
     KernelArgs sa = KernelArgs();
@@ -462,7 +469,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const int grid = (int)std::min<int64_t>(n_tiles, resident);
   KernelArgs a;
   a.scratch = nullptr;
-  if (variant != KV_FUSED_SMEM) {
+  if (variant != KV_FUSED_SMEM && variant != KV_FUSED_SMEM5) {
     const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(rec_reals, 1) * real_size(precision);
     a.scratch = workspace(device, stream, rec_bytes).scratch;
   }

@@ -288,7 +288,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   // BASE_REC = false (fused driver): no base record; the only child of the root that is walked is slot 0,
   // whose parent frame is the initial `cur`.
   template <bool BASE_REC, class LinkSink>
-  static TFK_FN P walk(const PlanView &pv, const T *qrow, T *rec, int stride, int o_base, int o_arec, int o_prec,
+  static TFK_FN P walk(const PlanView &pv, const T *qrow, T *rec, T *rec_f, int stride, int o_base, int o_arec, int o_prec,
                        int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
@@ -296,7 +296,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
       if (sl.frame_ld != FRAME_RUNNING && (BASE_REC || sl.frame_ld != FRAME_BASE)) // a child of the root, or the
-        cur = get_pose(rec, stride, sl.frame_ld == FRAME_BASE ? o_base : o_frame + 7 * sl.frame_ld); // 2nd.. child of a branch point
+        cur = (sl.frame_ld == FRAME_BASE) ? get_pose(rec, stride, o_base) : get_pose(rec_f, stride, o_frame + 7 * sl.frame_ld); // 2nd.. child of a branch point
       // pose_transform(parent, local), pose.cpp:139-146: position first (it uses the parent's rotation)
       T ang = T(0);
       if (sl.kind != SLOT_FIXED) ang = qrow[sl.qcol];
@@ -346,7 +346,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
             cur.q = O::qmul(cur.q, O::qmul_axis(oq, sl.axc, ax, sn, cs));
         }
       }
-      if (sl.frame_st >= 0) put_pose(rec, stride, o_frame + 7 * sl.frame_st, cur);
+      if (sl.frame_st >= 0) put_pose(rec_f, stride, o_frame + 7 * sl.frame_st, cur);
       if (sl.arec >= 0) { // src/kinematics.cpp:143-147: axis of the joint in the root frame
         if (sl.flags & SF_INV_AFTER) inv = O::qget_inverse(cur.q);
         V ax;
@@ -609,27 +609,34 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       if (LREC == 7) put_quat(rec, stride, at + 3, cur.q);
     }
   };
-  static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) {
+  // rec: [base | arec | prec] of this configuration; rec_link: where its frames and link records go (the same array,
+  // or a second one biased so that the absolute offsets h.off_lrec + .. still apply: fk_twophase_kernel)
+  static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) { phase_a(pv, qrow, rec, rec, stride); }
+  static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, T *rec_link, int stride) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
     put_pose(rec, stride, h.off_base, base);
     if (h.off_arec - h.off_base > 7) store_base_ctx(h, base, rec, stride); // Jacobian with a moving base
     StoreLinks sink;
     sink.h = &h;
-    sink.rec = rec;
+    sink.rec = rec_link;
     sink.stride = stride;
     if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
-    walk<true>(pv, qrow, rec, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
+    walk<true>(pv, qrow, rec, rec_link, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
   }
 
   // two-phase driver, phase B: one thread per (configuration, requested link)
   template <class OutSink> static TFK_FN void phase_b(const PlanView &pv, const T *rec, int stride, int o, OutSink &out) {
+    phase_b(pv, rec, rec, stride, o, out);
+  }
+  template <class OutSink>
+  static TFK_FN void phase_b(const PlanView &pv, const T *rec, const T *rec_link, int stride, int o, OutSink &out) {
     const PlanHeader &h = *pv.h;
     const int lat = h.off_lrec + pv.lrec_of_out[o] * LREC;
     P e;
-    e.p = get_vec(rec, stride, lat);
+    e.p = get_vec(rec_link, stride, lat);
     e.q = O::qidentity();
-    if (LREC == 7) e.q = get_quat(rec, stride, lat + 3);
+    if (LREC == 7) e.q = get_quat(rec_link, stride, lat + 3);
     BaseFromRec bs;
     bs.rec = rec;
     bs.stride = stride;
@@ -894,7 +901,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
     if (h.fz_arec > 0) put_pose(rec, stride, 0, base); // Jacobian with a moving base: re-read for the base columns
-    const P e = walk<false>(pv, qrow, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
+    const P e = walk<false>(pv, qrow, rec, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
     BaseComputed bs;
     bs.rec = rec;
     bs.stride = stride;

@@ -216,7 +216,9 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
 }
 #endif
 
-template <class Core>
+// SMEM_HOT: [base | arec | prec] (what every (configuration, link) item re-reads) live in shared memory and only the
+// branch-point frames and the link records go through the block-private scratch; otherwise all records do.
+template <class Core, bool SMEM_HOT>
 __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
@@ -231,9 +233,13 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   pv.cols = pp.cols;
   pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
   pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
-  const SmemLayout L = smem_layout(a.table_bytes, h.n_in, 0, (int)sizeof(T));
+  const SmemLayout L = smem_layout(a.table_bytes, h.n_in, SMEM_HOT ? h.off_frame : 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  // frames and link records: element k of configuration i at rec_link[(h.off_frame + k) * TILE + i] (biased when the hot part is
+  // not in the scratch, so that the plan's absolute offsets apply to both arrays)
+  T *rec_link = SMEM_HOT ? static_cast<T *>(a.scratch) + ((long long)blockIdx.x * (h.rec_size - h.off_frame) - h.off_frame) * TFK_TILE
+                         : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  T *rec = SMEM_HOT ? reinterpret_cast<T *>(smem + L.rec_off) : rec_link;
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
@@ -250,7 +256,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
     __syncthreads();
-    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, rec_link + threadIdx.x, TFK_TILE);
     __syncthreads();
     const int items = nv * h.n_out;
     const long long hbase = (a.row0 + i0) * h.n_out;
@@ -262,7 +268,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
       fac.nvalid = items - it0 < 32 ? items - it0 : 32;
       fac.head0 = hbase + it0;
       StagedSink<T, Core::D> out = fac.make();
-      Core::phase_b(pv, rec + il, TFK_TILE, o, out);
+      Core::phase_b(pv, rec + il, rec_link + il, TFK_TILE, o, out);
     }
     __syncthreads();
   }
@@ -486,6 +492,8 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
     fk_fused_kernel<Core, true, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_FUSED_GMEM)
     fk_fused_kernel<Core, false, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+  else if (variant == KV_TWOPHASE_SMEM)
+    fk_twophase_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_SQDIST)
     launch_sqdist<Core>(a, pp, grid, smem_bytes, stream);
   else if (variant == KV_COM)
@@ -493,7 +501,7 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
   else if (variant == KV_INERTIA)
     launch_inertia<Core>(a, pp, grid, smem_bytes, stream);
   else
-    fk_twophase_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+    fk_twophase_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   return cudaGetLastError();
 }
 
@@ -504,7 +512,8 @@ template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes,
   const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>
                    : variant == KV_FUSED_SMEM ? (const void *)fk_fused_kernel<Core, true, 4>
                    : variant == KV_FUSED_GMEM ? (const void *)fk_fused_kernel<Core, false, 4>
-                                              : (const void *)fk_twophase_kernel<Core>;
+                   : variant == KV_TWOPHASE_SMEM ? (const void *)fk_twophase_kernel<Core, true>
+                                              : (const void *)fk_twophase_kernel<Core, false>;
   cudaError_t e = cudaSuccess;
   if (smem_bytes > 48 * 1024) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
   if (e != cudaSuccess) return e;

@@ -91,7 +91,7 @@ struct PlanHeader {
   int32_t n_in;       // reals per input row: n_cols (+3 PLANER, +6 FLOATING)
   int32_t n_out_cols; // Jacobian columns: same count (PLANER keeps x, y, yaw: __init__.py:154-158)
   int32_t lrec_size;  // 3 (IGNORE) or 7
-  // per-config record layout, in reals.  Two-phase kernel: [base 7|26 | arec | prec | lrec | frames];
+  // per-config record layout, in reals.  Two-phase kernel: [base 7|26 | arec | prec | frames | lrec];
   // fused single-link kernel: [base pose 7 | arec | prec | frames] (fz_*).  has_base_ctx: the base record
   // carries the inverse pose and tweaked rotations (Jacobian with a moving base).
   int32_t off_base, off_arec, off_prec, off_lrec, off_frame, rec_size;

@@ -248,9 +248,11 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 7;
   h.off_arec = h.off_base + base_rec;
   h.off_prec = h.off_arec + 3 * n_arec;
-  h.off_lrec = h.off_prec + 3 * n_prec;
-  h.off_frame = h.off_lrec + h.lrec_size * n_lrec;
-  h.rec_size = h.off_frame + 7 * b.frames_max;
+  // [base | arec | prec] are what every (configuration, link) item re-reads (small: shared memory when it fits);
+  // branch-point frames and link records come last (block-private scratch in L2)
+  h.off_frame = h.off_prec + 3 * n_prec;
+  h.off_lrec = h.off_frame + 7 * b.frames_max;
+  h.rec_size = h.off_lrec + h.lrec_size * n_lrec;
   // fused single-link kernel: the link pose and the base context stay in registers
   h.fz_arec = (jac && key.base_type != BASE_FIXED) ? 7 : 0; // base pose, re-read for the base columns
   h.fz_prec = h.fz_arec + 3 * n_arec;
