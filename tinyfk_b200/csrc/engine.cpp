@@ -626,10 +626,9 @@ void Engine::sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq
     if (in_row) ck(cudaMemcpyAsync(pp.dq[0], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(q)");
     sqdists_device(cur, st, pp.dq[0], nc, ps, pp.dP[0], ps.with_grads ? pp.dJ[0] : nullptr, nc, 0);
     ck(cudaMemcpyAsync(static_cast<char *>(sq) + (size_t)r0 * row_out, pp.dP[0], (size_t)nc * row_out, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(sq)");
-    if (ps.with_grads)
-      for (int c = 0; c < h.n_out_cols; ++c)
-        ck(cudaMemcpyAsync(static_cast<char *>(G) + ((size_t)c * n + r0) * row_out, static_cast<char *>(pp.dJ[0]) + (size_t)c * nc * row_out,
-                           (size_t)nc * row_out, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(G)");
+    if (ps.with_grads && h.n_out_cols > 0)
+      ck(cudaMemcpy2DAsync(static_cast<char *>(G) + (size_t)r0 * row_out, (size_t)n * row_out, pp.dJ[0], (size_t)nc * row_out,
+                           (size_t)nc * row_out, (size_t)h.n_out_cols, cudaMemcpyDeviceToHost, st), "cudaMemcpy2DAsync(G)");
     ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
   }
   // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:205-209)
@@ -851,10 +850,9 @@ void Engine::com_host(const void *q, int64_t n, const ComSpec &cs_in, void *com,
     com_device(cur, st, pp.dq[0], nc, cs, pp.dP[0], cs.with_jacobian ? pp.dJ[0] : nullptr, nc, 0);
     comT.resize((size_t)nc * 3 * sz);
     ck(cudaMemcpyAsync(comT.data(), pp.dP[0], (size_t)nc * 3 * sz, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(com)");
-    if (cs.with_jacobian)
-      for (int c = 0; c < n_dof; ++c)
-        ck(cudaMemcpyAsync(static_cast<char *>(J) + ((size_t)c * n + r0) * 3 * sz, static_cast<char *>(pp.dJ[0]) + (size_t)c * nc * 3 * sz,
-                           (size_t)nc * 3 * sz, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(J)");
+    if (cs.with_jacobian && n_dof > 0)
+      ck(cudaMemcpy2DAsync(static_cast<char *>(J) + (size_t)r0 * 3 * sz, (size_t)n * 3 * sz, pp.dJ[0], (size_t)nc * 3 * sz,
+                           (size_t)nc * 3 * sz, (size_t)n_dof, cudaMemcpyDeviceToHost, st), "cudaMemcpy2DAsync(J)");
     ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
     for (int64_t i = 0; i < nc; ++i) // (3, nc) component-major -> (n, 3) rows
       for (int k = 0; k < 3; ++k)

@@ -117,7 +117,22 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   if (o.rot_type < 0 || o.rot_type > 2) throw std::invalid_argument("bad rot_type");
   const bool f32 = o.precision == PREC_F32;
   std::string s;
-  s += "#define TFK_SPEC_PLAN 1\n#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n";
+  s += "#define TFK_SPEC_PLAN 1\n";
+  // which helpers are inlined into the straight-line code (tuning knob for experiments: TFK_JIT_DEFINES="A=1;B=1")
+  if (const char *d = std::getenv("TFK_JIT_DEFINES")) {
+    std::string x(d);
+    size_t i = 0;
+    while (i < x.size()) {
+      size_t j = x.find(';', i);
+      if (j == std::string::npos) j = x.size();
+      std::string kv = x.substr(i, j - i);
+      const size_t eq = kv.find('=');
+      if (!kv.empty()) s += "#define " + (eq == std::string::npos ? kv : kv.substr(0, eq) + " " + kv.substr(eq + 1)) + "\n";
+      i = j + 1;
+    }
+  } else {
+    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n";
+  }
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;
