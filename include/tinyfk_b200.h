@@ -111,7 +111,8 @@ TFK_API int tfk_solve_fk_host(tfk_model *m, const void *q, int64_t n, const int 
 /* Same computation on DEVICE-resident buffers of `device`, enqueued on `stream` (a cudaStream_t; NULL =
  * the legacy default stream) and not synchronised.  The destination arrays are dimensioned for ld_cfg
  * configurations and this call fills configurations [row0, row0 + n).  Does not touch the model's stored
- * state.  This is the entry the throughput metric is timed on. */
+ * state.  This is the entry the throughput metric is timed on.  After the first call with a signature on a stream the
+ * call only enqueues one kernel: it may be captured into a CUDA graph on that stream. */
 TFK_API int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
                                 const int *elink_ids, int n_link, const int *joint_ids, int n_joint,
                                 int rot_type, int base_type, int with_jacobian, int precision, void *d_P,
