@@ -646,6 +646,34 @@ void Engine::sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq
   }
 }
 
+// The weight tables of the centre-of-mass / inertia kernels are tiny and rarely change: one buffer per (device, stream),
+// re-uploaded (in the kernel's real type) only when the table or the precision differs from what is there.
+const void *Engine::upload_weights(int device, cudaStream_t stream, const std::vector<double> &w, int precision) {
+  WeightBuf &wb = weight_bufs_[std::make_pair(device, stream)];
+  const size_t need = std::max<size_t>(w.size() * real_size(precision), 16);
+  if (wb.bytes < need) {
+    if (wb.d) {
+      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
+      cudaFree(wb.d);
+      wb.d = nullptr;
+      wb.bytes = 0;
+    }
+    ck(cudaMalloc(&wb.d, need), "cudaMalloc(weights)");
+    wb.bytes = need;
+    wb.host.clear();
+  }
+  if (wb.host != w || wb.precision != precision) {
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // earlier launches still read the old table
+    std::vector<float> wf(w.begin(), w.end());
+    const void *src = precision == PREC_F32 ? static_cast<const void *>(wf.data()) : static_cast<const void *>(w.data());
+    ck(cudaMemcpyAsync(wb.d, src, w.size() * real_size(precision), cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(weights)");
+    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // pageable temporaries
+    wb.host = w;
+    wb.precision = precision;
+  }
+  return wb.d;
+}
+
 // ---- centre of mass (reference src/wrapper.cpp:126-179) --------------------------------------------------------
 // Plan links = the model's "_com" links in id order, then the action links (RotationType IGNORE).
 void Engine::com_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const ComSpec &cs, void *d_com,
@@ -672,33 +700,11 @@ void Engine::com_device(int device, cudaStream_t stream, const void *d_q, int64_
   if (!d_q && reinterpret_cast<const PlanHeader *>(e.blob.data())->n_in > 0) throw std::invalid_argument("q is null");
   if (!d_com) throw std::invalid_argument("com is null");
   if (cs.with_jacobian && !d_J) throw std::invalid_argument("J is null but with_jacobian is set");
-  const std::vector<double> &w = ct.w;
   DeviceGuard g(device);
-  WeightBuf &wb = weight_bufs_[std::make_pair(device, stream)];
-  const size_t need = w.size() * real_size(cs.precision);
-  if (wb.bytes < need) {
-    if (wb.d) {
-      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
-      cudaFree(wb.d);
-      wb.d = nullptr;
-      wb.bytes = 0;
-    }
-    ck(cudaMalloc(&wb.d, need), "cudaMalloc(weights)");
-    wb.bytes = need;
-    wb.host.clear();
-  }
-  if (wb.host != w || wb.precision != cs.precision) {
-    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // earlier launches still read the old table
-    std::vector<float> wf(w.begin(), w.end());
-    const void *src = cs.precision == PREC_F32 ? static_cast<const void *>(wf.data()) : static_cast<const void *>(w.data());
-    ck(cudaMemcpyAsync(wb.d, src, need, cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(weights)");
-    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)"); // pageable temporaries
-    wb.host = w;
-    wb.precision = cs.precision;
-  }
+  const void *d_w = upload_weights(device, stream, ct.w, cs.precision);
   LaunchExtra ex = LaunchExtra();
   ex.variant = KV_COM;
-  ex.d_weights = wb.d;
+  ex.d_weights = d_w;
   ex.n_com = ct.n_com;
   ex.n_act = ct.n_act;
   ex.mass_total = ct.mass_total;
@@ -728,32 +734,10 @@ void Engine::inertia_device(int device, cudaStream_t stream, const void *d_q, in
   if (!d_q && n_joint > 0) throw std::invalid_argument("q is null");
   if (!d_out) throw std::invalid_argument("out is null");
   DeviceGuard g(device);
-  WeightBuf &wb = weight_bufs_[std::make_pair(device, stream)];
-  const std::vector<double> &w = it.w;
-  const size_t need = w.size() * real_size(precision);
-  if (wb.bytes < need) {
-    if (wb.d) {
-      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
-      cudaFree(wb.d);
-      wb.d = nullptr;
-      wb.bytes = 0;
-    }
-    ck(cudaMalloc(&wb.d, need), "cudaMalloc(weights)");
-    wb.bytes = need;
-    wb.host.clear();
-  }
-  if (wb.host != w || wb.precision != precision) {
-    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
-    std::vector<float> wf(w.begin(), w.end());
-    const void *src = precision == PREC_F32 ? static_cast<const void *>(wf.data()) : static_cast<const void *>(w.data());
-    ck(cudaMemcpyAsync(wb.d, src, need, cudaMemcpyHostToDevice, stream), "cudaMemcpyAsync(weights)");
-    ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(weights)");
-    wb.host = w;
-    wb.precision = precision;
-  }
+  const void *d_w = upload_weights(device, stream, it.w, precision);
   LaunchExtra ex = LaunchExtra();
   ex.variant = KV_INERTIA;
-  ex.d_weights = wb.d;
+  ex.d_weights = d_w;
   ex.n_com = (int)it.links.size();
   ex.mass_total = it.mass_total;
   launch(device, stream, e, precision, d_q, n, d_out, nullptr, ld_cfg, row0, &ex);

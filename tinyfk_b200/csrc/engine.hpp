@@ -166,6 +166,7 @@ private:
     int precision = -1;
   };
   std::map<std::pair<int, cudaStream_t>, WeightBuf> weight_bufs_;
+  const void *upload_weights(int device, cudaStream_t stream, const std::vector<double> &w, int precision);
   void release_device_memory();
 
   std::vector<std::unique_ptr<PlanEntry>> plans_;
