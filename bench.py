@@ -229,6 +229,12 @@ def measured_peaks():
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from the committed
 # `ncu --set full` capture (profiles/), keyed by workload; None until a capture exists
+# FP64 warp instructions per 32 configurations of the dominant kernel, from the same capture (executed-opcode histogram:
+# DMUL + DADD + DFMA + DSETP); an FP64 instruction occupies its scheduler's FP64 pipe for 2 cycles on B200
+# (tools/ubench/fp64_pipe.cu), which gives the kernel's FP64-pipe bound next to the HBM one
+NCU_FP64_PER_WARP = {
+    ("cfg2", "fp64", "spec"): 2130,     # profiles/r1_full_cfg2_strict_v8.txt (ncu: FP64 pipe 48 % active)
+}
 NCU_TRAFFIC_BYTES = {
     ("cfg2", "fp64"): 577.6e6,  # profiles/r1_full_cfg2_strict_v8.txt: 84.0 MB read + 493.7 MB written (algorithmic 637.5 MB)
 }
@@ -379,6 +385,14 @@ def run_ours(args):
                                   "instruction issue / the FP64 pipe, not by HBM: DESIGN.md section 3") if not prec
                                  else "FP32 opt-in mode"},
         }
+        key = (cfg, args.precision, "spec" if "spec" in str(info.get("kernel")) else "generic")
+        if key in NCU_FP64_PER_WARP and clk and clk.get("sm_mhz"):
+            sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+            bound_ms = (n / 32.0) * NCU_FP64_PER_WARP[key] * 2.0 / (4 * sms * clk["sm_mhz"] * 1e6) * 1e3
+            out["roofline"]["fp64_pipe"] = {"fp64_warp_instructions_per_32_configs": NCU_FP64_PER_WARP[key],
+                                            "bound_ms": bound_ms, "frac": bound_ms / kern_ms,
+                                            "note": "2 cycles per FP64 warp instruction per scheduler, 4 schedulers x %d SMs at "
+                                                    "the sampled SM clock" % sms}
         if e2e is not None:
             out["e2e"] = e2e
         if not args.no_cpu_baseline and world == 1:
