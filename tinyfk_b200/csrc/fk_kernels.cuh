@@ -182,6 +182,39 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
   pv.masks = spec::k_mask0;
   pv.lrec_of_out = nullptr;
   const PlanHeader &h = spec::k_h;
+#if defined(TFK_SPEC_DIRECT_Q)
+  // no q tile: every thread reads its own input row straight from global memory (constant offsets; the rows of a warp
+  // are one contiguous run, L1 serves the repeats) -- shared memory holds only the warps' staging strips and the
+  // records, which lets more warps stay resident
+  T *stg0 = reinterpret_cast<T *>(smem);
+  T *rec = stg0 + (TFK_TILE / 32) * TFK_STG;
+  rec += threadIdx.x;
+  const T *q = static_cast<const T *>(a.q);
+  const int warp = threadIdx.x >> 5;
+
+  StagedFactory<T, Core::D> fac;
+  fac.P = static_cast<T *>(a.P);
+  fac.J = static_cast<T *>(a.J);
+  fac.ldP = a.ld_cfg;
+  fac.stg = stg0 + warp * TFK_STG;
+
+  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i0 = tile * TFK_TILE;
+    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
+    int nvalid = nv - warp * 32;
+    nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
+    if (nvalid > 0) {
+      const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1;
+      fac.nvalid = nvalid;
+      fac.head0 = a.row0 + i0 + warp * 32;
+      Core::run_fused(pv, q + (i0 + row) * h.n_in, rec, TFK_TILE, fac);
+    }
+    __syncthreads(); // keeps the block's warps together in the straight-line code (instruction cache)
+  }
+}
+#else
   const SmemLayout L = smem_layout(0, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
   T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
@@ -214,6 +247,7 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
     __syncthreads();
   }
 }
+#endif
 #endif
 
 // SMEM_HOT: [base | arec | prec] (what every (configuration, link) item re-reads) live in shared memory and only the

@@ -113,7 +113,7 @@ bool nvrtc_available(std::string *why) {
 }
 
 std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
-  if (o.tile != 128 && o.tile != 256) throw std::invalid_argument("tile must be 128 or 256");
+  if (o.tile < 32 || o.tile > 512 || o.tile % 32) throw std::invalid_argument("tile must be a multiple of 32 up to 512");
   if (o.rot_type < 0 || o.rot_type > 2) throw std::invalid_argument("bad rot_type");
   const bool f32 = o.precision == PREC_F32;
   std::string s;
@@ -133,6 +133,7 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   } else {
     s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n";
   }
+  if (o.direct_q) s += "#define TFK_SPEC_DIRECT_Q 1\n";
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;

@@ -23,6 +23,7 @@ struct SpecOptions {
   int rot_type;   // compile-time RotationType of FkCore
   int tile;       // threads per block == configurations per tile (128 | 256)
   int blocks_per_sm;
+  int direct_q;   // 1: no q tile in shared memory (fk_kernels.cuh TFK_SPEC_DIRECT_Q)
 };
 
 // The translation unit handed to NVRTC for this plan (exposed for tests and for the cache key).
