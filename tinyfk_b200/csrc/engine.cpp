@@ -93,7 +93,7 @@ Engine::SpecKernel::~SpecKernel() {
 }
 
 // ---- plan specialisation (jit.hpp) -------------------------------------------------------------------------------
-bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *direct_q, std::string *why) const {
+bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
   if (h->n_out != 1) {
     if (why) *why = "plan specialisation exists for one requested link (the fused kernel) only";
@@ -106,12 +106,11 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
   const int rb = (int)real_size(precision);
   const int limit = 227 * 1024; // registers allow 512 (FP64) / 768 (FP32) resident threads
   // Shared memory of the specialised kernel: one staging strip per warp + the thread-private records (no q tile: every
-  // thread reads its own input row from global memory at constant offsets, fk_kernels.cuh TFK_SPEC_DIRECT_Q).
+  // thread reads its own input row from global memory at constant offsets).
   // 256-thread blocks, two per SM: the blocks of an SM then walk the long straight-line code close together, which the
   // instruction cache rewards (measured on cfg2: 2 x 256 threads 0.245 ms, 4 x 128 0.258, 3 x 192 0.266, 1 x 512 0.256)
-  *direct_q = 1;
   {
-    const int sm = (256 / 32) * (32 * 7) * rb + h->fz_size * 256 * rb;
+    const int sm = fused_smem_bytes(256, h->fz_size, rb);
     int b = precision == PREC_F32 ? 3 : 2;
     while (b > 2 && b * (sm + 1024) > limit) --b;
     if (b * (sm + 1024) <= limit) {
@@ -122,7 +121,7 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
     }
   }
   // larger records: 128-thread blocks, as many as fit (at least two)
-  const int sm = (128 / 32) * (32 * 7) * rb + h->fz_size * 128 * rb;
+  const int sm = fused_smem_bytes(128, h->fz_size, rb);
   int b = precision == PREC_F32 ? 6 : 4;
   while (b > 2 && b * (sm + 1024) > limit) --b;
   if (b * (sm + 1024) > limit) {
@@ -143,7 +142,7 @@ void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
       if (!(wait && sk.state == SPEC_COMPILING)) return;
     } else {
       std::string why;
-      if (!spec_eligible(e, precision, &sk.tile, &sk.bps, &sk.smem, &sk.direct_q, &why)) throw std::invalid_argument(why);
+      if (!spec_eligible(e, precision, &sk.tile, &sk.bps, &sk.smem, &why)) throw std::invalid_argument(why);
       if (!nvrtc_available(&why)) {
         sk.state = SPEC_FAILED;
         sk.error = why;
@@ -156,7 +155,6 @@ void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
       o.rot_type = h->rot_type;
       o.tile = sk.tile;
       o.blocks_per_sm = sk.bps;
-      o.direct_q = sk.direct_q;
       const std::string src = plan_to_source(e.blob);
       SpecKernel *p = &sk; // heap-allocated with the plan entry; its destructor joins this thread
       sk.worker = std::thread([p, src, o] {
@@ -423,10 +421,11 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     variant = ex->variant;
   } else if (h->n_out == 1) {
     rec_reals = h->fz_size;
-    L = smem_layout(plan_bytes, h->n_in, rec_reals, rb);
+    L = SmemLayout();
+    L.total = fused_smem_bytes(TFK_TILE, rec_reals, rb);
     variant = KV_FUSED_SMEM;
     if (L.total > 100 * 1024) { // keep at least two blocks per SM; beyond that records go to L2
-      L = smem_layout(plan_bytes, h->n_in, 0, rb);
+      L.total = fused_smem_bytes(TFK_TILE, 0, rb);
       variant = KV_FUSED_GMEM;
     } else if (5 * (L.total + 1024) <= 228 * 1024) {
       variant = KV_FUSED_SMEM5; // a fifth block fits next to four: take the build that leaves registers for it

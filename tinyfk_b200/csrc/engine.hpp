@@ -109,7 +109,7 @@ private:
     std::vector<char> cubin;
     bool from_cache = false;
     std::thread worker;
-    int tile = 0, bps = 0, smem = 0, direct_q = 0;
+    int tile = 0, bps = 0, smem = 0;
     cudaLibrary_t lib = nullptr;
     cudaKernel_t kernel = nullptr;
     std::map<int, int> blocks_per_sm; // device -> occupancy (also marks the shared-memory attribute as set there)
@@ -123,7 +123,7 @@ private:
     SpecKernel spec[2];                       // by precision
     int64_t configs_served = 0;
   };
-  bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *direct_q, std::string *why) const;
+  bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const;
   void spec_start(PlanEntry &e, int precision, bool wait);
   bool spec_launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const KernelArgs &a);
   struct Workspace { // one per (device, stream): concurrent launches never share records

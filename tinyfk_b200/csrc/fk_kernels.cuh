@@ -133,36 +133,36 @@ __global__ void __launch_bounds__(TFK_TILE, BPS) fk_fused_kernel(const KernelArg
   pv.masks = pp.mask0;
   pv.lrec_of_out = nullptr; // one output: never read
   const PlanHeader &h = pp.h;
-  const SmemLayout L = smem_layout(0, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
-  T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
+  // shared memory: [one staging strip per warp | thread-private records].  There is no q tile: every thread reads its
+  // own input row from global memory (a warp's rows are one contiguous run; L1 serves the repeated sectors), which
+  // measured faster than staging the tile (no staging pass, one barrier less).
+  T *stg0 = reinterpret_cast<T *>(smem);
+  T *rec = SMEM_REC ? stg0 + fused_strip_reals(TFK_TILE)
                     : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.fz_size;
   rec += threadIdx.x;
   const T *q = static_cast<const T *>(a.q);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp = threadIdx.x >> 5;
 
   StagedFactory<T, Core::D> fac;
   fac.P = static_cast<T *>(a.P);
   fac.J = static_cast<T *>(a.J);
   fac.ldP = a.ld_cfg; // n_out == 1
-  fac.stg = qs + warp * 32 * L.q_pitch; // the warp's own q rows, dead once the walk has read them
+  fac.stg = stg0 + warp * TFK_STG;
 
   const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long i0 = tile * TFK_TILE;
     const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
-    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
-    __syncthreads();
     int nvalid = nv - warp * 32;
     nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
     if (nvalid > 0) {
       const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1; // tail lanes redo the last row, store nothing
       fac.nvalid = nvalid;
       fac.head0 = a.row0 + i0 + warp * 32;
-      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, fac);
+      Core::run_fused(pv, q + (i0 + row) * h.n_in, rec, TFK_TILE, fac);
     }
-    __syncthreads();
+    __syncthreads(); // keeps the block's warps together in the code (instruction cache)
   }
 }
 
@@ -182,12 +182,11 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
   pv.masks = spec::k_mask0;
   pv.lrec_of_out = nullptr;
   const PlanHeader &h = spec::k_h;
-#if defined(TFK_SPEC_DIRECT_Q)
   // no q tile: every thread reads its own input row straight from global memory (constant offsets; the rows of a warp
   // are one contiguous run, L1 serves the repeats) -- shared memory holds only the warps' staging strips and the
   // records, which lets more warps stay resident
   T *stg0 = reinterpret_cast<T *>(smem);
-  T *rec = stg0 + (TFK_TILE / 32) * TFK_STG;
+  T *rec = stg0 + fused_strip_reals(TFK_TILE);
   rec += threadIdx.x;
   const T *q = static_cast<const T *>(a.q);
   const int warp = threadIdx.x >> 5;
@@ -214,40 +213,6 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
     __syncthreads(); // keeps the block's warps together in the straight-line code (instruction cache)
   }
 }
-#else
-  const SmemLayout L = smem_layout(0, h.n_in, SMEM_REC ? h.fz_size : 0, (int)sizeof(T));
-  T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = SMEM_REC ? reinterpret_cast<T *>(smem + L.rec_off)
-                    : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.fz_size;
-  rec += threadIdx.x;
-  const T *q = static_cast<const T *>(a.q);
-  const int warp = threadIdx.x >> 5;
-
-  StagedFactory<T, Core::D> fac;
-  fac.P = static_cast<T *>(a.P);
-  fac.J = static_cast<T *>(a.J);
-  fac.ldP = a.ld_cfg;
-  fac.stg = qs + warp * 32 * L.q_pitch;
-
-  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long i0 = tile * TFK_TILE;
-    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
-    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
-    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
-    __syncthreads();
-    int nvalid = nv - warp * 32;
-    nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
-    if (nvalid > 0) {
-      const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1;
-      fac.nvalid = nvalid;
-      fac.head0 = a.row0 + i0 + warp * 32;
-      Core::run_fused(pv, qs + row * L.q_pitch, rec, TFK_TILE, fac);
-    }
-    __syncthreads();
-  }
-}
-#endif
 #endif
 
 // SMEM_HOT: [base | arec | prec] (what every (configuration, link) item re-reads) live in shared memory and only the

@@ -62,6 +62,11 @@ struct SmemLayout {
 // q tile pitch: odd (conflict-free 64-bit reads at one row per thread) and >= 7 so that a warp's own 32
 // rows can double as its staging strip (32 x pose_dim reals) once the angles have been consumed
 TFK_HDI int q_pitch_of(int n_in) { return (n_in < 7 ? 7 : n_in) | 1; }
+// fused kernels (one requested link): [one staging strip of 32 x 7 reals per warp | records], no q tile
+TFK_HDI int fused_strip_reals(int tile) { return (tile / 32) * (32 * 7); }
+TFK_HDI int fused_smem_bytes(int tile, int rec_reals_in_smem, int real_bytes) {
+  return (fused_strip_reals(tile) + rec_reals_in_smem * tile) * real_bytes;
+}
 TFK_HDI SmemLayout smem_layout_tile(int tile, int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
   SmemLayout L;
   L.plan_bytes = (table_bytes + 15) & ~15;

@@ -133,7 +133,6 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   } else {
     s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n";
   }
-  if (o.direct_q) s += "#define TFK_SPEC_DIRECT_Q 1\n";
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;

@@ -21,9 +21,8 @@ namespace tfk {
 struct SpecOptions {
   int precision;  // PREC_F64_STRICT | PREC_F32
   int rot_type;   // compile-time RotationType of FkCore
-  int tile;       // threads per block == configurations per tile (128 | 256)
+  int tile;       // threads per block == configurations per tile (a multiple of 32)
   int blocks_per_sm;
-  int direct_q;   // 1: no q tile in shared memory (fk_kernels.cuh TFK_SPEC_DIRECT_Q)
 };
 
 // The translation unit handed to NVRTC for this plan (exposed for tests and for the cache key).
