@@ -414,6 +414,12 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     rec_reals = h->rec_size;
     L = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, 0, rb);
     variant = KV_SQDIST;
+    const SmemLayout Lh = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, h->off_frame, rb);
+    if (3 * (Lh.total + 1024) <= 227 * 1024) {
+      L = Lh;
+      variant = KV_SQDIST_SMEM;
+      rec_reals = h->rec_size - h->off_frame;
+    }
   } else if (com) {
     rec_reals = h->rec_size;
     const int n_w = ex->variant == KV_INERTIA ? 7 * ex->n_com : ex->n_com + ex->n_act;

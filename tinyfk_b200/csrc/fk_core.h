@@ -672,9 +672,14 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     return T(2) * ((a0 * d.x + a1 * d.y) + a2 * d.z);
   }
   static TFK_FN void pair_sqdist(const PlanView &pv, const T *rec, int o1, int o2, bool valid, T *sq, T *G, long long ldG) {
+    pair_sqdist(pv, rec, rec, o1, o2, valid, sq, G, ldG);
+  }
+  // rec: [base | axes | positions] of the configuration; rec_link: its link records (see phase_a)
+  static TFK_FN void pair_sqdist(const PlanView &pv, const T *rec, const T *rec_link, int o1, int o2, bool valid, T *sq, T *G,
+                                 long long ldG) {
     const PlanHeader &h = *pv.h;
-    const V p1 = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o1] * LREC);
-    const V p2 = get_vec(rec, STRIDE, h.off_lrec + pv.lrec_of_out[o2] * LREC);
+    const V p1 = get_vec(rec_link, STRIDE, h.off_lrec + pv.lrec_of_out[o1] * LREC);
+    const V p2 = get_vec(rec_link, STRIDE, h.off_lrec + pv.lrec_of_out[o2] * LREC);
     V d;
     d.x = p1.x - p2.x;
     d.y = p1.y - p2.y;

@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
 // compute_inter_link_squared_dists (src/wrapper.cpp:189-237): phase A as in the two-phase kernel (plan over the
 // union of the pairs' links, positions only), then one thread per (configuration, pair): consecutive threads
 // write consecutive entries of sqdists and of every gradient column -- coalesced without staging.
-template <class Core>
+template <class Core, bool SMEM_HOT>
 __global__ void __launch_bounds__(TFK_TILE, 4) fk_sqdist_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
@@ -293,9 +293,12 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_sqdist_kernel(const KernelArgs
   pv.cols = pp.cols;
   pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
   pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
-  const SmemLayout L = smem_layout(tab + ((2 * a.n_pairs * 4 + 15) & ~15), h.n_in, 0, (int)sizeof(T));
+  const SmemLayout L = smem_layout(tab + ((2 * a.n_pairs * 4 + 15) & ~15), h.n_in, SMEM_HOT ? h.off_frame : 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  // as fk_twophase_kernel: base/axis/position records in shared memory when they fit, frames and link records in scratch
+  T *rec_link = SMEM_HOT ? static_cast<T *>(a.scratch) + ((long long)blockIdx.x * (h.rec_size - h.off_frame) - h.off_frame) * TFK_TILE
+                         : static_cast<T *>(a.scratch) + (size_t)blockIdx.x * TFK_TILE * h.rec_size;
+  T *rec = SMEM_HOT ? reinterpret_cast<T *>(smem + L.rec_off) : rec_link;
   const T *q = static_cast<const T *>(a.q);
   T *sq = static_cast<T *>(a.P);
   T *G = static_cast<T *>(a.J);
@@ -308,14 +311,14 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_sqdist_kernel(const KernelArgs
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
     __syncthreads();
-    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, TFK_TILE);
+    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, rec_link + threadIdx.x, TFK_TILE);
     __syncthreads();
     const int items = nv * a.n_pairs;
     const long long hbase = (a.row0 + i0) * a.n_pairs;
     for (int it = threadIdx.x; it < items; it += TFK_TILE) {
       const int il = it / a.n_pairs;
       const int j = it - il * a.n_pairs;
-      Core::pair_sqdist(pv, rec + il, pairs[j], pairs[a.n_pairs + j], true, sq + hbase + it, G ? G + hbase + it : nullptr, ldG);
+      Core::pair_sqdist(pv, rec + il, rec_link + il, pairs[j], pairs[a.n_pairs + j], true, sq + hbase + it, G ? G + hbase + it : nullptr, ldG);
     }
     __syncthreads();
   }
@@ -449,14 +452,22 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_inertia_kernel(const KernelArg
 
 #if !defined(__CUDACC_RTC__) // host-side launch helpers (not part of a run-time compiled translation unit)
 // the pair kernel exists for RotationType IGNORE only (positions); other instantiations never reach it
-template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, int grid, int smem_bytes, cudaStream_t stream) {
-  fk_sqdist_kernel<Core><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+template <class Core> typename std::enable_if<Core::D == 3, void>::type launch_sqdist(const KernelArgs &a, const PlanParams &pp, bool hot, int grid, int smem_bytes, cudaStream_t stream) {
+  if (hot)
+    fk_sqdist_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
+  else
+    fk_sqdist_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
 }
-template <class Core> typename std::enable_if<Core::D != 3, void>::type launch_sqdist(const KernelArgs &, const PlanParams &, int, int, cudaStream_t) {}
-template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type occupancy_sqdist(int smem_bytes, int *blocks_per_sm) {
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fk_sqdist_kernel<Core>, TFK_TILE, smem_bytes);
+template <class Core> typename std::enable_if<Core::D != 3, void>::type launch_sqdist(const KernelArgs &, const PlanParams &, bool, int, int, cudaStream_t) {}
+template <class Core> typename std::enable_if<Core::D == 3, cudaError_t>::type occupancy_sqdist(bool hot, int smem_bytes, int *blocks_per_sm) {
+  const void *fn = hot ? (const void *)fk_sqdist_kernel<Core, true> : (const void *)fk_sqdist_kernel<Core, false>;
+  if (smem_bytes > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fn, TFK_TILE, smem_bytes);
 }
-template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_sqdist(int, int *blocks_per_sm) {
+template <class Core> typename std::enable_if<Core::D != 3, cudaError_t>::type occupancy_sqdist(bool, int, int *blocks_per_sm) {
   *blocks_per_sm = 0;
   return cudaSuccess;
 }
@@ -493,8 +504,8 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
     fk_fused_kernel<Core, false, 4><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
   else if (variant == KV_TWOPHASE_SMEM)
     fk_twophase_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
-  else if (variant == KV_SQDIST)
-    launch_sqdist<Core>(a, pp, grid, smem_bytes, stream);
+  else if (variant == KV_SQDIST || variant == KV_SQDIST_SMEM)
+    launch_sqdist<Core>(a, pp, variant == KV_SQDIST_SMEM, grid, smem_bytes, stream);
   else if (variant == KV_COM)
     launch_com<Core>(a, pp, grid, smem_bytes, stream);
   else if (variant == KV_INERTIA)
@@ -505,7 +516,7 @@ cudaError_t launch_fk_core(const KernelArgs &a, const PlanParams &pp, int varian
 }
 
 template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes, int *blocks_per_sm) {
-  if (variant == KV_SQDIST) return occupancy_sqdist<Core>(smem_bytes, blocks_per_sm);
+  if (variant == KV_SQDIST || variant == KV_SQDIST_SMEM) return occupancy_sqdist<Core>(variant == KV_SQDIST_SMEM, smem_bytes, blocks_per_sm);
   if (variant == KV_COM) return occupancy_com<Core>(smem_bytes, blocks_per_sm);
   if (variant == KV_INERTIA) return occupancy_inertia<Core>(smem_bytes, blocks_per_sm);
   const void *fn = variant == KV_FUSED_SMEM5  ? (const void *)fk_fused_kernel<Core, true, 5>

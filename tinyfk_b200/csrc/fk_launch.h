@@ -25,6 +25,7 @@ enum KernelVariant {
   KV_COM = 5,         // centre of mass (+ Jacobian): phase A -> records -> mass-weighted sums in link-id order
   KV_INERTIA = 6,
   KV_TWOPHASE_SMEM = 8, // several links, [base | arec | prec] in shared memory, frames and link records in scratch
+  KV_SQDIST_SMEM = 9,   // KV_SQDIST with [base | arec | prec] in shared memory
   KV_FUSED_SPEC = 7,  // plan-specialised build of the fused kernel, compiled at run time (jit.cpp)
      // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
