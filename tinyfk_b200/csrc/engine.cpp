@@ -415,7 +415,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     L = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, 0, rb);
     variant = KV_SQDIST;
     const SmemLayout Lh = smem_layout(table_bytes + ((2 * n_pairs * 4 + 15) & ~15), h->n_in, h->off_frame, rb);
-    if (3 * (Lh.total + 1024) <= 227 * 1024) {
+    if (3 * (Lh.total + 1024) <= 227 * 1024 && !std::getenv("TFK_NO_SMEM_HOT")) { // (env: A/B knob for measurements)
       L = Lh;
       variant = KV_SQDIST_SMEM;
       rec_reals = h->rec_size - h->off_frame;
@@ -442,7 +442,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
     variant = KV_TWOPHASE;
     // the records every (configuration, link) item re-reads go to shared memory when three blocks still fit on an SM
     const SmemLayout Lh = smem_layout(plan_bytes, h->n_in, h->off_frame, rb);
-    if (3 * (Lh.total + 1024) <= 227 * 1024) {
+    if (3 * (Lh.total + 1024) <= 227 * 1024 && !std::getenv("TFK_NO_SMEM_HOT")) {
       L = Lh;
       variant = KV_TWOPHASE_SMEM;
       rec_reals = h->rec_size - h->off_frame;
