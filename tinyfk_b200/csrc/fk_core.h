@@ -721,6 +721,29 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     }
     // forward finite difference columns, src/kinematics.cpp:182-232 (position rows only)
     const typename M::Den deps = M::den_(T(1e-7));
+    if (h.base_type == 1) { // PLANER: yaw column only, every base quantity yaw-only (fk_math.h, emit_planer_yaw)
+      const PlanerCtx c = bs.planer();
+      const typename O::QZ ii = O::qz_get_inverse(c.binv.q), ki = O::qz_get_inverse(c.bk);
+      V n1, n2;
+      {
+        const V a1 = O::rotate_z_i(c.binv.q, ii, p1), a2 = O::rotate_z_i(c.binv.q, ii, p2);
+        V b1, b2;
+        b1.x = a1.x + c.binv.p.x, b1.y = a1.y + c.binv.p.y, b1.z = a1.z + c.binv.p.z;
+        b2.x = a2.x + c.binv.p.x, b2.y = a2.y + c.binv.p.y, b2.z = a2.z + c.binv.p.z;
+        const V r1 = O::rotate_z_i(c.bk, ki, b1), r2 = O::rotate_z_i(c.bk, ki, b2);
+        n1.x = (r1.x + base_p.x) - p1.x, n1.y = (r1.y + base_p.y) - p1.y, n1.z = (r1.z + base_p.z) - p1.z;
+        n2.x = (r2.x + base_p.x) - p2.x, n2.y = (r2.y + base_p.y) - p2.y, n2.z = (r2.z + base_p.z) - p2.z;
+      }
+      T m1[3] = {n1.x, n1.y, n1.z}, m2[3] = {n2.x, n2.y, n2.z};
+      M::divn_(m1, deps);
+      M::divn_(m2, deps);
+      V j1, j2;
+      j1.x = m1[0], j1.y = m1[1], j1.z = m1[2];
+      j2.x = m2[0], j2.y = m2[1], j2.z = m2[2];
+      const T g = grad_entry(j1, j2, d);
+      if (valid) G[(h.n_cols + n_trans) * ldG] = g;
+      return;
+    }
     V be1, be2;
     {
       const P binv = bs.binv();

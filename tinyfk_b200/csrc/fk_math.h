@@ -558,9 +558,9 @@ template <class M> struct Ops {
     c.w = a.w * b.w - a.z * b.z;
     return c;
   }
-  // Rotation * Vector3 (pose.h:265-282), q yaw-only
-  static TFK_FN V rotate_z(const QZ &q, const V &v) {
-    const QZ i = qz_get_inverse(q);
+  // Rotation * Vector3 (pose.h:265-282), q yaw-only; i = GetInverse(q) (the reference recomputes it per call: same
+  // operands, same bits, so callers that rotate several vectors by one q take it once)
+  static TFK_FN V rotate_z_i(const QZ &q, const QZ &i, const V &v) {
     Q t;
     t.x = v.x * i.w + v.y * i.z;
     t.y = -(v.x * i.z) + v.y * i.w;
@@ -572,6 +572,7 @@ template <class M> struct Ops {
     r.z = q.w * t.z + q.z * t.w;
     return r;
   }
+  static TFK_FN V rotate_z(const QZ &q, const V &v) { return rotate_z_i(q, qz_get_inverse(q), v); }
   // Pose::inverse (pose.h:329-339) of a yaw-only pose
   static TFK_FN PZ inverse_z(const PZ &a) {
     PZ o;
