@@ -233,10 +233,10 @@ def measured_peaks():
 # DMUL + DADD + DFMA + DSETP); an FP64 instruction occupies its scheduler's FP64 pipe for 2 cycles on B200
 # (tools/ubench/fp64_pipe.cu), which gives the kernel's FP64-pipe bound next to the HBM one
 NCU_FP64_PER_WARP = {
-    ("cfg2", "fp64", "spec"): 2130,     # profiles/r1_full_cfg2_strict_v8.txt (ncu: FP64 pipe 48 % active)
+    ("cfg2", "fp64", "spec"): 2140,     # profiles/r1_full_cfg2_strict_v9.txt (ncu: FP64 pipe 51 % active)
 }
 NCU_TRAFFIC_BYTES = {
-    ("cfg2", "fp64"): 577.6e6,  # profiles/r1_full_cfg2_strict_v8.txt: 84.0 MB read + 493.7 MB written (algorithmic 637.5 MB)
+    ("cfg2", "fp64"): 578.0e6,  # profiles/r1_full_cfg2_strict_v9.txt: 84.0 MB read + 494.0 MB written (algorithmic 637.5 MB)
 }
 
 
