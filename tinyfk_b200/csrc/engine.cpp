@@ -395,6 +395,13 @@ Engine::Workspace &Engine::workspace(int device, cudaStream_t stream, size_t byt
   return w;
 }
 
+// fk_pos_kernel (entry-per-thread phase B for RotationType IGNORE) is opt-in while it measures slower than the
+// two-phase kernel on cfg4 (profiles/README.md): TFK_POS_KERNEL=1 selects it
+static bool pos_kernel_enabled() {
+  const char *v = std::getenv("TFK_POS_KERNEL");
+  return v && *v && *v != '0';
+}
+
 void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n,
                     void *d_P, void *d_J, int64_t ld_cfg, int64_t row0, const LaunchExtra *ex) {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
@@ -408,7 +415,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
-  int variant, rec_reals;
+  int variant, rec_reals, rec_stride = TFK_TILE, pos_sub = 0;
   SmemLayout L;
   if (sqdist) {
     rec_reals = h->rec_size;
@@ -447,6 +454,25 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
       variant = KV_TWOPHASE_SMEM;
       rec_reals = h->rec_size - h->off_frame;
     }
+    // position-only queries (RotationType IGNORE): the entry-per-thread kernel; plan records in the scratch
+    // ([k][TILE + 1]); shared memory holds a sub-tile's link positions and, when three blocks still fit, the
+    // column-ordered joint records (else they go to the scratch too).  Largest sub-tile that fits wins.
+    if (h->rot_type == 0 && h->n_cols <= 64 && pos_kernel_enabled()) {
+      const int n_crec = h->with_jacobian ? 6 * h->n_cols : 0;
+      bool found = false;
+      for (int in_smem = 1; in_smem >= 0 && !found; --in_smem)
+        for (int sub = 32; sub >= 8 && !found; sub >>= 1) {
+          if (in_smem && std::getenv("TFK_NO_SMEM_HOT")) continue;
+          const SmemLayout Lp = smem_layout_pos(plan_bytes, h->n_in, h->n_lrec, sub, in_smem ? n_crec : 0, rb);
+          if (3 * (Lp.total + 1024) > 227 * 1024) continue;
+          found = true;
+          L = Lp;
+          pos_sub = sub;
+          variant = in_smem ? KV_POS_SMEM : KV_POS;
+          rec_stride = TFK_POS_STRIDE;
+          rec_reals = h->rec_size + (in_smem ? 0 : n_crec);
+        }
+    }
   }
   if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5) && jit_mode != JIT_OFF) {
     KernelArgs sa = KernelArgs();
@@ -479,7 +505,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   KernelArgs a;
   a.scratch = nullptr;
   if (variant != KV_FUSED_SMEM && variant != KV_FUSED_SMEM5) {
-    const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(rec_reals, 1) * real_size(precision);
+    const size_t rec_bytes = (size_t)grid * rec_stride * (size_t)std::max(rec_reals, 1) * real_size(precision);
     a.scratch = workspace(device, stream, rec_bytes).scratch;
   }
   a.tables = table_bytes ? plan_on_device(e, device, stream) + h->off_outs : nullptr;
@@ -492,6 +518,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.J = d_J;
   a.pairs = sqdist ? ex->d_pairs : nullptr;
   a.n_pairs = n_pairs;
+  a.sub_cfg = pos_sub;
   a.weights = com ? ex->d_weights : nullptr;
   a.n_com = com ? ex->n_com : 0;
   a.n_act = com ? ex->n_act : 0;

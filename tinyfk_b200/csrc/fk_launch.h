@@ -28,6 +28,8 @@ enum KernelVariant {
   KV_SQDIST_SMEM = 9,   // KV_SQDIST with [base | arec | prec] in shared memory
   KV_FUSED_SPEC = 7,  // plan-specialised build of the fused kernel, compiled at run time (jit.cpp)
      // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
+  KV_POS = 10,       // several links, RotationType IGNORE: phase A -> records -> one thread per OUTPUT ENTRY (fk_pos_kernel)
+  KV_POS_SMEM = 11,  // KV_POS with the column-ordered joint records in shared memory
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };
@@ -46,6 +48,7 @@ struct KernelArgs {
   int n_pairs;
   // KV_INERTIA: P = out (9, ld_cfg); weights = 7 reals per com link (mass, ixx, ixy, ixz, iyy, iyz, izz); n_com, mass_total
   // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
+  int sub_cfg;         // fk_pos_kernel: configurations per phase-B sub-tile (power of two, <= 32)
   const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
   int n_com, n_act;
   double mass_total, vfs, com_diag;
@@ -79,6 +82,19 @@ TFK_HDI SmemLayout smem_layout_tile(int tile, int table_bytes, int n_in, int rec
 }
 TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
   return smem_layout_tile(TFK_TILE, table_bytes, n_in, rec_reals_in_smem, real_bytes);
+}
+
+// fk_pos_kernel: records are [k][TFK_TILE + 1] (odd pitch: a warp reading three consecutive elements of ONE
+// configuration hits three banks, and one element of 32 configurations hits 32)
+enum { TFK_POS_STRIDE = TFK_TILE + 1 };
+// shared memory: [per-output tables | q tile, later the sub-tile's link positions [3*n_lrec][sub + 1], later the warps'
+// staging strips | column-ordered joint records (or none)]
+TFK_HDI SmemLayout smem_layout_pos(int table_bytes, int n_in, int n_lrec, int sub, int rec_reals_in_smem, int real_bytes) {
+  SmemLayout L = smem_layout_tile(TFK_TILE, table_bytes, n_in, 0, real_bytes);
+  const int lps = (3 * n_lrec * (sub + 1) * real_bytes + 15) & ~15;
+  if (L.rec_off - L.q_off < lps) L.rec_off = L.q_off + lps;
+  L.total = L.rec_off + rec_reals_in_smem * TFK_POS_STRIDE * real_bytes;
+  return L;
 }
 
 #if !defined(__CUDACC_RTC__)

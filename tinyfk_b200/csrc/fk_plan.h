@@ -57,6 +57,9 @@ enum {
   SF_INV_BEFORE = 1,  // GetInverse(parent.q) is not in the running `inv` yet and the translation needs it
   SF_INV_AFTER = 2,   // GetInverse(cur.q) is needed after the slot (joint record) and is not valid yet
   SF_PRISM_OQ = 4,    // prismatic behind a rotated origin: local.p = oquat * (axis*d) * oinv + opos
+  SF_LEAF = 8,        // fixed link without needed children (sphere centre, tool frame, "_com" link) of a several-link
+                      // plan: its pose is computed on the side and the running frame stays its parent's, so siblings
+                      // need no branch-point frame (same arithmetic per link; only the bookkeeping differs)
 };
 
 struct PlanSlot {

@@ -21,10 +21,12 @@ struct Builder {
   std::vector<PlanSlot> slots;
   std::vector<int> parent_slot;   // per slot: slot of the parent link, -1 when the parent is the root
   int frames_live, frames_max;
+  bool leaf_mode; // several requested links: fixed leaves are computed on the side (SF_LEAF); the fused single-link
+                  // kernel returns the running frame as the link's pose and keeps the plain order
 
   Builder(const KinematicModel &model, const PlanKey &k)
       : m(model), key(k), needed(model.n_links(), 0), qcol_of_joint(model.n_joints(), -1),
-        slot_of_link(model.n_links(), -1), frames_live(0), frames_max(0) {}
+        slot_of_link(model.n_links(), -1), frames_live(0), frames_max(0), leaf_mode(k.elink_ids.size() > 1) {}
 
   static int vclass(double x, double y, double z) {
     const int nz = (x != 0.0) + (y != 0.0) + (z != 0.0);
@@ -97,10 +99,19 @@ struct Builder {
     s.axis[2] = l.axis.z;
     classify(s);
 
-    int n_children = 0;
-    for (int c : l.children)
-      if (needed[c]) ++n_children;
-    if (n_children >= 2) {
+    // needed children: fixed leaves first (computed on the side, SF_LEAF: they leave the running frame alone), then
+    // the subtrees; only a link with two or more SUBTREES has to keep its frame
+    std::vector<int> leaves, inner;
+    for (int c : l.children) {
+      if (!needed[c]) continue;
+      bool has_needed_child = false;
+      for (int g : m.links()[c].children)
+        if (needed[g]) has_needed_child = true;
+      const LinkRec &lc = m.links()[c];
+      const bool driven = lc.jid >= 0 && qcol_of_joint[lc.jid] >= 0;
+      (leaf_mode && !has_needed_child && !driven ? leaves : inner).push_back(c);
+    }
+    if (inner.size() >= 2) {
       s.frame_st = frames_live++;
       if (frames_live > frames_max) frames_max = frames_live;
     }
@@ -108,9 +119,12 @@ struct Builder {
     slots.push_back(s);
     parent_slot.push_back(l.parent >= 0 ? slot_of_link[l.parent] : -1);
     const int my_frame = s.frame_st;
+    for (int c : leaves) {
+      visit(c, FRAME_RUNNING);
+      slots[slot_of_link[c]].flags |= SF_LEAF;
+    }
     bool first = true;
-    for (int c : l.children) {
-      if (!needed[c]) continue;
+    for (int c : inner) {
       visit(c, first ? (int)FRAME_RUNNING : my_frame);
       first = false;
     }
@@ -194,6 +208,7 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
         if (!valid) sl.flags |= SF_INV_BEFORE;
         valid = true;
       }
+      if (sl.flags & SF_LEAF) continue; // computed on the side: the running frame (and its inverse) stay the parent's
       if (sl.rot != ROT_NONE) valid = false;
       if (sl.arec >= 0) {
         if (!valid) sl.flags |= SF_INV_AFTER;
