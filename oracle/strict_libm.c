@@ -28,5 +28,6 @@ void tfkm_sincos_v(const double *x, double *s, double *c, long n) { for (long i 
 /* SIMT-restructured variants (tinyfk_b200/csrc/fkmath_simt.h): must be bit-identical to the above */
 #include "../tinyfk_b200/csrc/fkmath_simt.h"
 void tfkm_sincos_simt_v(const double *x, double *s, double *c, long n) { for (long i = 0; i < n; ++i) { TfkSinCos r = tfk_sincos_simt(x[i]); s[i] = r.s; c[i] = r.c; } }
+void tfkm_sincos2_simt_v(const double *xa, const double *xb, double *sa, double *ca, double *sb, double *cb, long n) { for (long i = 0; i < n; ++i) { TfkSinCos2 r = tfk_sincos2_simt(xa[i], xb[i]); sa[i] = r.a.s; ca[i] = r.a.c; sb[i] = r.b.s; cb[i] = r.b.c; } }
 void tfkm_asin_simt_v(const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_asin_simt(x[i]); }
 void tfkm_atan2_simt_v(const double *y, const double *x, double *o, long n) { for (long i = 0; i < n; ++i) o[i] = tfk_atan2_simt(y[i], x[i]); }

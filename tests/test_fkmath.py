@@ -118,6 +118,17 @@ def test_simt_variants_are_bit_identical(lib):
     nn = ~np.isnan(s0)
     assert _bits_equal(s0[nn], s1[nn]) and _bits_equal(c0[nn], c1[nn]) and np.isnan(s1[~nn]).all() and np.isnan(c1[~nn]).all()
 
+    # two arguments at once (tfk_sincos2_simt: what the plan-specialised walk calls for pairs of joints), every
+    # argument paired with an unrelated one so that rare inputs meet ordinary ones on both sides
+    xb = np.roll(x, 12345)
+    sa, ca, sb, cb = (np.empty_like(x) for _ in range(4))
+    lib.tfkm_sincos2_simt_v(x.ctypes.data_as(_dp), xb.ctypes.data_as(_dp), sa.ctypes.data_as(_dp), ca.ctypes.data_as(_dp),
+                            sb.ctypes.data_as(_dp), cb.ctypes.data_as(_dp), ctypes.c_long(x.size))
+    assert _bits_equal(s0[nn], sa[nn]) and _bits_equal(c0[nn], ca[nn]) and np.isnan(sa[~nn]).all() and np.isnan(ca[~nn]).all()
+    nb = np.roll(nn, 12345)
+    assert _bits_equal(np.roll(s0, 12345)[nb], sb[nb]) and _bits_equal(np.roll(c0, 12345)[nb], cb[nb])
+    assert np.isnan(sb[~nb]).all() and np.isnan(cb[~nb]).all()
+
     x = np.concatenate([rng.uniform(-1, 1, n), rng.uniform(0.9, 1.0, n // 4), -rng.uniform(0.4, 0.6, n // 4),
                         rng.normal(size=n // 4) * 10.0 ** rng.integers(-12, 0, n // 4), sp])
     a0, a1 = _call1(lib, "tfkm_asin_v", x), _call1(lib, "tfkm_asin_simt_v", x)

@@ -463,14 +463,14 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
       for (int in_smem = 1; in_smem >= 0 && !found; --in_smem)
         for (int sub = 32; sub >= 8 && !found; sub >>= 1) {
           if (in_smem && std::getenv("TFK_NO_SMEM_HOT")) continue;
-          const SmemLayout Lp = smem_layout_pos(plan_bytes, h->n_in, h->n_lrec, sub, in_smem ? n_crec : 0, rb);
+          const SmemLayout Lp = smem_layout_pos(plan_bytes, h->n_in, h->n_lrec, h->n_out, sub, in_smem ? n_crec : 0, rb);
           if (3 * (Lp.total + 1024) > 227 * 1024) continue;
           found = true;
           L = Lp;
           pos_sub = sub;
           variant = in_smem ? KV_POS_SMEM : KV_POS;
           rec_stride = TFK_POS_STRIDE;
-          rec_reals = h->rec_size + (in_smem ? 0 : n_crec);
+          rec_reals = h->off_lrec + (in_smem ? 0 : n_crec); // link positions go straight into P
         }
     }
   }

@@ -292,6 +292,14 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
                        int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
+#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR)
+    // Plan-specialised build: the slot loop is unrolled over a compile-time plan, so "is there a second revolute
+    // joint ahead" folds.  Revolute joints are taken in pairs: the first one's slot evaluates sin/cos of BOTH half
+    // angles in one call (M::sincos2_: two independent chains that interleave), the second one's slot uses the
+    // kept pair.  Same operations per angle, same bits.
+    T sn_kept = T(0), cs_kept = T(0);
+    bool kept = false;
+#endif
     TFK_PLAN_LOOP
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
@@ -341,7 +349,25 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
         } else {
           // Joint::transform for REVOLUTE/CONTINUOUS, joint.h:231-240 (axis is NOT normalised)
           T sn, cs;
+#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR)
+          if (kept) {
+            sn = sn_kept, cs = cs_kept;
+            kept = false;
+          } else {
+            int nx = -1;
+            TFK_UNROLL
+            for (int t = h.n_slots - 1; t > s; --t)
+              if (pv.slots[t].rot >= ROT_REV) nx = t;
+            if (nx >= 0) {
+              M::sincos2_(ang * T(0.5), qrow[pv.slots[nx].qcol] * T(0.5), &sn, &cs, &sn_kept, &cs_kept);
+              kept = true;
+            } else {
+              M::sincos_(ang * T(0.5), &sn, &cs);
+            }
+          }
+#else
           M::sincos_(ang * T(0.5), &sn, &cs);
+#endif
           V ax;
           ax.x = T(sl.axis[0]), ax.y = T(sl.axis[1]), ax.z = T(sl.axis[2]);
           if (sl.rot == ROT_REV)
@@ -618,16 +644,21 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   // or a second one biased so that the absolute offsets h.off_lrec + .. still apply: fk_twophase_kernel)
   static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, int stride) { phase_a(pv, qrow, rec, rec, stride); }
   static TFK_FN void phase_a(const PlanView &pv, const T *qrow, T *rec, T *rec_link, int stride) {
+    StoreLinks sink;
+    sink.h = pv.h;
+    sink.rec = rec_link;
+    sink.stride = stride;
+    phase_a_sink(pv, qrow, rec, rec_link, stride, sink);
+  }
+  // the same with the caller's link sink (fk_pos_kernel writes link positions straight into P)
+  template <class LinkSink>
+  static TFK_FN void phase_a_sink(const PlanView &pv, const T *qrow, T *rec, T *rec_f, int stride, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
     put_pose(rec, stride, h.off_base, base);
     if (h.off_arec - h.off_base > 7) store_base_ctx(h, base, rec, stride); // Jacobian with a moving base
-    StoreLinks sink;
-    sink.h = &h;
-    sink.rec = rec_link;
-    sink.stride = stride;
     if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
-    walk<true>(pv, qrow, rec, rec_link, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
+    walk<true>(pv, qrow, rec, rec_f, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);
   }
 
   // two-phase driver, phase B: one thread per (configuration, requested link)
@@ -636,17 +667,24 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   }
   template <class OutSink>
   static TFK_FN void phase_b(const PlanView &pv, const T *rec, const T *rec_link, int stride, int o, OutSink &out) {
-    const PlanHeader &h = *pv.h;
-    const int lat = h.off_lrec + pv.lrec_of_out[o] * LREC;
+    phase_b(pv, rec, load_link(pv, rec_link, o), o, out);
+  }
+  // the pose phase A recorded for output o (the kernel loads the NEXT item's while it works on the current one)
+  static TFK_FN P load_link(const PlanView &pv, const T *rec_link, int o) {
+    const int lat = pv.h->off_lrec + pv.lrec_of_out[o] * LREC;
     P e;
-    e.p = get_vec(rec_link, stride, lat);
+    e.p = get_vec(rec_link, STRIDE, lat);
     e.q = O::qidentity();
-    if (LREC == 7) e.q = get_quat(rec_link, stride, lat + 3);
+    if (LREC == 7) e.q = get_quat(rec_link, STRIDE, lat + 3);
+    return e;
+  }
+  template <class OutSink> static TFK_FN void phase_b(const PlanView &pv, const T *rec, const P &e, int o, OutSink &out) {
+    const PlanHeader &h = *pv.h;
     BaseFromRec bs;
     bs.rec = rec;
-    bs.stride = stride;
+    bs.stride = STRIDE;
     bs.at = h.off_base;
-    emit_link(pv, e, o, rec, stride, h.off_arec, h.off_prec, bs, out);
+    emit_link(pv, e, o, rec, STRIDE, h.off_arec, h.off_prec, bs, out);
   }
 
   // ---------------------------------------------------------------------------------------------

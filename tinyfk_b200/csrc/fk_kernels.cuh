@@ -274,24 +274,39 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
 }
 
 // Several links, RotationType IGNORE (collision-sphere centres + 3 x n position Jacobians: the store-bound shape,
-// BASELINE cfg4).  Phase A as in fk_twophase_kernel (all plan records in the block-private scratch, [k][TILE + 1]).
-// Each thread then copies its configuration's joint records into COLUMN ORDER, crec[6c + 0..2] = world axis of
-// column c's joint, crec[6c + 3..5] = its position (shared memory when three blocks fit, else scratch), which
-// takes the plan's (axis record, position record) indirection out of phase B.  Phase B has no per-(configuration,
-// link) interpreter: every thread owns one ENTRY of a Jacobian column (configuration il, link o, row r; consecutive
-// threads = consecutive addresses, plain coalesced streaming stores, no staging strip, no warp barrier) and walks
-// the columns with it at a constant record stride: four record reads, five FP64 operations, one select and one
-// store per entry (same products in the same order as FkCore::emit_link).  Only the finite-difference
-// base-rotation columns (moving base) are produced per (configuration, link) through the staged sink.
+// BASELINE cfg4).
+//   Phase A: thread per configuration, as fk_twophase_kernel, except that link positions are written STRAIGHT INTO P
+//   (they are output anyway; the partial sectors merge in L2) and the joint records into the block's scratch
+//   ([k][TILE + 1]); the thread then copies its joint records into COLUMN ORDER, crec[6c + 0..2] = world axis of
+//   column c's joint, crec[6c + 3..5] = its position (shared memory when three blocks fit, else scratch), which
+//   takes the plan's (axis record, position record) indirection out of phase B.
+//   Phase B, in sub-tiles of `sub` configurations: their rows of P (contiguous) are read back from L2 into shared
+//   memory, then every thread owns one ENTRY of a Jacobian column (configuration il, link o, row r; consecutive
+//   threads = consecutive addresses, plain coalesced streaming stores, no staging strip, no warp barrier) and walks
+//   the columns with it at a constant record stride: four record reads, five FP64 operations, one select and one
+//   store per entry (same products in the same order as FkCore::emit_link).  Only the finite-difference
+//   base-rotation columns (moving base) are produced per (configuration, link) through the staged sink.
+template <class T> struct PosLinkSink { // FkCore::walk's link sink: positions of the link's outputs, into P
+  T *P;            // P + (row of this configuration) * n_out
+  long long ldP;
+  const int *first_out, *next_out; // outputs that name link record l: first_out[l], next_out[o], ... -1
+  template <class Pose> __device__ __forceinline__ void link(int lrec, const Pose &cur) const {
+    for (int o = first_out[lrec]; o >= 0; o = next_out[o]) {
+      P[o] = cur.p.x;
+      P[ldP + o] = cur.p.y;
+      P[2 * ldP + o] = cur.p.z;
+    }
+  }
+};
+
 template <class Core, bool SMEM_CREC>
-__global__ void __launch_bounds__(TFK_TILE, 4) fk_pos_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+__global__ void __launch_bounds__(TFK_TILE, 3) fk_pos_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
   typedef typename Core::T T;
   enum { S = Core::REC_STRIDE };
   static_assert(S == TFK_POS_STRIDE, "fk_pos_kernel wants the [k][TILE + 1] record layout");
   extern __shared__ __align__(16) unsigned char smem[];
   for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
     *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
-  __syncthreads();
   const PlanHeader &h = pp.h;
   PlanView pv;
   pv.h = &pp.h;
@@ -300,17 +315,28 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_pos_kernel(const KernelArgs a,
   pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
   pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
   const int n_out = h.n_out, n_cols = h.n_cols;
+  int *first_out = reinterpret_cast<int *>(smem + ((a.table_bytes + 15) & ~15)), *next_out = first_out + h.n_lrec;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int l = 0; l < h.n_lrec; ++l) first_out[l] = -1;
+    for (int o = n_out - 1; o >= 0; --o) {
+      const int l = pv.lrec_of_out[o];
+      next_out[o] = first_out[l];
+      first_out[l] = o;
+    }
+  }
+  __syncthreads();
   const int n_crec = h.with_jacobian ? 6 * n_cols : 0;
-  const SmemLayout L = smem_layout_pos(a.table_bytes, h.n_in, h.n_lrec, a.sub_cfg, SMEM_CREC ? n_crec : 0, (int)sizeof(T));
+  const int sub = a.sub_cfg, lpitch = pos_lpitch(sub, n_out);
+  const SmemLayout L = smem_layout_pos(a.table_bytes, h.n_in, h.n_lrec, n_out, sub, SMEM_CREC ? n_crec : 0, (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * S * (h.rec_size + (SMEM_CREC ? 0 : n_crec));
-  T *crec = SMEM_CREC ? reinterpret_cast<T *>(smem + L.rec_off) : rec + (size_t)S * h.rec_size;
+  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * S * (h.off_lrec + (SMEM_CREC ? 0 : n_crec));
+  T *crec = SMEM_CREC ? reinterpret_cast<T *>(smem + L.rec_off) : rec + (size_t)S * h.off_lrec;
   const T *q = static_cast<const T *>(a.q);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n_trans = h.base_type == 0 ? 0 : (h.base_type == 1 ? 2 : 3);
   const long long ldP = a.ld_cfg * n_out, ldJ = ldP * 3;
-  const unsigned d3 = 3u * (unsigned)n_out;
-  const unsigned m_out = 0xffffffffu / (unsigned)n_out + 1u, m_d3 = 0xffffffffu / d3 + 1u; // x / d == umulhi(x, m) for x*d < 2^32, d > 1
+  const unsigned m_out = n_out > 1 ? 0xffffffffu / (unsigned)n_out + 1u : 0u; // x / d == umulhi(x, m) for x*d < 2^32, d > 1
   unsigned long long prism = 0ull; // columns of prismatic joints (src/kinematics.cpp:149-151): J = axis
   for (int c = 0; c < n_cols; ++c)
     if (pp.cols[c].prismatic) prism |= 1ull << c;
@@ -325,12 +351,19 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_pos_kernel(const KernelArgs a,
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long i0 = tile * TFK_TILE;
     const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    const long long hbase = (a.row0 + i0) * n_out;
+    T *Pt = static_cast<T *>(a.P) + hbase;
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
     __syncthreads();
     if ((int)threadIdx.x < nv) {
       T *mine = rec + threadIdx.x;
-      Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, mine, mine, S);
+      PosLinkSink<T> sink;
+      sink.P = Pt + (long long)threadIdx.x * n_out;
+      sink.ldP = ldP;
+      sink.first_out = first_out;
+      sink.next_out = next_out;
+      Core::phase_a_sink(pv, qs + threadIdx.x * L.q_pitch, mine, mine, S, sink);
       T *cr = crec + threadIdx.x;
       TFK_NOUNROLL
       for (int c = 0; c < n_crec / 6; ++c) { // joint records -> column order (a column no link depends on keeps zeros)
@@ -348,86 +381,67 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_pos_kernel(const KernelArgs a,
         for (int k = 0; k < 6; ++k) cr[(6 * c + k) * S] = v[k];
       }
     }
-    __syncthreads();
-    const int items = nv * n_out;
-    const long long hbase = (a.row0 + i0) * n_out;
-    // Phase B in sub-tiles of `sub` configurations: their link positions are pulled out of the scratch with
-    // coalesced loads into lps[3*n_lrec][sub + 1] (shared memory, aliases the dead q tile), so that lanes that
-    // differ in (link, row) read conflict-free from shared memory instead of one L2 sector each.
-    const int sub = a.sub_cfg, sub_sh = 31 - __clz(sub), lpitch = sub + 1;
-    const int n_lrow = 3 * h.n_lrec;
-    for (int s0 = 0; s0 < nv; s0 += sub) {
-      const int ns = nv - s0 < sub ? nv - s0 : sub;
-      __syncthreads(); // the q tile / the previous sub-tile's positions are dead
-      for (int idx = threadIdx.x; idx < (n_lrow << sub_sh); idx += TFK_TILE) {
-        const int row = idx >> sub_sh, l = idx & (sub - 1);
-        if (l < ns) qs[row * lpitch + l] = rec[(h.off_lrec + row) * S + s0 + l];
-      }
-      __syncthreads();
-      const int sitems = ns * n_out;
-      { // P: one thread per (configuration, link), three coalesced column stores
-        T *Pt = static_cast<T *>(a.P) + hbase + (long long)s0 * n_out;
-        for (int it = threadIdx.x; it < sitems; it += TFK_TILE) {
-          const int il = (int)__umulhi((unsigned)it, m_out);
-          const int o = it - il * n_out;
-          const T *lp = qs + pv.lrec_of_out[o] * 3 * lpitch + il;
-          __stcs(Pt + it, lp[0]);
-          __stcs(Pt + ldP + it, lp[lpitch]);
-          __stcs(Pt + 2 * ldP + it, lp[2 * lpitch]);
+    if (h.with_jacobian) {
+      const int items = nv * n_out;
+      for (int s0 = 0; s0 < nv; s0 += sub) {
+        const int ns = nv - s0 < sub ? nv - s0 : sub;
+        const int sitems = ns * n_out;
+        __syncthreads(); // phase A's stores are visible; the q tile / the previous sub-tile's positions are dead
+        for (int d = 0; d < 3; ++d) { // the sub-tile's rows of P are contiguous: coalesced copy (L2 hits)
+          const T *src = Pt + d * ldP + (long long)s0 * n_out;
+          for (int k = threadIdx.x; k < sitems; k += TFK_TILE) qs[d * lpitch + k] = src[k];
         }
-      }
-      if (h.with_jacobian) {
+        __syncthreads();
         T *Jt = static_cast<T *>(a.J) + (hbase + (long long)s0 * n_out) * 3;
         const int entries = sitems * 3;
         for (int e = threadIdx.x; e < entries; e += TFK_TILE) {
-          const int il = (int)__umulhi((unsigned)e, m_d3);
-          const int rem = e - il * (int)d3;
-          const int o = (int)__umulhi((unsigned)rem, 0x55555556u); // rem / 3
-          const int r = rem - 3 * o;
+          const int item = (int)__umulhi((unsigned)e, 0x55555556u); // e / 3
+          const int r = e - 3 * item;
+          const int il = (int)__umulhi((unsigned)item, m_out);
+          const int o = item - il * n_out;
           const int r1 = r == 2 ? 0 : r + 1, r2 = r == 0 ? 2 : r - 1;
-          const T *lp = qs + pv.lrec_of_out[o] * 3 * lpitch + il;
-          const T p1 = lp[r1 * lpitch], p2 = lp[r2 * lpitch];
+          const T p1 = qs[r1 * lpitch + item], p2 = qs[r2 * lpitch + item];
           const T *cc = crec + s0 + il;
-          const T *c0 = cc + r * S, *c1 = cc + r1 * S, *c2 = cc + r2 * S;
+          const T *c1 = cc + r1 * S, *c2 = cc + r2 * S;
           const uint32_t *mk = pv.masks + o * h.mask_words;
           T *pj = Jt + e;
           for (int cb = 0; cb < n_cols; cb += 32) {
-            const uint32_t m = mk[cb >> 5], pm = (uint32_t)(prism >> cb);
+            const uint32_t m = mk[cb >> 5];
             const int ce = n_cols - cb < 32 ? n_cols - cb : 32;
-#pragma unroll 4
+#pragma unroll 8
             for (int c = 0; c < ce; ++c) {
               // (axis x (p - pos))_r = a[r1]*d[r2] - a[r2]*d[r1]: urdf::cross_product, pose.cpp:90-94, component r
               const T a1 = c1[0], a2 = c2[0];
               const T d1 = p1 - c1[3 * S], d2 = p2 - c2[3 * S];
               T v = a1 * d2 - a2 * d1;
-              if ((pm >> c) & 1u) v = c0[0]; // uniform
               v = ((m >> c) & 1u) ? v : T(0); // the joint does not move this link (include/tinyfk.hpp:31-46)
               __stcs(pj, v);
               pj += ldJ;
-              c0 += 6 * S, c1 += 6 * S, c2 += 6 * S;
+              c1 += 6 * S, c2 += 6 * S;
             }
           }
           for (int k = 0; k < n_trans; ++k) { // base translation columns, src/kinematics.cpp:194-196
             __stcs(pj, r == k ? T(1) : T(0));
             pj += ldJ;
           }
+          for (unsigned long long pb = prism; pb; pb &= pb - 1) { // prismatic joints: the column is the axis itself
+            const int c = __ffsll((long long)pb) - 1;
+            const T v = ((mk[c >> 5] >> (c & 31)) & 1u) ? cc[(6 * c + r) * S] : T(0);
+            __stcs(Jt + e + c * ldJ, v);
+          }
         }
       }
-    }
-    if (h.with_jacobian) {
       __syncthreads(); // the last sub-tile's positions are dead: the strips below alias them
       if (h.base_type != 0) { // base rotation columns: one thread per (configuration, link), staged stores
         for (int it0 = warp * 32; it0 < items; it0 += TFK_TILE) {
           const int it = it0 + lane;
           const int itc = it < items ? it : items - 1;
           const int il = (int)__umulhi((unsigned)itc, m_out);
-          const int o = itc - il * n_out;
           fac.nvalid = items - it0 < 32 ? items - it0 : 32;
           fac.head0 = hbase + it0;
           StagedSink<T, 3> out = fac.make();
-          const T *lp = rec + (h.off_lrec + pv.lrec_of_out[o] * 3) * S + il;
           typename Core::V ep;
-          ep.x = lp[0], ep.y = lp[S], ep.z = lp[2 * S];
+          ep.x = Pt[itc], ep.y = Pt[ldP + itc], ep.z = Pt[2 * ldP + itc];
           Core::emit_base_rot_pos(pv, ep, rec + il, out);
         }
       }

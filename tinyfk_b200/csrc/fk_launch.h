@@ -87,11 +87,13 @@ TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem,
 // fk_pos_kernel: records are [k][TFK_TILE + 1] (odd pitch: a warp reading three consecutive elements of ONE
 // configuration hits three banks, and one element of 32 configurations hits 32)
 enum { TFK_POS_STRIDE = TFK_TILE + 1 };
-// shared memory: [per-output tables | q tile, later the sub-tile's link positions [3*n_lrec][sub + 1], later the warps'
-// staging strips | column-ordered joint records (or none)]
-TFK_HDI SmemLayout smem_layout_pos(int table_bytes, int n_in, int n_lrec, int sub, int rec_reals_in_smem, int real_bytes) {
-  SmemLayout L = smem_layout_tile(TFK_TILE, table_bytes, n_in, 0, real_bytes);
-  const int lps = (3 * n_lrec * (sub + 1) * real_bytes + 15) & ~15;
+// shared memory: [per-output tables | outputs of every link record (first_out[n_lrec], next_out[n_out]) | q tile, later
+// the sub-tile's link positions [3][sub*n_out | 1], later the warps' staging strips | column-ordered joint records (or none)]
+TFK_HDI int pos_lpitch(int sub, int n_out) { return (sub * n_out) | 1; }
+TFK_HDI SmemLayout smem_layout_pos(int table_bytes, int n_in, int n_lrec, int n_out, int sub, int rec_reals_in_smem, int real_bytes) {
+  const int tb = ((table_bytes + 15) & ~15) + (((n_lrec + n_out) * 4 + 15) & ~15);
+  SmemLayout L = smem_layout_tile(TFK_TILE, tb, n_in, 0, real_bytes);
+  const int lps = (3 * pos_lpitch(sub, n_out) * real_bytes + 15) & ~15;
   if (L.rec_off - L.q_off < lps) L.rec_off = L.q_off + lps;
   L.total = L.rec_off + rec_reals_in_smem * TFK_POS_STRIDE * real_bytes;
   return L;

@@ -73,6 +73,16 @@ struct MathPortable {
     *c = r.c;
   }
 #endif
+  // two arguments at once (fkmath_simt.h: the two evaluations interleave; same bits as two sincos_ calls)
+#if defined(__CUDACC__)
+  static __host__ __device__ __noinline__ TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
+#else
+  static inline TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
+#endif
+  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
+    const TfkSinCos2 r = sincos2_call_(xa, xb);
+    *sa = r.a.s, *ca = r.a.c, *sb = r.b.s, *cb = r.b.c;
+  }
   static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
   static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
   static TFK_FN double atan2_rare_(double y, double x) { return tfk_atan2(y, x); } // same bits, out of line
@@ -172,6 +182,10 @@ struct MathNative64 {
     *c = ::cos(x);
 #endif
   }
+  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
+    sincos_(xa, sa, ca);
+    sincos_(xb, sb, cb);
+  }
   static TFK_FN double asin_(double x) { return ::asin(x); }
   static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
   static TFK_FN double atan2_rare_(double y, double x) { return ::atan2(y, x); }
@@ -201,6 +215,10 @@ struct MathNative32 {
     *s = ::sinf(x);
     *c = ::cosf(x);
 #endif
+  }
+  static TFK_FN void sincos2_(float xa, float xb, float *sa, float *ca, float *sb, float *cb) {
+    sincos_(xa, sa, ca);
+    sincos_(xb, sb, cb);
   }
   static TFK_FN float asin_(float x) { return ::asinf(x); }
   static TFK_FN float atan2_(float y, float x) { return ::atan2f(y, x); }

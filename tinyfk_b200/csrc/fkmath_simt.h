@@ -175,6 +175,66 @@ TFK_HD TfkSinCos tfk_sincos_simt(double x) {
   return out;
 }
 
+/* sin and cos of TWO arguments at once: the two evaluations are independent dependency chains, and written as one
+   straight-line body (selects instead of the `small` branch, one shared test for the rare inputs) the compiler
+   interleaves them -- twice the instruction-level parallelism for a thread whose next step needs both (the walk
+   down a kinematic chain knows every joint angle up front).  Same operations per argument as tfk_sincos_simt:
+   bit-identical results. */
+typedef struct {
+  TfkSinCos a, b;
+} TfkSinCos2;
+
+TFK_HD TfkSinCos2 tfk_sincos2_simt(double xa, double xb) {
+  TfkSinCos2 out;
+  const int32_t hxa = tfk_hi32(xa) & 0x7fffffff, hxb = tfk_hi32(xb) & 0x7fffffff;
+  if (TFK_UNLIKELY((hxa >= 0x41392000) | (hxb >= 0x41392000))) { /* |x| >= ~1.64e6, inf, nan: rare */
+    out.a = tfk_sincos_simt(xa);
+    out.b = tfk_sincos_simt(xb);
+    return out;
+  }
+  const double ta = fabs(xa), tb = fabs(xb);
+  const int smalla = tfk_abs_bits(xa) <= 0x3fe921fb54442d18ull, smallb = tfk_abs_bits(xb) <= 0x3fe921fb54442d18ull;
+  int na = (int)(ta * TFK_KC(invpio2, TFK_INVPIO2) + 0.5), nb = (int)(tb * TFK_KC(invpio2, TFK_INVPIO2) + 0.5);
+  const double fna = (double)na, fnb = (double)nb;
+  const double ra = ta - fna * TFK_KC(pio2_1, TFK_PIO2_1), rb = tb - fnb * TFK_KC(pio2_1, TFK_PIO2_1);
+  const double wa = fna * TFK_KC(pio2_1t, TFK_PIO2_1T), wb = fnb * TFK_KC(pio2_1t, TFK_PIO2_1T);
+  double a0a = ra - wa, a0b = rb - wb;
+  {
+    const int ia = ((hxa >> 20) & 0x7ff) - ((tfk_hi32(a0a) >> 20) & 0x7ff);
+    const int ib = ((hxb >> 20) & 0x7ff) - ((tfk_hi32(a0b) >> 20) & 0x7ff);
+    if (TFK_UNLIKELY((!smalla & (ia > 16)) | (!smallb & (ib > 16)))) { /* cancellation near a multiple of pi/2: rare */
+      out.a = tfk_sincos_simt(xa);
+      out.b = tfk_sincos_simt(xb);
+      return out;
+    }
+  }
+  double a1a = (ra - a0a) - wa, a1b = (rb - a0b) - wb;
+  if (smalla) {
+    na = 0;
+    a0a = ta;
+    a1a = 0.0;
+  }
+  if (smallb) {
+    nb = 0;
+    a0b = tb;
+    a1b = 0.0;
+  }
+  const int32_t sxa = tfk_hi32(xa), sxb = tfk_hi32(xb);
+  const double y0a = tfk_xor_sign(a0a, sxa), y0b = tfk_xor_sign(a0b, sxb);
+  const double y1a = tfk_xor_sign(a1a, smalla ? 0 : sxa), y1b = tfk_xor_sign(a1b, smallb ? 0 : sxb);
+  if (sxa < 0) na = -na;
+  if (sxb < 0) nb = -nb;
+  const double ksa = tfk_ksin_simt(y0a, y1a), kca = tfk_kcos_simt(y0a, y1a);
+  const double ksb = tfk_ksin_simt(y0b, y1b), kcb = tfk_kcos_simt(y0b, y1b);
+  double ssa = (na & 1) ? kca : ksa, cca = (na & 1) ? ksa : kca;
+  double ssb = (nb & 1) ? kcb : ksb, ccb = (nb & 1) ? ksb : kcb;
+  out.a.s = tfk_xor_sign(ssa, (int32_t)((uint32_t)na << 30));
+  out.a.c = tfk_xor_sign(cca, (int32_t)((uint32_t)(na + 1) << 30));
+  out.b.s = tfk_xor_sign(ssb, (int32_t)((uint32_t)nb << 30));
+  out.b.c = tfk_xor_sign(ccb, (int32_t)((uint32_t)(nb + 1) << 30));
+  return out;
+}
+
 TFK_HD double tfk_asin_pq_simt(double z, double *q) {
   *q = 1.0 + z * (TFK_KC(aq1, TFK_AQ1) + z * (TFK_KC(aq2, TFK_AQ2) + z * (TFK_KC(aq3, TFK_AQ3) + z * TFK_KC(aq4, TFK_AQ4))));
   return z * (TFK_KC(ap0, TFK_AP0) +

@@ -1,0 +1,15 @@
+mkdir -p gpurun_out
+( time python -m pytest tests -m gpu -x -q ) 2>&1 | tail -6 > gpurun_out/t.log
+cat gpurun_out/t.log
+: > gpurun_out/b.log
+python bench.py --no-cpu-baseline --no-e2e >> gpurun_out/b.log 2>&1
+for c in cfg3 cfg4 cfg5; do python bench.py --workload $c --no-cpu-baseline --no-e2e >> gpurun_out/b.log 2>&1; done
+python bench.py --workload cfg4 --precision fp32 --no-cpu-baseline --no-e2e >> gpurun_out/b.log 2>&1
+python - <<PY
+import json
+for l in open("gpurun_out/b.log"):
+    if l.startswith("{"):
+        d=json.loads(l); print(d["config"]["workload"][:40], d["dtype"], "%.3e"%d["value"], "%.4f ms"%d["ms_per_step"], "frac %.3f"%d["roofline"]["frac"], d["config"]["launch"])
+    else: print(l[:300])
+PY
+python tools/time_sqdists.py 2>&1 | grep "one arm" | tail -4
