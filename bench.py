@@ -233,10 +233,12 @@ def measured_peaks():
 # DMUL + DADD + DFMA + DSETP); an FP64 instruction occupies its scheduler's FP64 pipe for 2 cycles on B200
 # (tools/ubench/fp64_pipe.cu), which gives the kernel's FP64-pipe bound next to the HBM one
 NCU_FP64_PER_WARP = {
-    ("cfg2", "fp64", "spec"): 2140,     # profiles/r1_full_cfg2_strict_v9.txt (ncu: FP64 pipe 51 % active)
+    ("cfg2", "fp64", "spec"): 2140,     # profiles/r1_full_cfg2_strict_v10.txt (ncu: FP64 pipe 52 % active)
 }
 NCU_TRAFFIC_BYTES = {
-    ("cfg2", "fp64"): 578.0e6,  # profiles/r1_full_cfg2_strict_v9.txt: 84.0 MB read + 494.0 MB written (algorithmic 637.5 MB)
+    ("cfg2", "fp64"): 578.7e6,   # profiles/r1_full_cfg2_strict_v10.txt: 84.2 MB read + 494.5 MB written (algorithmic 637.5 MB)
+    ("cfg4", "fp64"): 3500.7e6,  # profiles/r1_full_cfg4_twophase_v10.txt: 36.0 MB read + 3464.6 MB written (algorithmic 3430.9 MB)
+    ("cfg5", "fp64"): 4030.8e6,  # profiles/r1_full_cfg5_twophase_v9.txt: 378.6 MB read + 3652.1 MB written (algorithmic 3471.3 MB)
 }
 
 
