@@ -289,7 +289,7 @@ def run_ours(args):
             si = model.specialize(lids, jids, rot, base, True, prec, wait=True)
             model.set_jit_mode(1)
             jit_note = "specialised on the plan in %.1f s%s" % (time.perf_counter() - t0, " (disk cache)" if si["from_cache"] else "")
-        except ValueError as e:  # several links: served by the two-phase kernel
+        except ValueError as e:  # tree too large for the unrolled build: the generic kernel serves the plan
             jit_note = "not applicable: %s" % e
         except RuntimeError as e:  # NVRTC missing: the generic kernel serves the plan
             jit_note = "unavailable: %s" % str(e).splitlines()[0]

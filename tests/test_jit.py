@@ -46,10 +46,52 @@ def test_specialisation_compiles_without_a_gpu_and_is_cached(tmp_path):
     m2 = capi.Model(W.urdf_text("pr2.urdf"), host_libm=0)
     b = m2.specialize(l, j, 1, 1, True, 0, wait=True, compile_only=True)
     assert b["from_cache"] == 1 and b["cubin_bytes"] == a["cubin_bytes"]
-    # several links: not a plan the fused kernel serves
+    # several links: the two-phase kernel is specialised (128-thread blocks)
     l2 = list(m.get_link_ids(["r_gripper_tool_frame", "r_elbow_flex_link"]))
+    c = m.specialize(l2, j, 0, 1, True, 0, wait=True, compile_only=True)
+    assert c["state"] == 2 and c["block"] == 128 and c["cubin_bytes"] > 10000
+    c = m.specialize(l2, j, 1, 1, True, 1, wait=True, compile_only=True)  # orientation rows: FP32 mode only
+    assert c["state"] == 2 and c["block"] == 128
     with pytest.raises(ValueError):
         m.specialize(l2, j, 1, 1, True, 0, wait=True, compile_only=True)
+    # more joints than the unrolled build takes
+    with pytest.raises(ValueError):
+        m.specialize(l2, list(range(m.n_joints)), 1, 1, True, 0, wait=True, compile_only=True)
+
+
+MULTI = [  # workload (BASELINE config), base override, jac, precision
+    ("cfg4", None, True, 0), ("cfg4", 2, True, 0), ("cfg4", 1, False, 0), ("cfg5", None, True, 1), ("cfg5", 1, True, 1),
+    ("cfg4", None, True, 1),
+]
+
+
+@pytest.mark.gpu
+@needs_nvrtc
+@pytest.mark.parametrize("cfg,base_o,jac,prec", MULTI)
+def test_gpu_specialised_two_phase_kernel_bit_for_bit(cfg, base_o, jac, prec):
+    """several links (Fetch spheres, PR2 50 links): the plan-specialised two-phase kernel against the generic one and
+    against the oracle; 333 configurations = ragged tail tile"""
+    import parity
+    pair = parity.Pair(W.CONFIGS[cfg][0], strict=True)
+    jids, lids, rot, base = pair.setup(cfg)
+    base = base if base_o is None else base_o
+    m = pair.prod
+    q = W.sample_q(m.get_joint_limits(jids), base, 333, seed=9, wide_pitch=True)
+    m.set_jit_mode(0)
+    P0, J0 = m.solve_fk(q, lids, jids, rot, base, jac, precision=prec)
+    assert m.last_launch_info()["kernel"].startswith("fk_twophase_kernel")
+    m.set_jit_mode(1)
+    info = m.specialize(lids, jids, rot, base, jac, prec, wait=True)
+    assert info["state"] == 3 and info["block"] == 128
+    P1, J1 = m.solve_fk(q, lids, jids, rot, base, jac, precision=prec)
+    Pr, Jr = pair.oracle_solve(q, lids, jids, rot, base, jac)
+    assert m.last_launch_info()["kernel"] == "tfk_spec_kernel (plan-specialised fk_twophase_kernel, NVRTC)"
+    if prec == 0:
+        assert np.array_equal(P0, P1) and (not jac or np.array_equal(J0, J1))
+        parity.assert_bitwise(P1, J1 if jac else P1, Pr, Jr if jac else Pr, cfg + " specialised two-phase")
+    else:  # FP32 mode: positions within 1e-5 of the oracle; against the generic FP32 kernel only contraction differs
+        assert np.abs(P0 - P1).max() < 1e-5 and (not jac or np.abs(J0 - J1).max() < 1e-4)
+        assert np.abs(P1[:, :3] - Pr[:, :3]).max() < 1e-5
 
 
 @pytest.mark.gpu

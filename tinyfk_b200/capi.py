@@ -352,7 +352,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 9: "fk_sqdist_kernel<joint records in shared memory>", 8: "fk_twophase_kernel<joint records in shared memory>", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)", 10: "fk_pos_kernel", 11: "fk_pos_kernel<column-ordered joint records in shared memory>"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 9: "fk_sqdist_kernel<joint records in shared memory>", 8: "fk_twophase_kernel<joint records in shared memory>", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)", 12: "tfk_spec_kernel (plan-specialised fk_twophase_kernel, NVRTC)", 10: "fk_pos_kernel", 11: "fk_pos_kernel<column-ordered joint records in shared memory>"}.get(k, "none")
         return d
 
 

@@ -93,11 +93,37 @@ Engine::SpecKernel::~SpecKernel() {
 }
 
 // ---- plan specialisation (jit.hpp) -------------------------------------------------------------------------------
-bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const {
+bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *kind, std::string *why) const {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
+  *kind = 0;
   if (h->n_out != 1) {
-    if (why) *why = "plan specialisation exists for one requested link (the fused kernel) only";
-    return false;
+    // several links: the two-phase kernel against this plan (same block shape and shared-memory rule as the generic
+    // launch: [base | arec | prec] in shared memory when three blocks fit)
+    if (h->n_slots > 128 || h->n_cols > 32) {
+      if (why) *why = "tree too large to unroll (more than 128 links or 32 joints)";
+      return false;
+    }
+    // measured (B200, profiles/README.md v10): FP32 gains 28 % (cfg4) with everything unrolled; strict FP64 gains 5 % on
+    // position-only requests (cfg4, walk kept rolled) and LOSES 12 % with orientation rows (cfg5: the unrolled RPY /
+    // finite-difference columns of 21 columns outgrow the instruction cache) -- those stay with the generic kernel
+    if (precision == PREC_F64_STRICT && h->rot_type != 0) {
+      if (why) *why = "several links with orientation rows in strict FP64: the generic two-phase kernel is faster";
+      return false;
+    }
+    const int rb = (int)real_size(precision);
+    const int table_bytes = (h->off_cols - h->off_outs + 15) & ~15;
+    const SmemLayout Lh = smem_layout(table_bytes, h->n_in, h->off_frame, rb);
+    const bool hot = 3 * (Lh.total + 1024) <= 227 * 1024 && !std::getenv("TFK_NO_SMEM_HOT");
+    const SmemLayout L = hot ? Lh : smem_layout(table_bytes, h->n_in, 0, rb);
+    if (L.total > 200 * 1024) {
+      if (why) *why = "plan too large for shared memory";
+      return false;
+    }
+    *tile = TFK_TILE;
+    *bps = hot ? 3 : 4;
+    *smem = L.total;
+    *kind = hot ? 2 : 1;
+    return true;
   }
   if (h->n_slots > 48 || h->n_cols > 32) {
     if (why) *why = "chain too long to unroll (more than 48 links or 32 joints)";
@@ -142,7 +168,7 @@ void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
       if (!(wait && sk.state == SPEC_COMPILING)) return;
     } else {
       std::string why;
-      if (!spec_eligible(e, precision, &sk.tile, &sk.bps, &sk.smem, &why)) throw std::invalid_argument(why);
+      if (!spec_eligible(e, precision, &sk.tile, &sk.bps, &sk.smem, &sk.kind, &why)) throw std::invalid_argument(why);
       if (!nvrtc_available(&why)) {
         sk.state = SPEC_FAILED;
         sk.error = why;
@@ -155,6 +181,7 @@ void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
       o.rot_type = h->rot_type;
       o.tile = sk.tile;
       o.blocks_per_sm = sk.bps;
+      o.kind = sk.kind;
       const std::string src = plan_to_source(e.blob);
       SpecKernel *p = &sk; // heap-allocated with the plan entry; its destructor joins this thread
       sk.worker = std::thread([p, src, o] {
@@ -260,6 +287,15 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
   const int64_t n_tiles = (a.n + sk.tile - 1) / sk.tile;
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
   KernelArgs args = a;
+  const PlanHeader *ph = reinterpret_cast<const PlanHeader *>(e.blob.data());
+  int rec_reals = ph->fz_size;
+  if (sk.kind != 0) { // two-phase: per-output tables and the block-private record scratch, sized for THIS grid
+    const int table_bytes = (ph->off_cols - ph->off_outs + 15) & ~15;
+    rec_reals = sk.kind == 2 ? ph->rec_size - ph->off_frame : ph->rec_size;
+    args.tables = plan_on_device(e, device, stream) + ph->off_outs;
+    args.table_bytes = table_bytes;
+    args.scratch = workspace(device, stream, (size_t)grid * sk.tile * (size_t)std::max(rec_reals, 1) * real_size(precision)).scratch;
+  }
   void *params[] = {&args};
   ck(cudaLaunchKernel(reinterpret_cast<const void *>(sk.kernel), dim3(grid), dim3(sk.tile), params, (size_t)sk.smem, stream), "launch (specialised kernel)");
   g_launches.fetch_add(1);
@@ -267,8 +303,8 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
   last_launch.block = sk.tile;
   last_launch.smem_bytes = sk.smem;
   last_launch.blocks_per_sm = it->second;
-  last_launch.rec_reals = reinterpret_cast<const PlanHeader *>(e.blob.data())->fz_size;
-  last_launch.variant = KV_FUSED_SPEC;
+  last_launch.rec_reals = rec_reals;
+  last_launch.variant = sk.kind == 0 ? KV_FUSED_SPEC : KV_TWOPHASE_SPEC;
   return true;
 }
 
@@ -474,7 +510,8 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
         }
     }
   }
-  if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5) && jit_mode != JIT_OFF) {
+  if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5 || variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM) && !ex &&
+      jit_mode != JIT_OFF) {
     KernelArgs sa = KernelArgs();
     sa.q = d_q;
     sa.n = n;

@@ -110,6 +110,7 @@ private:
     bool from_cache = false;
     std::thread worker;
     int tile = 0, bps = 0, smem = 0;
+    int kind = 0;      // jit.hpp SpecOptions::kind: 0 fused, 1 two-phase, 2 two-phase with the joint records in shared memory
     cudaLibrary_t lib = nullptr;
     cudaKernel_t kernel = nullptr;
     std::map<int, int> blocks_per_sm; // device -> occupancy (also marks the shared-memory attribute as set there)
@@ -123,7 +124,7 @@ private:
     SpecKernel spec[2];                       // by precision
     int64_t configs_served = 0;
   };
-  bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, std::string *why) const;
+  bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *kind, std::string *why) const;
   void spec_start(PlanEntry &e, int precision, bool wait);
   bool spec_launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const KernelArgs &a);
   struct Workspace { // one per (device, stream): concurrent launches never share records

@@ -34,10 +34,19 @@
 #else
 #define TFK_PLAN_LOOP _Pragma("unroll 1")
 #endif
+// the walk down the tree: unrolled with the plan for a single chain (fused kernel); a several-link plan keeps ONE copy
+// of the slot body (TFK_SPEC_ROLLED_WALK: 50-130 slots of straight-line code do not fit the instruction cache of an SM
+// whose 12-16 warps are spread over it -- measured slower than the generic kernel) and unrolls only the column loops
+#if defined(TFK_SPEC_PLAN) && !defined(TFK_SPEC_ROLLED_WALK)
+#define TFK_WALK_LOOP _Pragma("unroll")
+#else
+#define TFK_WALK_LOOP _Pragma("unroll 1")
+#endif
 #else
 #define TFK_UNROLL
 #define TFK_NOUNROLL
 #define TFK_PLAN_LOOP
+#define TFK_WALK_LOOP
 #endif
 
 namespace tfk {
@@ -292,7 +301,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
                        int o_frame, P cur, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     Q inv = O::qidentity(); // GetInverse(q of the frame the next rotation uses), valid where the plan says so
-#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR)
+#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR) && !defined(TFK_SPEC_ROLLED_WALK)
     // Plan-specialised build: the slot loop is unrolled over a compile-time plan, so "is there a second revolute
     // joint ahead" folds.  Revolute joints are taken in pairs: the first one's slot evaluates sin/cos of BOTH half
     // angles in one call (M::sincos2_: two independent chains that interleave), the second one's slot uses the
@@ -300,7 +309,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     T sn_kept = T(0), cs_kept = T(0);
     bool kept = false;
 #endif
-    TFK_PLAN_LOOP
+    TFK_WALK_LOOP
     for (int s = 0; s < h.n_slots; ++s) {
       const PlanSlot &sl = pv.slots[s];
       // SF_LEAF (several-link plans only): a fixed link without needed children is computed on the side -- the
@@ -349,7 +358,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
         } else {
           // Joint::transform for REVOLUTE/CONTINUOUS, joint.h:231-240 (axis is NOT normalised)
           T sn, cs;
-#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR)
+#if defined(TFK_SPEC_PLAN) && defined(TFK_SPEC_SINCOS_PAIR) && !defined(TFK_SPEC_ROLLED_WALK)
           if (kept) {
             sn = sn_kept, cs = cs_kept;
             kept = false;

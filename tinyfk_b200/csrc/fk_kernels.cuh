@@ -217,19 +217,18 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
 
 // SMEM_HOT: [base | arec | prec] (what every (configuration, link) item re-reads) live in shared memory and only the
 // branch-point frames and the link records go through the block-private scratch; otherwise all records do.
+// pv0: where the plan's header, slots and columns are (the kernel parameter, or the compile-time tables of a
+// plan-specialised build); the per-output tables (indexed per lane in phase B) are copied to shared memory either way.
 template <class Core, bool SMEM_HOT>
-__global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+__device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const PlanView &pv0) {
   typedef typename Core::T T;
   extern __shared__ __align__(16) unsigned char smem[];
   // per-output tables (indexed per lane in phase B) -> shared memory; everything else stays in the constant bank
   for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
     *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
   __syncthreads();
-  const PlanHeader &h = pp.h;
-  PlanView pv;
-  pv.h = &pp.h;
-  pv.slots = pp.slots;
-  pv.cols = pp.cols;
+  const PlanHeader &h = *pv0.h;
+  PlanView pv = pv0;
   pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
   pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
   const SmemLayout L = smem_layout(a.table_bytes, h.n_in, SMEM_HOT ? h.off_frame : 0, (int)sizeof(T));
@@ -272,6 +271,33 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
     __syncthreads();
   }
 }
+
+template <class Core, bool SMEM_HOT>
+__global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
+  PlanView pv;
+  pv.h = &pp.h;
+  pv.slots = pp.slots;
+  pv.cols = pp.cols;
+  pv.lrec_of_out = nullptr; // set by the body (shared memory)
+  pv.masks = nullptr;
+  fk_twophase_body<Core, SMEM_HOT>(a, pv);
+}
+
+#if defined(TFK_SPEC_PLAN)
+// Plan-specialised build of the two-phase kernel (several requested links): header, slots and columns are the
+// compile-time tables tfk::spec::k_*, so the walk of phase A and the column loops of phase B unroll into the
+// straight-line arithmetic of THIS robot/query; the per-output tables still come from a.tables.  Same source, same
+// compiler flags, same bits as the generic kernel.
+template <class Core, bool SMEM_HOT> __device__ __forceinline__ void fk_twophase_spec_body(const KernelArgs &a) {
+  PlanView pv;
+  pv.h = &spec::k_h;
+  pv.slots = spec::k_slots;
+  pv.cols = spec::k_cols;
+  pv.lrec_of_out = nullptr;
+  pv.masks = nullptr;
+  fk_twophase_body<Core, SMEM_HOT>(a, pv);
+}
+#endif
 
 // Several links, RotationType IGNORE (collision-sphere centres + 3 x n position Jacobians: the store-bound shape,
 // BASELINE cfg4).

@@ -30,6 +30,7 @@ enum KernelVariant {
      // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
   KV_POS = 10,       // several links, RotationType IGNORE: phase A -> records -> one thread per OUTPUT ENTRY (fk_pos_kernel)
   KV_POS_SMEM = 11,  // KV_POS with the column-ordered joint records in shared memory
+  KV_TWOPHASE_SPEC = 12, // plan-specialised build of the two-phase kernel (several links), compiled at run time
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
 };

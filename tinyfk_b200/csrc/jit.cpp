@@ -133,14 +133,19 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   } else {
     s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
   }
+  if (o.kind != 0 && !f32) s += "#define TFK_SPEC_ROLLED_WALK 1\n"; // several links, FP64: fk_core.h TFK_WALK_LOOP
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;
   s += "#include \"fk_kernels.cuh\"\n";
   s += "extern \"C\" __global__ void __launch_bounds__(tfk::TFK_TILE, " + std::to_string(o.blocks_per_sm) +
        ") tfk_spec_kernel(const tfk::KernelArgs a) {\n";
-  s += std::string("  tfk::fk_fused_spec_body<tfk::FkCore<") + (f32 ? "tfk::MathNative32, true, " : "tfk::MathPortable, false, ") +
-       std::to_string(o.rot_type) + ", tfk::TFK_TILE>, true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
+  const std::string core = std::string("tfk::FkCore<") + (f32 ? "tfk::MathNative32, true, " : "tfk::MathPortable, false, ") +
+                           std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
+  if (o.kind == 0)
+    s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
+  else
+    s += "  tfk::fk_twophase_spec_body<" + core + ", " + (o.kind == 2 ? "true" : "false") + ">(a);\n}\n";
   return s;
 }
 

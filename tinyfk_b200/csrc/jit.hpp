@@ -23,6 +23,7 @@ struct SpecOptions {
   int rot_type;   // compile-time RotationType of FkCore
   int tile;       // threads per block == configurations per tile (a multiple of 32)
   int blocks_per_sm;
+  int kind = 0;   // 0: fused kernel (one requested link); 1: two-phase kernel; 2: two-phase, joint records in shared memory
 };
 
 // The translation unit handed to NVRTC for this plan (exposed for tests and for the cache key).

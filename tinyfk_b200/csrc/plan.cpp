@@ -351,7 +351,9 @@ std::string plan_to_source(const std::vector<unsigned char> &blob) {
   const PlanSlot *slots = reinterpret_cast<const PlanSlot *>(blob.data() + h.off_slots);
   const PlanCol *cols = reinterpret_cast<const PlanCol *>(blob.data() + h.off_cols);
   const uint32_t *masks = reinterpret_cast<const uint32_t *>(blob.data() + h.off_masks);
-  if (h.n_out != 1 || h.mask_words > 2) throw std::invalid_argument("plan specialisation exists for one requested link only");
+  // several links: the per-output tables (link record of every output, relevance masks) are indexed per lane and stay
+  // a run-time table (KernelArgs::tables); k_mask0 is the first output's mask (all the fused kernel needs)
+  if (h.mask_words > 2) throw std::invalid_argument("plan specialisation: more than 64 joints");
   std::string o = "namespace tfk { namespace spec {\n";
   // PlanHeader, in declaration order (fk_plan.h)
   o += "static __device__ constexpr PlanHeader k_h = {" + std::to_string(h.n_slots);
