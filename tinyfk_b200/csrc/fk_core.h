@@ -83,6 +83,10 @@ template <class T> struct DirectSink {
     T *Jc = J + c * ldJ + head * D;
     for (int r = 0; r < D; ++r) Jc[r] = v[r];
   }
+  TFK_FN void put_J2(int c, const T (&v0)[7], const T (&v1)[7]) const { // columns c and c + 1
+    put_J(c, v0);
+    put_J(c + 1, v1);
+  }
 };
 
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
@@ -406,6 +410,30 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   // base and a Jacobian, and only after the joint columns, to keep few values live).
   // `out` gets put_P(d, value) and put_J(column, values[pose_dim]); columns arrive in increasing
   // order and every entry of J is written.
+  // RotationType IGNORE: column c of the position Jacobian (src/kinematics.cpp:131-162, rows 0..2) without a divergent
+  // region -- the joint's records are read whether or not it moves this link and a select discards them -- so that the
+  // loads and cross products of neighbouring columns overlap.  Same expressions as the general loop of emit_link.
+  static TFK_FN void pos_col(const PlanView &pv, const P &e, const uint32_t *mask, int c, const T *rec, int o_arec, int o_prec,
+                             T (&v)[7]) {
+    v[0] = v[1] = v[2] = v[3] = v[4] = v[5] = v[6] = T(0);
+    const PlanCol &pc = pv.cols[c];
+    if (pc.arec < 0) return; // the joint moves none of the requested links (uniform)
+    const bool relevant = (mask[c >> 5] >> (c & 31)) & 1u;
+    const V aw = get_vec(rec, STRIDE, o_arec + 3 * pc.arec);
+    V r = aw; // prismatic: the axis itself (src/kinematics.cpp:149-151)
+    if (!pc.prismatic) {
+      const V cp = get_vec(rec, STRIDE, o_prec + 3 * pc.prec);
+      V d;
+      d.x = e.p.x - cp.x;
+      d.y = e.p.y - cp.y;
+      d.z = e.p.z - cp.z;
+      r = O::cross(aw, d);
+    }
+    v[0] = relevant ? r.x : T(0);
+    v[1] = relevant ? r.y : T(0);
+    v[2] = relevant ? r.z : T(0);
+  }
+
   template <class BaseSrc, class OutSink>
   static TFK_FN void emit_link(const PlanView &pv, const P &e, int o, const T *rec, int stride, int o_arec, int o_prec,
                                BaseSrc &bs, OutSink &out) {
@@ -437,8 +465,22 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
 
     // joint columns, src/kinematics.cpp:131-180
     const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
+    if (ROT == 0) { // position rows only: two columns per round of the output sink (pos_col: no divergent region)
+      TFK_PLAN_LOOP
+      for (int c = 0; c + 1 < h.n_cols; c += 2) {
+        T v0[7], v1[7];
+        pos_col(pv, e, mask, c, rec, o_arec, o_prec, v0);
+        pos_col(pv, e, mask, c + 1, rec, o_arec, o_prec, v1);
+        out.put_J2(c, v0, v1);
+      }
+      if (h.n_cols & 1) {
+        T v[7];
+        pos_col(pv, e, mask, h.n_cols - 1, rec, o_arec, o_prec, v);
+        out.put_J(h.n_cols - 1, v);
+      }
+    }
     TFK_PLAN_LOOP
-    for (int c = 0; c < h.n_cols; ++c) {
+    for (int c = 0; ROT != 0 && c < h.n_cols; ++c) {
       T v[7];
       v[0] = v[1] = v[2] = v[3] = v[4] = v[5] = v[6] = T(0);
       const bool relevant = (mask[c >> 5] >> (c & 31)) & 1u;

@@ -69,6 +69,33 @@ template <class T, int D> struct StagedSink {
     __syncwarp();
     pJ += ldJ;
   }
+  // two consecutive columns in one round (needs 2 * 32 * D <= TFK_STG reals: pose_dim 3): half the warp barriers, and
+  // the second column's strip reads and stores overlap the first one's
+  __device__ __forceinline__ void put_J2(int, const T (&v0)[7], const T (&v1)[7]) {
+    static_assert(D != 3 || 2 * 32 * D <= TFK_STG, "strip too small for two columns");
+#pragma unroll
+    for (int r = 0; r < D; ++r) {
+      stg_w[r] = v0[r];
+      stg_w[32 * D + r] = v1[r];
+    }
+    __syncwarp();
+    T *pJ1 = pJ + ldJ;
+    if (cnt == 32 * D) {
+#pragma unroll
+      for (int k = 0; k < D; ++k) __stcs(pJ + 32 * k, stg_r[32 * k]);
+#pragma unroll
+      for (int k = 0; k < D; ++k) __stcs(pJ1 + 32 * k, stg_r[32 * D + 32 * k]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < D; ++k)
+        if (lane + 32 * k < cnt) {
+          __stcs(pJ + 32 * k, stg_r[32 * k]);
+          __stcs(pJ1 + 32 * k, stg_r[32 * D + 32 * k]);
+        }
+    }
+    __syncwarp();
+    pJ += 2 * ldJ;
+  }
 };
 
 // builds the sink of one warp-load of consecutive rows: head0 = P row of lane 0, nvalid = rows present
