@@ -285,15 +285,39 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
     __syncthreads();
     const int items = nv * h.n_out;
     const long long hbase = (a.row0 + i0) * h.n_out;
+    // one (configuration, link) item per lane.  Position-only records (3 reals): the NEXT item's record is requested
+    // from the scratch (L2) before the current item is worked on, so its latency hides behind a whole item instead of
+    // stalling the item's first arithmetic; 7-real records are loaded where they are used (no registers to spare).
+    enum { PREFETCH = Core::LREC == 3 };
+    int il = 0, o = 0;
+    typename Core::P e;
+    e.p.x = e.p.y = e.p.z = T(0);
+    e.q.x = e.q.y = e.q.z = e.q.w = T(0);
+    if (PREFETCH && warp * 32 < items) {
+      const int itc = warp * 32 + lane < items ? warp * 32 + lane : items - 1;
+      il = itc / h.n_out;
+      o = itc - il * h.n_out;
+      e = Core::load_link(pv, rec_link + il, o);
+    }
     for (int it0 = warp * 32; it0 < items; it0 += TFK_TILE) {
-      const int it = it0 + lane;
-      const int itc = it < items ? it : items - 1;
-      const int il = itc / h.n_out;
-      const int o = itc - il * h.n_out;
+      if (!PREFETCH) {
+        const int itc = it0 + lane < items ? it0 + lane : items - 1;
+        il = itc / h.n_out;
+        o = itc - il * h.n_out;
+        e = Core::load_link(pv, rec_link + il, o);
+      }
+      const int il_c = il, o_c = o;
+      const typename Core::P e_c = e;
+      if (PREFETCH && it0 + TFK_TILE < items) {
+        const int itn = it0 + TFK_TILE + lane < items ? it0 + TFK_TILE + lane : items - 1;
+        il = itn / h.n_out;
+        o = itn - il * h.n_out;
+        e = Core::load_link(pv, rec_link + il, o);
+      }
       fac.nvalid = items - it0 < 32 ? items - it0 : 32;
       fac.head0 = hbase + it0;
       StagedSink<T, Core::D> out = fac.make();
-      Core::phase_b(pv, rec + il, rec_link + il, TFK_TILE, o, out);
+      Core::phase_b(pv, rec + il_c, e_c, o_c, out);
     }
     __syncthreads();
   }
