@@ -120,7 +120,7 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
       return false;
     }
     *tile = TFK_TILE;
-    *bps = hot ? 3 : 4;
+    *bps = hot ? std::min(4, (227 * 1024) / (L.total + 1024)) : 4;
     *smem = L.total;
     *kind = hot ? 2 : 1;
     return true;

@@ -321,7 +321,8 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       const bool leaf = BASE_REC && (sl.flags & SF_LEAF);
       const P parent = cur;
       if (sl.frame_ld != FRAME_RUNNING && (BASE_REC || sl.frame_ld != FRAME_BASE)) // a child of the root, or the
-        cur = (sl.frame_ld == FRAME_BASE) ? get_pose(rec, stride, o_base) : get_pose(rec_f, stride, o_frame + 7 * sl.frame_ld); // 2nd.. child of a branch point
+        cur = (sl.frame_ld == FRAME_BASE) ? (h.base_type == 0 ? base_pose_from_tail(h, qrow) : get_pose(rec, stride, o_base)) // (FIXED: plan constant)
+                                          : get_pose(rec_f, stride, o_frame + 7 * sl.frame_ld); // 2nd.. child of a branch point
       // pose_transform(parent, local), pose.cpp:139-146: position first (it uses the parent's rotation)
       T ang = T(0);
       if (sl.kind != SLOT_FIXED) ang = qrow[sl.qcol];
@@ -706,7 +707,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   static TFK_FN void phase_a_sink(const PlanView &pv, const T *qrow, T *rec, T *rec_f, int stride, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
-    put_pose(rec, stride, h.off_base, base);
+    if (h.base_type != 0) put_pose(rec, stride, h.off_base, base); // a FIXED base is a constant of the plan: no record
     if (h.off_arec - h.off_base > 7) store_base_ctx(h, base, rec, stride); // Jacobian with a moving base
     if (h.root_lrec >= 0) sink.link(h.root_lrec, base); // the root link's pose is the base pose (kinematics.cpp:51-58)
     walk<true>(pv, qrow, rec, rec_f, stride, h.off_base, h.off_arec, h.off_prec, h.off_frame, base, sink);

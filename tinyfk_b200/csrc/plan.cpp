@@ -260,7 +260,8 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.off_base = 0;
   // the base pose always has a record (7 reals; children of the root re-read it); a Jacobian with a moving
   // base adds the inverse pose and the tweaked rotations of the finite-difference columns
-  const int base_rec = (jac && key.base_type != BASE_FIXED) ? (int)TFK_BASE_REC : 7;
+  // (a FIXED base is a constant of the plan, h.base_pose: no record at all)
+  const int base_rec = key.base_type == BASE_FIXED ? 0 : (jac ? (int)TFK_BASE_REC : 7);
   h.off_arec = h.off_base + base_rec;
   h.off_prec = h.off_arec + 3 * n_arec;
   // [base | arec | prec] are what every (configuration, link) item re-reads (small: shared memory when it fits);
