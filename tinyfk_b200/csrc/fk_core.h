@@ -87,6 +87,10 @@ template <class T> struct DirectSink {
     put_J(c, v0);
     put_J(c + 1, v1);
   }
+  TFK_FN void put_J_unit(int c, int k) const { // column c = unit vector e_k on every link (base translation columns)
+    T *Jc = J + c * ldJ + head * D;
+    for (int r = 0; r < D; ++r) Jc[r] = (r == k) ? T(1) : T(0);
+  }
 };
 
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
@@ -523,14 +527,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     // base translation columns, src/kinematics.cpp:194-196
     const int n_trans = (h.base_type == 1) ? 2 : 3;
     TFK_PLAN_LOOP
-    for (int k = 0; k < n_trans; ++k) {
-      T v[7];
-      v[0] = (k == 0) ? T(1) : T(0);
-      v[1] = (k == 1) ? T(1) : T(0);
-      v[2] = (k == 2) ? T(1) : T(0);
-      v[3] = v[4] = v[5] = v[6] = T(0);
-      out.put_J(h.n_cols + k, v);
-    }
+    for (int k = 0; k < n_trans; ++k) out.put_J_unit(h.n_cols + k, k); // a constant pattern: no staging needed
     // base rotation columns: FLOATING keeps roll, pitch, yaw; PLANER keeps yaw only
     if (!ANALYTIC_BASE && h.base_type == 1) {
       emit_planer_yaw(h, e, erpy, bs, out);

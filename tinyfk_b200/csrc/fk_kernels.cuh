@@ -69,6 +69,17 @@ template <class T, int D> struct StagedSink {
     __syncwarp();
     pJ += ldJ;
   }
+  // a column that is the unit vector e_k on every row group (base translation columns, src/kinematics.cpp:194-196):
+  // element j of the warp's run is row j % D -- written straight from registers, no strip, no barrier
+  __device__ __forceinline__ void put_J_unit(int, int k) {
+    const int row0 = lane % D;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      const int row = (row0 + (32 * i) % D) % D;
+      if (lane + 32 * i < cnt) __stcs(pJ + 32 * i, row == k ? T(1) : T(0));
+    }
+    pJ += ldJ;
+  }
   // two consecutive columns in one round (needs 2 * 32 * D <= TFK_STG reals: pose_dim 3): half the warp barriers, and
   // the second column's strip reads and stores overlap the first one's
   __device__ __forceinline__ void put_J2(int, const T (&v0)[7], const T (&v1)[7]) {
