@@ -365,7 +365,7 @@ std::string plan_to_source(const std::vector<unsigned char> &blob) {
   o += ", ";
   put_reals(o, h.base_pose);
   o += "};\n";
-  o += "static __device__ constexpr PlanSlot k_slots[" + std::to_string(std::max(h.n_slots, 1)) + "] = {\n";
+  o += "static __constant__ constexpr PlanSlot k_slots[" + std::to_string(std::max(h.n_slots, 1)) + "] = {\n";
   for (int s = 0; s < h.n_slots; ++s) {
     const PlanSlot &sl = slots[s];
     o += "  {";
@@ -381,7 +381,7 @@ std::string plan_to_source(const std::vector<unsigned char> &blob) {
   }
   if (h.n_slots == 0) o += "  {}\n";
   o += "};\n";
-  o += "static __device__ constexpr PlanCol k_cols[" + std::to_string(std::max(h.n_cols, 1)) + "] = {\n";
+  o += "static __constant__ constexpr PlanCol k_cols[" + std::to_string(std::max(h.n_cols, 1)) + "] = {\n";
   for (int c = 0; c < h.n_cols; ++c)
     o += "  {" + std::to_string(cols[c].arec) + ", " + std::to_string(cols[c].prec) + ", " + std::to_string(cols[c].prismatic) + ", 0},\n";
   if (h.n_cols == 0) o += "  {}\n";
