@@ -39,6 +39,10 @@ namespace tfk {
 
 enum { TFK_STG = 32 * 7 }; // reals in a warp's staging strip: 32 rows x pose_dim <= 7
 
+template <class T> struct Pair2;
+template <> struct Pair2<double> { typedef double2 type; };
+template <> struct Pair2<float> { typedef float2 type; };
+
 // Output sink of the kernels.  put_J must be called by all 32 lanes of the warp together, once per
 // Jacobian column, in increasing column order (it advances a running column pointer).
 template <class T, int D> struct StagedSink {
@@ -49,6 +53,7 @@ template <class T, int D> struct StagedSink {
   T *stg_r; // the strip + lane (what this lane copies out)
   int lane, cnt; // cnt = valid lanes * D
   bool valid;
+  bool wide; // every column of the warp's run and the strip are aligned for pair (2 * sizeof(T)) accesses
 
   __device__ __forceinline__ void begin() const { __syncwarp(); }
   __device__ __forceinline__ void put_P(int d, T v) const {
@@ -91,7 +96,18 @@ template <class T, int D> struct StagedSink {
     }
     __syncwarp();
     T *pJ1 = pJ + ldJ;
-    if (cnt == 32 * D) {
+    if (cnt == 32 * D && wide) {
+      // the two strips are contiguous (2 * 32 * D reals = 32 * D pairs): D rounds of 16-byte (FP64) strip reads and
+      // stores instead of 2 * D rounds of 8-byte ones; pair j < 16 * D belongs to the first column
+      typedef typename Pair2<T>::type T2;
+      const T2 *s2 = reinterpret_cast<const T2 *>(stg_r - lane);
+#pragma unroll
+      for (int k = 0; k < D; ++k) {
+        const int j = lane + 32 * k;
+        T *col = j < 16 * D ? pJ - lane + 2 * j : pJ1 - lane + 2 * (j - 16 * D);
+        __stcs(reinterpret_cast<T2 *>(col), s2[j]);
+      }
+    } else if (cnt == 32 * D) {
 #pragma unroll
       for (int k = 0; k < D; ++k) __stcs(pJ + 32 * k, stg_r[32 * k]);
 #pragma unroll
@@ -128,6 +144,8 @@ template <class T, int D> struct StagedFactory {
     s.stg_r = stg + lane;
     s.cnt = nvalid * D;
     s.valid = lane < nvalid;
+    s.wide = ((reinterpret_cast<unsigned long long>(J + head0 * D) | reinterpret_cast<unsigned long long>(stg)) % (2 * sizeof(T)) == 0) &&
+             s.ldJ % 2 == 0;
     return s;
   }
 };
