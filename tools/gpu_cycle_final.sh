@@ -19,3 +19,4 @@ PY
 ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches_cfg2.csv python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e > gpurun_out/ncu_l.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:tfk_spec -s 3 -c 1 -f -o gpurun_out/prof_cfg2_final python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu2.log 2>&1
 ls -la gpurun_out | head -30
+ncu --set full --clock-control none --import-source on -k regex:tfk_spec -s 3 -c 1 -f -o gpurun_out/prof_cfg4_final python bench.py --workload cfg4 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu4.log 2>&1
