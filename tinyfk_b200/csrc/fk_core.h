@@ -109,50 +109,56 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   typedef PoseT<T> P;
 
   static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
-    rec[(at + 0) * STRIDE] = a.p.x;
-    rec[(at + 1) * STRIDE] = a.p.y;
-    rec[(at + 2) * STRIDE] = a.p.z;
-    rec[(at + 3) * STRIDE] = a.q.x;
-    rec[(at + 4) * STRIDE] = a.q.y;
-    rec[(at + 5) * STRIDE] = a.q.z;
-    rec[(at + 6) * STRIDE] = a.q.w;
+    T *r_ = rec + at * STRIDE; // one address, constant offsets
+    r_[0 * STRIDE] = a.p.x;
+    r_[1 * STRIDE] = a.p.y;
+    r_[2 * STRIDE] = a.p.z;
+    r_[3 * STRIDE] = a.q.x;
+    r_[4 * STRIDE] = a.q.y;
+    r_[5 * STRIDE] = a.q.z;
+    r_[6 * STRIDE] = a.q.w;
   }
   static TFK_FN P get_pose(const T *rec, int stride, int at) {
+    const T *r_ = rec + at * STRIDE; // one address, constant offsets
     P a;
-    a.p.x = rec[(at + 0) * STRIDE];
-    a.p.y = rec[(at + 1) * STRIDE];
-    a.p.z = rec[(at + 2) * STRIDE];
-    a.q.x = rec[(at + 3) * STRIDE];
-    a.q.y = rec[(at + 4) * STRIDE];
-    a.q.z = rec[(at + 5) * STRIDE];
-    a.q.w = rec[(at + 6) * STRIDE];
+    a.p.x = r_[0 * STRIDE];
+    a.p.y = r_[1 * STRIDE];
+    a.p.z = r_[2 * STRIDE];
+    a.q.x = r_[3 * STRIDE];
+    a.q.y = r_[4 * STRIDE];
+    a.q.z = r_[5 * STRIDE];
+    a.q.w = r_[6 * STRIDE];
     return a;
   }
   static TFK_FN V get_vec(const T *rec, int stride, int at) {
+    const T *r_ = rec + at * STRIDE; // one address, constant offsets
     V a;
-    a.x = rec[(at + 0) * STRIDE];
-    a.y = rec[(at + 1) * STRIDE];
-    a.z = rec[(at + 2) * STRIDE];
+    a.x = r_[0 * STRIDE];
+    a.y = r_[1 * STRIDE];
+    a.z = r_[2 * STRIDE];
     return a;
   }
   static TFK_FN void put_vec(T *rec, int stride, int at, const V &a) {
-    rec[(at + 0) * STRIDE] = a.x;
-    rec[(at + 1) * STRIDE] = a.y;
-    rec[(at + 2) * STRIDE] = a.z;
+    T *r_ = rec + at * STRIDE; // one address, constant offsets
+    r_[0 * STRIDE] = a.x;
+    r_[1 * STRIDE] = a.y;
+    r_[2 * STRIDE] = a.z;
   }
   static TFK_FN Q get_quat(const T *rec, int stride, int at) {
+    const T *r_ = rec + at * STRIDE; // one address, constant offsets
     Q a;
-    a.x = rec[(at + 0) * STRIDE];
-    a.y = rec[(at + 1) * STRIDE];
-    a.z = rec[(at + 2) * STRIDE];
-    a.w = rec[(at + 3) * STRIDE];
+    a.x = r_[0 * STRIDE];
+    a.y = r_[1 * STRIDE];
+    a.z = r_[2 * STRIDE];
+    a.w = r_[3 * STRIDE];
     return a;
   }
   static TFK_FN void put_quat(T *rec, int stride, int at, const Q &a) {
-    rec[(at + 0) * STRIDE] = a.x;
-    rec[(at + 1) * STRIDE] = a.y;
-    rec[(at + 2) * STRIDE] = a.z;
-    rec[(at + 3) * STRIDE] = a.w;
+    T *r_ = rec + at * STRIDE; // one address, constant offsets
+    r_[0 * STRIDE] = a.x;
+    r_[1 * STRIDE] = a.y;
+    r_[2 * STRIDE] = a.z;
+    r_[3 * STRIDE] = a.w;
   }
 
   // ---------------------------------------------------------------------------------------------
