@@ -232,3 +232,37 @@ def test_full_size_cfg2_properties():
     parity.assert_bitwise(P[sel], Jv[sel].reshape(-1, nj + 3), Pr, Jr, "1M spot rows")
     P2, J2 = pair.prod_solve(q, lids, jids, rot, base, True)
     assert np.array_equal(P, P2) and np.array_equal(J, J2)
+
+
+@pytest.mark.parametrize("rot,precision", [(0, 0), (1, 0), (2, 1)])
+def test_half_tiles_when_the_last_wave_is_short(rot, precision):
+    """several links, ONE launch (device entry) of a little more than one wave of 128-configuration tiles (148 SMs x
+    3-4 blocks): the engine runs 64-configuration tiles (fk_launch.h:twophase_tile_cfgs); ragged tail of 37
+    configurations.  Rows of the first tile, of tiles of the second round and of the tail equal the oracle"""
+    import torch
+
+    pair = Pair("fetch.urdf", strict=True)
+    jids, lids, _, _ = pair.setup("cfg4")
+    lids = lids[:3]
+    base, nl = 2, 3
+    n = 148 * 4 * 128 + 9 * 128 + 37
+    q = _inputs(pair, jids, base, n, seed=5)
+    dt, npdt = (torch.float64, np.float64) if precision == 0 else (torch.float32, np.float32)
+    dq = torch.from_numpy(q.astype(npdt)).cuda()
+    pd, nd = W.pose_dim(rot), q.shape[1]
+    dP = torch.full((pd, n * nl), float("nan"), dtype=dt, device="cuda")
+    dJ = torch.full((nd, n * nl * pd), float("nan"), dtype=dt, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    pair.prod.solve_fk_device(0, st, dq.data_ptr(), n, lids, jids, rot, base, True, precision, dP.data_ptr(), dJ.data_ptr(), n, 0)
+    torch.cuda.synchronize()
+    assert "twophase" in pair.prod.last_launch_info()["kernel"]
+    P, J = dP.cpu().numpy().T.astype(np.float64), dJ.cpu().numpy().T.astype(np.float64)
+    assert np.isfinite(P).all() and np.isfinite(J).all()
+    sel = np.r_[0:200, 148 * 4 * 64 - 100:148 * 4 * 64 + 100, 148 * 3 * 64 - 50:148 * 3 * 64 + 50, n - 300:n]
+    Pr, Jr = pair.oracle_solve(q[sel], lids, jids, rot, base, True)
+    Ps = P.reshape(n, nl, pd)[sel].reshape(-1, pd)
+    Js = J.reshape(n, nl * pd, nd)[sel].reshape(-1, nd)
+    if precision == 0:
+        parity.assert_bitwise(Ps, Js, Pr, Jr, "half tiles rot %d" % rot)
+    else:
+        assert np.abs(Ps - Pr).max() <= parity.TOL_F32 and np.abs(Js - Jr).max() <= parity.TOL_F32

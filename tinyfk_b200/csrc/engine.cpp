@@ -284,9 +284,12 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
     if (b < 1) throw CudaError("specialised kernel does not fit on an SM");
     it = sk.blocks_per_sm.insert(std::make_pair(device, b)).first;
   }
-  const int64_t n_tiles = (a.n + sk.tile - 1) / sk.tile;
+  // two-phase: configurations per tile (fk_launch.h:twophase_tile_cfgs; the two-phase builds use TFK_TILE threads)
+  const int tile_cfgs = sk.kind != 0 ? twophase_tile_cfgs(a.n, (int64_t)sm_count(device) * it->second) : sk.tile;
+  const int64_t n_tiles = (a.n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
   KernelArgs args = a;
+  if (sk.kind != 0) args.sub_cfg = tile_cfgs;
   const PlanHeader *ph = reinterpret_cast<const PlanHeader *>(e.blob.data());
   int rec_reals = ph->fz_size;
   if (sk.kind != 0) { // two-phase: per-output tables and the block-private record scratch, sized for THIS grid
@@ -536,8 +539,10 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   } else {
     bps = oit->second;
   }
-  const int64_t n_tiles = (n + TFK_TILE - 1) / TFK_TILE;
+  const bool twophase = variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM;
   const int64_t resident = (int64_t)sm_count(device) * bps;
+  const int tile_cfgs = twophase ? twophase_tile_cfgs(n, resident) : (int)TFK_TILE;
+  const int64_t n_tiles = (n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, resident);
   KernelArgs a;
   a.scratch = nullptr;
@@ -555,7 +560,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.J = d_J;
   a.pairs = sqdist ? ex->d_pairs : nullptr;
   a.n_pairs = n_pairs;
-  a.sub_cfg = pos_sub;
+  a.sub_cfg = twophase ? tile_cfgs : pos_sub;
   a.weights = com ? ex->d_weights : nullptr;
   a.n_com = com ? ex->n_com : 0;
   a.n_act = com ? ex->n_act : 0;

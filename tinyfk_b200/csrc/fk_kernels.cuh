@@ -303,12 +303,15 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
   fac.ldP = a.ld_cfg * h.n_out;
   fac.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
 
-  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
+  // configurations per tile: TFK_TILE, or less when the batch has too few full tiles to load the SMs evenly
+  // (twophase_tile_cfgs, fk_launch.h) -- phase A then leaves threads idle, phase B spreads the tile's items over all
+  const int tc = a.sub_cfg > 0 ? a.sub_cfg : (int)TFK_TILE;
+  const long long n_tiles = (a.n + tc - 1) / tc;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long i0 = tile * TFK_TILE;
-    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
+    const long long i0 = tile * tc;
+    const int nv = (a.n - i0 < tc) ? (int)(a.n - i0) : tc;
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
-    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
+    prefetch_q_tile(q, i0 + (long long)gridDim.x * tc, a.n, h.n_in);
     __syncthreads();
     if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, rec_link + threadIdx.x, TFK_TILE);
     __syncthreads();

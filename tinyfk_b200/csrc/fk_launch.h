@@ -50,6 +50,7 @@ struct KernelArgs {
   // KV_INERTIA: P = out (9, ld_cfg); weights = 7 reals per com link (mass, ixx, ixy, ixz, iyy, iyz, izz); n_com, mass_total
   // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
   int sub_cfg;         // fk_pos_kernel: configurations per phase-B sub-tile (power of two, <= 32)
+                       // fk_twophase_kernel: configurations per tile (0 = TFK_TILE), twophase_tile_cfgs()
   const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
   int n_com, n_act;
   double mass_total, vfs, com_diag;
@@ -90,6 +91,17 @@ TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem,
 enum { TFK_POS_STRIDE = TFK_TILE + 1 };
 // shared memory: [per-output tables | outputs of every link record (first_out[n_lrec], next_out[n_out]) | q tile, later
 // the sub-tile's link positions [3][sub*n_out | 1], later the warps' staging strips | column-ordered joint records (or none)]
+// fk_twophase_kernel: configurations per tile.  When the batch needs more than one wave of resident blocks, the last
+// wave is partly empty (cfg5 FP32: 512 tiles of 128 on 444 resident blocks = two rounds for 68 blocks, one for the
+// rest); half tiles even that out at the price of idle threads in phase A, so they are used only when the busiest
+// block gets at least 8 % fewer configurations.  (With a single wave -- cfg5 FP64: 512 tiles, 592 slots -- half tiles
+// measured 3 % slower: the SMs are latency-bound and three or four co-resident blocks take about the same time.)
+TFK_HDI int twophase_tile_cfgs(long long n, long long resident_blocks) {
+  const long long full = (((n + TFK_TILE - 1) / TFK_TILE + resident_blocks - 1) / resident_blocks) * TFK_TILE;
+  const int tc = TFK_TILE / 2;
+  const long long half = (((n + tc - 1) / tc + resident_blocks - 1) / resident_blocks) * tc;
+  return half * 108 < full * 100 ? tc : (int)TFK_TILE;
+}
 TFK_HDI int pos_lpitch(int sub, int n_out) { return (sub * n_out) | 1; }
 TFK_HDI SmemLayout smem_layout_pos(int table_bytes, int n_in, int n_lrec, int n_out, int sub, int rec_reals_in_smem, int real_bytes) {
   const int tb = ((table_bytes + 15) & ~15) + (((n_lrec + n_out) * 4 + 15) & ~15);
