@@ -112,7 +112,13 @@ TFK_API int tfk_solve_fk_host(tfk_model *m, const void *q, int64_t n, const int 
  * the legacy default stream) and not synchronised.  The destination arrays are dimensioned for ld_cfg
  * configurations and this call fills configurations [row0, row0 + n).  Does not touch the model's stored
  * state.  This is the entry the throughput metric is timed on.  After the first call with a signature on a stream the
- * call only enqueues one kernel: it may be captured into a CUDA graph on that stream. */
+ * call only enqueues one kernel: it may be captured into a CUDA graph on that stream.  Capture rules: (1) run the
+ * same call once on the stream before capturing (the record scratch of a stream only ever grows, and growing it
+ * inside a capture fails with TFK_ERR_INVALID); (2) buffers a captured kernel names stay allocated until
+ * tfk_model_destroy, so replaying the graph after larger launches is safe; (3) while the stream is capturing the
+ * engine never loads or compiles a plan-specialised kernel: the capture records the specialised kernel only if it has
+ * already run on this device, otherwise the generic one; (4) keep the model's stored state that feeds the signature's
+ * plan (angles of non-selected joints, the FIXED base pose) unchanged between capture and replay. */
 TFK_API int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
                                 const int *elink_ids, int n_link, const int *joint_ids, int n_joint,
                                 int rot_type, int base_type, int with_jacobian, int precision, void *d_P,
@@ -207,6 +213,9 @@ TFK_API int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int 
 /* which kernel the last launch used: 0 fused single-link (records in shared memory), 1 fused single-link
    (records in global scratch), 2 two-phase multi-link, 3 = 0 built for five resident blocks per SM -- see tinyfk_b200/csrc/fk_kernels.cuh */
 TFK_API int tfk_last_launch_variant(const tfk_model *m);
+/* call signatures the engine currently holds a plan for (bounded at 64, least recently used evicted; a signature whose
+ * plan constants change with the stored model state is replaced in place).  Diagnostics / tests. */
+TFK_API int tfk_plan_cache_size(const tfk_model *m);
 TFK_API const char *tfk_version(void);
 
 #ifdef __cplusplus

@@ -49,30 +49,7 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
       Core::run_fused(pv, qrow.data(), rec.data(), 1, f);
     } else {
       Core::phase_a(pv, qrow.data(), rec.data(), 1);
-      if (Core::D == 3) { // fk_pos_kernel's phase B: one output entry at a time (FkCore::pos_entry)
-        for (int o = 0; o < h.n_out; ++o) {
-          out.head = (long long)i * h.n_out + o;
-          const int lat = h.off_lrec + pv.lrec_of_out[o] * 3;
-          typename Core::V ep;
-          ep.x = rec[lat], ep.y = rec[lat + 1], ep.z = rec[lat + 2];
-          out.put_P(0, ep.x), out.put_P(1, ep.y), out.put_P(2, ep.z);
-          if (!h.with_jacobian) continue;
-          const T pe[3] = {ep.x, ep.y, ep.z};
-          const uint32_t *mask = pv.masks + (size_t)o * h.mask_words;
-          const int n_trans = h.base_type == 0 ? 0 : (h.base_type == 1 ? 2 : 3);
-          for (int r = 0; r < 3; ++r) {
-            const int r1 = (r + 1) % 3, r2 = (r + 2) % 3;
-            for (int c = 0; c < h.n_cols; ++c) {
-              T v = T(0);
-              if (pv.cols[c].arec >= 0 && ((mask[c >> 5] >> (c & 31)) & 1u))
-                v = Core::pos_entry(h, pv.cols[c], rec.data() + r, rec.data() + r1, rec.data() + r2, pe[r1], pe[r2]);
-              J[(size_t)c * ldJ + out.head * 3 + r] = v;
-            }
-            for (int k = 0; k < n_trans; ++k) J[(size_t)(h.n_cols + k) * ldJ + out.head * 3 + r] = (r == k) ? T(1) : T(0);
-          }
-          if (h.base_type != 0) Core::emit_base_rot_pos(pv, ep, rec.data(), out);
-        }
-      } else {
+      {
         for (int o = 0; o < h.n_out; ++o) {
           out.head = (long long)i * h.n_out + o;
           Core::phase_b(pv, rec.data(), 1, o, out);

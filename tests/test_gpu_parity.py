@@ -137,11 +137,14 @@ def test_multi_chunk_host_path_and_pinned_buffers():
     Pp.free(), Jp.free()
 
 
-def test_fp32_mode_within_1e5():
-    """opt-in FP32 mode: 1e-5 on positions, quaternions and position / quaternion Jacobian rows.  RPY angles
-    and RPY Jacobian rows are conditioning-limited: the map quaternion -> rpy amplifies ANY input error by
-    1/cos(pitch) (angles) and 1/cos(pitch)^2 (rpy_derivative divides by cos(pitch), src/kinematics.cpp:18-21),
-    so their bound is scaled by exactly that factor (measured on B200: 1.3e-6 / 1.1e-5 at |cos| >= 0.2)."""
+def test_fp32_mode_within_1e5(capsys):
+    """opt-in FP32 mode, north_star "1e-5 in FP32".  Tier 1 (asserted at 1e-5 abs, every entry): positions, quaternions
+    and their Jacobian rows.  RPY angles and RPY Jacobian rows are functions of the quaternion whose condition number is
+    1/cos(pitch) (angles) and 1/cos(pitch)^2 (rpy_derivative divides by cos(pitch), src/kinematics.cpp:18-21): an FP32
+    quaternion that is correct to half an ulp already moves them by more than 1e-5 near the gimbal.  For those the test
+    MEASURES and prints the max abs error and the fraction of entries above 1e-5, asserts 1e-5 on every entry whose
+    |cos(pitch)| >= 0.5, asserts the fraction above 1e-5 stays small, and keeps the conditioning bound as tier 2."""
+    report = []
     for cfg in ("cfg2", "cfg3", "cfg4", "cfg5"):
         pair = Pair(W.CONFIGS[cfg][0], strict=False)
         jids, lids, rot, base = pair.setup(cfg)
@@ -151,15 +154,35 @@ def test_fp32_mode_within_1e5():
         P, J = pair.prod_solve(q, lids, jids, rot, base, True, precision=1)
         assert P.dtype == np.float32 and J.dtype == np.float32
         pd = W.pose_dim(rot)
-        eP = parity.rel_err(P, Pr)
-        eJ = parity.rel_err(J, Jr).reshape(-1, pd, J.shape[1])
-        assert eP[:, :3].max() <= parity.TOL_F32 and eJ[:, :3].max() <= parity.TOL_F32, (cfg, eP[:, :3].max())
+        aP = np.abs(P - Pr)
+        aJ = np.abs(J - Jr).reshape(-1, pd, J.shape[1])
+        assert aP[:, :3].max() <= parity.TOL_F32 and aJ[:, :3].max() <= parity.TOL_F32, (cfg, aP[:, :3].max(), aJ[:, :3].max())
+        line = "%s: max|dP_xyz| %.2e  max|dJ_xyz| %.2e" % (cfg, aP[:, :3].max(), aJ[:, :3].max())
         if rot == W.ROT_XYZW:
-            assert eP[:, 3:].max() <= parity.TOL_F32 and eJ[:, 3:].max() <= parity.TOL_F32
+            assert aP[:, 3:].max() <= parity.TOL_F32 and aJ[:, 3:].max() <= parity.TOL_F32
+            line += "  max|dP_quat| %.2e  max|dJ_quat| %.2e" % (aP[:, 3:].max(), aJ[:, 3:].max())
         if rot == W.ROT_RPY:
-            c = np.maximum(np.abs(np.cos(Pr[:, 4])), 1e-3)
-            assert (eP[:, 3:] <= parity.TOL_F32 / c[:, None]).all(), cfg
-            assert (eJ[:, 3:] <= parity.TOL_F32 / (c * c)[:, None, None]).all(), cfg
+            cosp = np.abs(np.cos(Pr[:, 4]))
+            well = cosp >= 0.5
+            fracP = float((aP[:, 3:] > parity.TOL_F32).mean())
+            fracJ = float((aJ[:, 3:] > parity.TOL_F32).mean())
+            line += ("  RPY angles: max %.2e (|cos|>=0.5: %.2e), %.3f%% of entries > 1e-5;  RPY rows of J: max %.2e "
+                     "(|cos|>=0.5: %.2e), %.3f%% > 1e-5;  min|cos pitch| %.3f"
+                     % (aP[:, 3:].max(), aP[well, 3:].max(), 100 * fracP, aJ[:, 3:].max(), aJ[well, 3:].max(), 100 * fracJ,
+                        cosp.min()))
+            # tier 1: well-conditioned rows meet 1e-5 outright (angles) / 4e-5 = 1e-5 / cos^2 at the edge of the set (rows)
+            assert aP[well, 3:].max() <= parity.TOL_F32, line
+            assert aJ[well, 3:].max() <= parity.TOL_F32 / 0.25, line
+            assert fracP <= 0.01 and fracJ <= 0.05, line
+            # tier 2: everywhere, the conditioning bound (relative above 1: |rows| grow like 1/cos too)
+            c = np.maximum(cosp, 1e-3)
+            eP = parity.rel_err(P, Pr)
+            eJ = parity.rel_err(J, Jr).reshape(-1, pd, J.shape[1])
+            assert (eP[:, 3:] <= parity.TOL_F32 / c[:, None]).all(), line
+            assert (eJ[:, 3:] <= parity.TOL_F32 / (c * c)[:, None, None]).all(), line
+        report.append(line)
+    with capsys.disabled():
+        print("\nFP32 mode vs the FP64 reference (measured):\n  " + "\n  ".join(report))
 
 
 def test_empty_and_edge_shapes():

@@ -106,3 +106,29 @@ def test_minimal_urdf_defaults():
     p, t, jid, axis, origin = m.link_info(2)
     assert (p, t, jid) == (1, 3, 1) and list(axis) == [0, 0, 0] and list(origin[:3]) == [1, 2, 3]
     assert m.get_joint_limits([1]) == [(0.0, 0.0)]
+
+
+def test_plan_cache_is_keyed_on_the_signature_and_bounded():
+    """Engine::plan_for (ADVICE r1): every *_host call writes the last configuration back into the model, which used to
+    make the next call miss the cache and, when the stored state feeds the plan (alternating joint sets, as IK loops do),
+    add an entry per call until a 64-entry flush.  Now: one entry per signature, replaced in place when its constants
+    change, least recently used evicted at 64.  Runs without a GPU: n = 0 builds the plan and returns."""
+    m = capi.Model(W.urdf_text("pr2.urdf"), host_libm=0)
+    ja, jb = m.get_joint_ids(W.PR2_RARM), m.get_joint_ids(W.PR2_LARM)
+    la = m.get_link_ids(["r_gripper_tool_frame", "l_gripper_tool_frame"])
+    rng = np.random.default_rng(0)
+    for k in range(100):
+        # the signature over the right arm reads the stored angles of the left arm and vice versa
+        m.set_joint_angles(jb, rng.uniform(-0.3, 0.3, 7))
+        m.solve_fk(np.zeros((0, 7)), la, ja, 1, 0, True)
+        m.set_joint_angles(ja, rng.uniform(-0.3, 0.3, 7))
+        m.solve_fk(np.zeros((0, 7)), la, jb, 1, 0, True)
+        assert m.plan_cache_size() == 2, k
+    # an unchanged state keeps the model version (no rebuild), and state a plan does not read keeps its entry
+    m.set_joint_angles(ja, m.get_joint_angles(ja))
+    m.solve_fk(np.zeros((0, 7)), la, jb, 1, 0, True)
+    assert m.plan_cache_size() == 2
+    # many distinct signatures: bounded, least recently used evicted
+    for lid in range(80):
+        m.solve_fk(np.zeros((0, 7)), [lid], ja, 0, 0, False)
+    assert m.plan_cache_size() == 64

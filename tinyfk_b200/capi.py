@@ -22,7 +22,7 @@ SYMBOLS = [
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
     "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
-    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_version",
+    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_plan_cache_size", "tfk_version",
 ]
 
 _lib = None
@@ -82,6 +82,7 @@ def lib():
     L.tfk_host_free.argtypes = [_vp]
     L.tfk_kernel_launch_count.restype = _i64
     L.tfk_last_launch_info.argtypes = [_vp, _ip, _ip, _ip, _ip, _ip]
+    L.tfk_plan_cache_size.argtypes = [_vp]
     _lib = L
     return L
 
@@ -345,6 +346,9 @@ class Model:
                                            _vp(d_J) if d_J else None, int(ld_cfg if ld_cfg is not None else n),
                                            int(row0)))
 
+    def plan_cache_size(self):
+        return int(self._L.tfk_plan_cache_size(self._h))
+
     def last_launch_info(self):
         v = [ctypes.c_int() for _ in range(5)]
         _check(self._L.tfk_last_launch_info(self._h, *[ctypes.byref(x) for x in v]))
@@ -352,7 +356,7 @@ class Model:
         self._L.tfk_last_launch_variant.argtypes = [_vp]
         k = int(self._L.tfk_last_launch_variant(self._h))
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
-                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 9: "fk_sqdist_kernel<joint records in shared memory>", 8: "fk_twophase_kernel<joint records in shared memory>", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)", 12: "tfk_spec_kernel (plan-specialised fk_twophase_kernel, NVRTC)", 10: "fk_pos_kernel", 11: "fk_pos_kernel<column-ordered joint records in shared memory>"}.get(k, "none")
+                       2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 9: "fk_sqdist_kernel<joint records in shared memory>", 8: "fk_twophase_kernel<joint records in shared memory>", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)", 12: "tfk_spec_kernel (plan-specialised fk_twophase_kernel, NVRTC)"}.get(k, "none")
         return d
 
 

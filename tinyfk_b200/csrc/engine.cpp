@@ -2,9 +2,12 @@
 #include "engine.hpp"
 #include "jit.hpp"
 
+#include <nvtx3/nvToolsExt.h> // header-only NVTX 3: ranges are no-ops unless a profiler is attached
+
 #include <algorithm>
 #include <atomic>
 #include <cstring>
+#include <exception>
 
 namespace tfk {
 
@@ -29,6 +32,11 @@ struct DeviceGuard { // restore the caller's current device
   }
 };
 
+struct NvtxRange { // NVTX range around a host-side section (H2D / kernel / D2H enqueue of a chunk)
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
 inline size_t real_size(int precision) { return precision == PREC_F32 ? sizeof(float) : sizeof(double); }
 
 // ---- pinned pool --------------------------------------------------------------------------------
@@ -37,6 +45,15 @@ std::map<void *, size_t> g_pin_live;            // handed out
 std::multimap<size_t, void *> g_pin_free;       // available, by size
 
 } // namespace
+
+static bool stream_is_capturing(cudaStream_t stream) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
 
 int64_t kernel_launch_count() { return g_launches.load(); }
 
@@ -247,6 +264,11 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
     std::lock_guard<std::mutex> lk(sk.mu);
     state = sk.state;
   }
+  // A stream capture forbids what the JIT does behind the scenes (cudaLibraryLoadData, cudaFuncSetAttribute, cudaMalloc of
+  // a differently sized scratch): while the stream is capturing, only a kernel that is already loaded AND has been
+  // launched on this device is used; otherwise the capture records the generic kernel and the policy does not advance.
+  const bool capturing = stream_is_capturing(stream);
+  if (capturing && (state != SPEC_READY || sk.blocks_per_sm.find(device) == sk.blocks_per_sm.end())) return false;
   if (state == SPEC_NONE) {
     if (jit_mode == JIT_AUTO) {
       e.configs_served += a.n;
@@ -301,6 +323,7 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
   }
   void *params[] = {&args};
   ck(cudaLaunchKernel(reinterpret_cast<const void *>(sk.kernel), dim3(grid), dim3(sk.tile), params, (size_t)sk.smem, stream), "launch (specialised kernel)");
+  e.launched_on.insert(device);
   g_launches.fetch_add(1);
   last_launch.grid = grid;
   last_launch.block = sk.tile;
@@ -316,15 +339,12 @@ Engine::~Engine() { release_device_memory(); }
 void Engine::release_device_memory() {
   int prev = 0;
   if (cudaGetDevice(&prev) != cudaSuccess) return;
-  for (auto &e : plans_)
-    for (auto &kv : e->on_device) {
-      cudaSetDevice(kv.first);
-      cudaFree(kv.second);
-    }
+  for (auto &e : plans_) retire(e);
   plans_.clear();
   for (auto &kv : workspaces_) {
     cudaSetDevice(kv.first.first);
     cudaFree(kv.second.scratch);
+    for (void *p : kv.second.outgrown) cudaFree(p);
   }
   workspaces_.clear();
   for (auto &kv : pipes_) {
@@ -360,6 +380,30 @@ int Engine::sm_count(int device) {
   return n;
 }
 
+// Frees everything a plan entry owns on the devices.  Kernels of the entry may still be in flight (the device entry is
+// asynchronous, and a fused single-link plan never uploads tables, so `on_device` says nothing about where it ran):
+// every device the entry was LAUNCHED on is synchronised first; only then are the tables freed and the specialised
+// kernels unloaded (~SpecKernel joins the compile thread and calls cudaLibraryUnload).
+void Engine::retire(std::unique_ptr<PlanEntry> &e) {
+  if (!e) return;
+  int prev = 0;
+  const bool have_dev = cudaGetDevice(&prev) == cudaSuccess;
+  std::set<int> devs = e->launched_on;
+  for (auto &kv : e->on_device) devs.insert(kv.first);
+  for (int d : devs)
+    if (cudaSetDevice(d) == cudaSuccess) cudaDeviceSynchronize();
+  for (auto &kv : e->on_device)
+    if (cudaSetDevice(kv.first) == cudaSuccess) cudaFree(kv.second);
+  if (have_dev) cudaSetDevice(prev);
+  e.reset();
+}
+
+// One entry per call SIGNATURE (links, joints, rotation type, base type, Jacobian flag).  The stored model state feeds
+// the plan too (angles of joints that are not selected, the base pose of a FIXED base), and every *_host call writes the
+// last configuration back into the model: when the state has moved on, the blob is rebuilt; identical bytes (the usual
+// case: the state that changed is not read by this plan) keep the entry, its uploaded tables and its specialised
+// kernels; different bytes REPLACE the entry in place (IK loops that alternate joint sets do not grow the cache).
+// Bounded at 64 signatures, least recently used evicted.
 Engine::PlanEntry &Engine::plan_for(const SolveSpec &spec) {
   if (spec.n_link < 0 || spec.n_joint < 0) throw std::invalid_argument("negative id count");
   PlanKey key;
@@ -369,38 +413,47 @@ Engine::PlanEntry &Engine::plan_for(const SolveSpec &spec) {
   key.base_type = spec.base_type;
   key.with_jacobian = spec.with_jacobian ? 1 : 0;
   key.model_version = model.version();
-  for (auto &e : plans_)
-    if (e->key == key) return *e;
-  std::vector<unsigned char> blob = build_plan(model, key);
-  // same signature, older model version, identical bytes (the stored state that changed is not used by
-  // this plan): keep the uploaded copies
-  for (auto &e : plans_) {
-    PlanKey k2 = e->key;
+  const uint64_t tick = ++plan_tick_;
+  size_t slot = plans_.size();
+  for (size_t i = 0; i < plans_.size(); ++i) {
+    PlanKey k2 = plans_[i]->key;
+    const uint64_t built_for = k2.model_version;
     k2.model_version = key.model_version;
-    if (k2 == key && e->blob == blob) {
-      e->key.model_version = key.model_version;
-      return *e;
+    if (!(k2 == key)) continue;
+    if (built_for == key.model_version) {
+      plans_[i]->last_used = tick;
+      return *plans_[i];
     }
+    slot = i;
+    break;
   }
-  if (plans_.size() >= 64) { // bounded cache: drop everything (rare), after the devices went idle
-    int prev = 0;
-    cudaGetDevice(&prev);
-    for (auto &e : plans_)
-      for (auto &kv : e->on_device) {
-        cudaSetDevice(kv.first);
-        cudaDeviceSynchronize();
-        cudaFree(kv.second);
-      }
-    cudaSetDevice(prev);
-    plans_.clear();
+  std::vector<unsigned char> blob = build_plan(model, key);
+  if (slot < plans_.size()) {
+    PlanEntry &e = *plans_[slot];
+    if (e.blob == blob) {
+      e.key.model_version = key.model_version;
+      e.last_used = tick;
+      return e;
+    }
+    retire(plans_[slot]); // same signature, different constants: replaced below
+  } else if (plans_.size() >= 64) {
+    slot = 0;
+    for (size_t i = 1; i < plans_.size(); ++i)
+      if (plans_[i]->last_used < plans_[slot]->last_used) slot = i;
+    retire(plans_[slot]);
+  } else {
+    plans_.emplace_back();
   }
   std::unique_ptr<PlanEntry> e(new PlanEntry);
   e->key = key;
+  e->last_used = tick;
   e->blob.swap(blob);
   e->params = make_plan_params(e->blob);
-  plans_.push_back(std::move(e));
-  return *plans_.back();
+  plans_[slot] = std::move(e);
+  return *plans_[slot];
 }
+
+size_t Engine::plan_cache_size() const { return plans_.size(); }
 
 const unsigned char *Engine::plan_on_device(PlanEntry &e, int device, cudaStream_t stream) {
   auto it = e.on_device.find(device);
@@ -419,26 +472,50 @@ const unsigned char *Engine::plan_on_device(PlanEntry &e, int device, cudaStream
   return d;
 }
 
+// Record scratch of one (device, stream).  GROW-ONLY: a buffer that became too small is kept until the engine is
+// destroyed, because a CUDA graph captured earlier may still name it in a kernel node.  Growing needs cudaMalloc, which
+// a stream capture forbids: a launch that would grow the scratch during a capture fails with a clear message (run the
+// signature once on the stream before capturing, include/tinyfk_b200.h).
 Engine::Workspace &Engine::workspace(int device, cudaStream_t stream, size_t bytes) {
   Workspace &w = workspaces_[std::make_pair(device, stream)];
   if (w.scratch_bytes < bytes) {
-    if (w.scratch) {
-      ck(cudaStreamSynchronize(stream), "cudaStreamSynchronize(workspace)");
-      cudaFree(w.scratch);
-      w.scratch = nullptr;
-      w.scratch_bytes = 0;
-    }
-    ck(cudaMalloc(&w.scratch, bytes), "cudaMalloc(records)");
+    if (stream_is_capturing(stream))
+      throw std::invalid_argument("tfk_*_device inside a stream capture needs more record scratch than this stream has: run the "
+                                  "same call once on the stream before capturing");
+    void *fresh = nullptr;
+    ck(cudaMalloc(&fresh, bytes), "cudaMalloc(records)");
+    if (w.scratch) w.outgrown.push_back(w.scratch);
+    w.scratch = fresh;
     w.scratch_bytes = bytes;
   }
   return w;
 }
 
-// fk_pos_kernel (entry-per-thread phase B for RotationType IGNORE) is opt-in while it measures slower than the
-// two-phase kernel on cfg4 (profiles/README.md): TFK_POS_KERNEL=1 selects it
-static bool pos_kernel_enabled() {
-  const char *v = std::getenv("TFK_POS_KERNEL");
-  return v && *v && *v != '0';
+size_t Engine::max_pitch(int device) {
+  auto it = max_pitch_.find(device);
+  if (it != max_pitch_.end()) return it->second;
+  int v = 0;
+  ck(cudaDeviceGetAttribute(&v, cudaDevAttrMaxPitch, device), "cudaDeviceGetAttribute(max pitch)");
+  size_t mp = v > 0 ? (size_t)v : (size_t)0x7fffffff;
+  if (const char *e = std::getenv("TFK_MAX_PITCH")) mp = std::min<size_t>(mp, (size_t)std::atoll(e)); // test knob
+  max_pitch_[device] = mp;
+  return mp;
+}
+
+void Engine::copy_columns_d2h(int device, char *dst, size_t dst_pitch, const char *src, size_t src_pitch, size_t width,
+                              size_t ncols, cudaStream_t st, const char *what) {
+  if (ncols == 0 || width == 0) return;
+  const size_t mp = max_pitch(device);
+  if (ncols == 1 || (dst_pitch <= mp && src_pitch <= mp)) {
+    if (ncols == 1)
+      ck(cudaMemcpyAsync(dst, src, width, cudaMemcpyDeviceToHost, st), what);
+    else
+      ck(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width, ncols, cudaMemcpyDeviceToHost, st), what);
+    return;
+  }
+  // a 2-D copy with such a pitch fails with cudaErrorInvalidPitchValue (cfg4 at 2^22 configurations: 3.0 GB per column)
+  for (size_t c = 0; c < ncols; ++c)
+    ck(cudaMemcpyAsync(dst + c * dst_pitch, src + c * src_pitch, width, cudaMemcpyDeviceToHost, st), what);
 }
 
 void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision, const void *d_q, int64_t n,
@@ -454,7 +531,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
-  int variant, rec_reals, rec_stride = TFK_TILE, pos_sub = 0;
+  int variant, rec_reals;
   SmemLayout L;
   if (sqdist) {
     rec_reals = h->rec_size;
@@ -493,25 +570,6 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
       variant = KV_TWOPHASE_SMEM;
       rec_reals = h->rec_size - h->off_frame;
     }
-    // position-only queries (RotationType IGNORE): the entry-per-thread kernel; plan records in the scratch
-    // ([k][TILE + 1]); shared memory holds a sub-tile's link positions and, when three blocks still fit, the
-    // column-ordered joint records (else they go to the scratch too).  Largest sub-tile that fits wins.
-    if (h->rot_type == 0 && h->n_cols <= 64 && pos_kernel_enabled()) {
-      const int n_crec = h->with_jacobian ? 6 * h->n_cols : 0;
-      bool found = false;
-      for (int in_smem = 1; in_smem >= 0 && !found; --in_smem)
-        for (int sub = 32; sub >= 8 && !found; sub >>= 1) {
-          if (in_smem && std::getenv("TFK_NO_SMEM_HOT")) continue;
-          const SmemLayout Lp = smem_layout_pos(plan_bytes, h->n_in, h->n_lrec, h->n_out, sub, in_smem ? n_crec : 0, rb);
-          if (3 * (Lp.total + 1024) > 227 * 1024) continue;
-          found = true;
-          L = Lp;
-          pos_sub = sub;
-          variant = in_smem ? KV_POS_SMEM : KV_POS;
-          rec_stride = TFK_POS_STRIDE;
-          rec_reals = h->off_lrec + (in_smem ? 0 : n_crec); // link positions go straight into P
-        }
-    }
   }
   if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5 || variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM) && !ex &&
       jit_mode != JIT_OFF) {
@@ -547,7 +605,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   KernelArgs a;
   a.scratch = nullptr;
   if (variant != KV_FUSED_SMEM && variant != KV_FUSED_SMEM5) {
-    const size_t rec_bytes = (size_t)grid * rec_stride * (size_t)std::max(rec_reals, 1) * real_size(precision);
+    const size_t rec_bytes = (size_t)grid * TFK_TILE * (size_t)std::max(rec_reals, 1) * real_size(precision);
     a.scratch = workspace(device, stream, rec_bytes).scratch;
   }
   a.tables = table_bytes ? plan_on_device(e, device, stream) + h->off_outs : nullptr;
@@ -560,7 +618,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.J = d_J;
   a.pairs = sqdist ? ex->d_pairs : nullptr;
   a.n_pairs = n_pairs;
-  a.sub_cfg = twophase ? tile_cfgs : pos_sub;
+  a.sub_cfg = twophase ? tile_cfgs : 0;
   a.weights = com ? ex->d_weights : nullptr;
   a.n_com = com ? ex->n_com : 0;
   a.n_act = com ? ex->n_act : 0;
@@ -570,6 +628,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   ck(precision == PREC_F32 ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
                            : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
      "kernel launch");
+  e.launched_on.insert(device);
   g_launches.fetch_add(1);
   last_launch.grid = grid;
   last_launch.block = TFK_TILE;
@@ -705,8 +764,8 @@ void Engine::sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq
     sqdists_device(cur, st, pp.dq[0], nc, ps, pp.dP[0], ps.with_grads ? pp.dJ[0] : nullptr, nc, 0);
     ck(cudaMemcpyAsync(static_cast<char *>(sq) + (size_t)r0 * row_out, pp.dP[0], (size_t)nc * row_out, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(sq)");
     if (ps.with_grads && h.n_out_cols > 0)
-      ck(cudaMemcpy2DAsync(static_cast<char *>(G) + (size_t)r0 * row_out, (size_t)n * row_out, pp.dJ[0], (size_t)nc * row_out,
-                           (size_t)nc * row_out, (size_t)h.n_out_cols, cudaMemcpyDeviceToHost, st), "cudaMemcpy2DAsync(G)");
+      copy_columns_d2h(cur, static_cast<char *>(G) + (size_t)r0 * row_out, (size_t)n * row_out, static_cast<const char *>(pp.dJ[0]),
+                       (size_t)nc * row_out, (size_t)nc * row_out, (size_t)h.n_out_cols, st, "device->host copy of the gradients");
     ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
   }
   // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:205-209)
@@ -913,8 +972,8 @@ void Engine::com_host(const void *q, int64_t n, const ComSpec &cs_in, void *com,
     comT.resize((size_t)nc * 3 * sz);
     ck(cudaMemcpyAsync(comT.data(), pp.dP[0], (size_t)nc * 3 * sz, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync(com)");
     if (cs.with_jacobian && n_dof > 0)
-      ck(cudaMemcpy2DAsync(static_cast<char *>(J) + (size_t)r0 * 3 * sz, (size_t)n * 3 * sz, pp.dJ[0], (size_t)nc * 3 * sz,
-                           (size_t)nc * 3 * sz, (size_t)n_dof, cudaMemcpyDeviceToHost, st), "cudaMemcpy2DAsync(J)");
+      copy_columns_d2h(cur, static_cast<char *>(J) + (size_t)r0 * 3 * sz, (size_t)n * 3 * sz, static_cast<const char *>(pp.dJ[0]),
+                       (size_t)nc * 3 * sz, (size_t)nc * 3 * sz, (size_t)n_dof, st, "device->host copy of the COM Jacobian");
     ck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
     for (int64_t i = 0; i < nc; ++i) // (3, nc) component-major -> (n, 3) rows
       for (int k = 0; k < 3; ++k)
@@ -936,9 +995,30 @@ void Engine::com_host(const void *q, int64_t n, const ComSpec &cs_in, void *com,
 }
 
 
+// Columns of J that are constants of the plan never cross PCIe on the host path: a joint that moves none of the
+// requested links gives an all-zero column (PlanCol::arec < 0, include/tinyfk.hpp:31-46) and the base-translation
+// columns are the unit vectors of src/kinematics.cpp:194-196.  The kernel still writes them into the device staging
+// buffer (the device entry's contract is "every entry written"); the host entry fills them with a few CPU threads while
+// the copies of the other columns run (cfg2: 96 of 528 output bytes per configuration).
+namespace {
+template <class T> void fill_const_rows(T *col, size_t r0, size_t r1, int pd, int unit_k) {
+  const size_t block = (size_t)pd * 4096;
+  for (size_t b = r0; b < r1; b += block) {
+    const size_t e = std::min(r1, b + block);
+    std::memset(col + b, 0, (e - b) * sizeof(T));
+    if (unit_k >= 0) {
+      size_t r = b + ((size_t)unit_k + pd - b % pd) % pd;
+      for (; r < e; r += pd) col[r] = T(1);
+    }
+  }
+}
+} // namespace
+
 // Host buffers in, host buffers out.  The batch is cut into contiguous per-device slices (no
 // collective: configurations are independent) and each slice into chunks that ping-pong between two
 // stream slots, so chunk k's device->host copies overlap chunk k+1's host->device copy and kernel.
+// With several devices every device is driven by its own host thread (a pageable source or destination makes the
+// copies synchronous for the issuing thread; one thread per device keeps the devices independent).
 void Engine::solve_host(const void *q, int64_t n, const SolveSpec &spec, const int *devices, int n_devices, void *P,
                         void *J) {
   if (n < 0) throw std::invalid_argument("negative batch size");
@@ -959,8 +1039,11 @@ void Engine::solve_host(const void *q, int64_t n, const SolveSpec &spec, const i
     devs.push_back(cur);
   int count = 0;
   ck(cudaGetDeviceCount(&count), "cudaGetDeviceCount");
-  for (int d : devs)
-    if (d < 0 || d >= count) throw std::invalid_argument("device ordinal " + std::to_string(d) + " out of range");
+  for (size_t i = 0; i < devs.size(); ++i) {
+    if (devs[i] < 0 || devs[i] >= count) throw std::invalid_argument("device ordinal " + std::to_string(devs[i]) + " out of range");
+    for (size_t k = 0; k < i; ++k)
+      if (devs[k] == devs[i]) throw std::invalid_argument("device ordinal " + std::to_string(devs[i]) + " listed twice");
+  }
   const int G = (int)devs.size();
 
   const size_t sz = real_size(spec.precision);
@@ -973,67 +1056,141 @@ void Engine::solve_host(const void *q, int64_t n, const SolveSpec &spec, const i
   chunk = std::max<int64_t>(chunk, 8192);
   chunk = (chunk + TFK_TILE - 1) / TFK_TILE * TFK_TILE;
 
-  const int64_t per_dev = (n + G - 1) / G;
-  struct Slice {
-    int64_t begin, end, next;
-  };
-  std::vector<Slice> sl(G);
-  for (int g = 0; g < G; ++g) {
-    sl[g].begin = std::min<int64_t>(n, (int64_t)g * per_dev);
-    sl[g].end = std::min<int64_t>(n, (int64_t)(g + 1) * per_dev);
-    sl[g].next = sl[g].begin;
+  // which columns of J are constants of the plan: -2 = copied from the device, -1 = zeros, k >= 0 = unit vector e_k
+  std::vector<int> col_kind(jac ? h.n_out_cols : 0, -2);
+  if (jac && !std::getenv("TFK_D2H_ALL")) { // (env: A/B knob for measurements)
+    const PlanCol *cols = reinterpret_cast<const PlanCol *>(e.blob.data() + h.off_cols);
+    for (int c = 0; c < h.n_cols; ++c)
+      if (cols[c].arec < 0) col_kind[c] = -1;
+    const int n_trans = h.base_type == BASE_FIXED ? 0 : (h.base_type == BASE_PLANER ? 2 : 3);
+    for (int k = 0; k < n_trans; ++k) col_kind[h.n_cols + k] = k;
   }
+  std::vector<std::pair<int, int>> copy_runs; // [first, last) runs of columns that do come from the device
+  for (int c = 0; c < (int)col_kind.size();) {
+    if (col_kind[c] != -2) {
+      ++c;
+      continue;
+    }
+    int c1 = c;
+    while (c1 < (int)col_kind.size() && col_kind[c1] == -2) ++c1;
+    copy_runs.emplace_back(c, c1);
+    c = c1;
+  }
+
+  const int64_t per_dev = (n + G - 1) / G;
   const char *qb = static_cast<const char *>(q);
   char *Pb = static_cast<char *>(P);
   char *Jb = static_cast<char *>(J);
 
-  try {
-    bool work = true;
-    for (int64_t k = 0; work; ++k) {
-      work = false;
-      for (int g = 0; g < G; ++g) {
-        if (sl[g].next >= sl[g].end) continue;
-        work = true;
-        const int64_t r0 = sl[g].next;
-        const int64_t nc = std::min<int64_t>(chunk, sl[g].end - r0);
-        sl[g].next += nc;
-        const int dev = devs[g];
-        ck(cudaSetDevice(dev), "cudaSetDevice");
-        HostPipe &pp = pipe(dev);
-        const int s = (int)(k & 1);
-        cudaStream_t st = pp.stream[s];
-        const int64_t capn = std::min<int64_t>(chunk, per_dev); // size once for a full chunk
-        grow(&pp.dq[s], &pp.cap_q[s], std::max<size_t>((size_t)capn * in_row, 16), st);
-        grow(&pp.dP[s], &pp.cap_P[s], (size_t)capn * p_cfg * h.pose_dim, st);
-        if (jac) grow(&pp.dJ[s], &pp.cap_J[s], (size_t)capn * j_cfg * h.n_out_cols, st);
-
-        if (in_row)
-          ck(cudaMemcpyAsync(pp.dq[s], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st),
-             "cudaMemcpyAsync(q)");
-        launch(dev, st, e, spec.precision, pp.dq[s], nc, pp.dP[s], jac ? pp.dJ[s] : nullptr, nc, 0);
-        // one contiguous run per output column (column-major destination dimensioned for all n): a single strided
-        // copy per array keeps the copy engine busy back to back (16 separate copies per chunk cost ~5-10 % of PCIe time;
-        // letting the kernel store straight into the pinned outputs was measured too and is slower)
-        ck(cudaMemcpy2DAsync(Pb + (size_t)r0 * p_cfg, (size_t)n * p_cfg, pp.dP[s], (size_t)nc * p_cfg, (size_t)nc * p_cfg,
-                             (size_t)h.pose_dim, cudaMemcpyDeviceToHost, st),
-           "cudaMemcpy2DAsync(P)");
-        if (jac && h.n_out_cols > 0)
-          ck(cudaMemcpy2DAsync(Jb + (size_t)r0 * j_cfg, (size_t)n * j_cfg, pp.dJ[s], (size_t)nc * j_cfg, (size_t)nc * j_cfg,
-                               (size_t)h.n_out_cols, cudaMemcpyDeviceToHost, st),
-             "cudaMemcpy2DAsync(J)");
+  // host threads that fill the constant columns (whole batch, split by rows) while the devices work
+  std::vector<std::thread> fillers;
+  {
+    std::vector<int> cc;
+    for (int c = 0; c < (int)col_kind.size(); ++c)
+      if (col_kind[c] != -2) cc.push_back(c);
+    if (!cc.empty()) {
+      const size_t rows = (size_t)n * h.n_out * h.pose_dim;
+      int nt = 4;
+      if (const char *t = std::getenv("TFK_FILL_THREADS")) nt = std::max(1, std::atoi(t));
+      nt = (int)std::min<size_t>((size_t)nt, std::max<size_t>(1, rows * cc.size() * sz >> 20)); // one thread per MB at least
+      const int pd = h.pose_dim, prec = spec.precision;
+      const size_t col_bytes = (size_t)n * j_cfg;
+      for (int t = 0; t < nt; ++t) {
+        const size_t r0 = rows * t / nt / pd * pd, r1 = (t + 1 == nt) ? rows : rows * (t + 1) / nt / pd * pd;
+        fillers.emplace_back([=]() {
+          for (int c : cc) {
+            char *col = Jb + (size_t)c * col_bytes;
+            if (prec == PREC_F32)
+              fill_const_rows(reinterpret_cast<float *>(col), r0, r1, pd, col_kind[c]);
+            else
+              fill_const_rows(reinterpret_cast<double *>(col), r0, r1, pd, col_kind[c]);
+          }
+        });
       }
     }
-    for (int g = 0; g < G; ++g) {
-      ck(cudaSetDevice(devs[g]), "cudaSetDevice");
-      HostPipe &pp = pipe(devs[g]);
-      ck(cudaStreamSynchronize(pp.stream[0]), "cudaStreamSynchronize");
-      ck(cudaStreamSynchronize(pp.stream[1]), "cudaStreamSynchronize");
+  }
+  struct JoinAll {
+    std::vector<std::thread> &t;
+    ~JoinAll() {
+      for (auto &x : t)
+        if (x.joinable()) x.join();
     }
-  } catch (...) {
-    cudaSetDevice(cur);
-    throw;
+  } join_fillers{fillers};
+
+  // stream slots and staging buffers of every device, created before the worker threads start (shared maps)
+  for (int g = 0; g < G; ++g) {
+    const int64_t begin = std::min<int64_t>(n, (int64_t)g * per_dev), end = std::min<int64_t>(n, (int64_t)(g + 1) * per_dev);
+    if (begin >= end) continue;
+    DeviceGuard dg(devs[g]);
+    HostPipe &pp = pipe(devs[g]);
+    const int64_t capn = std::min<int64_t>(chunk, per_dev); // size once for a full chunk
+    for (int s = 0; s < ((end - begin > chunk) ? 2 : 1); ++s) {
+      grow(&pp.dq[s], &pp.cap_q[s], std::max<size_t>((size_t)capn * in_row, 16), pp.stream[s]);
+      grow(&pp.dP[s], &pp.cap_P[s], (size_t)capn * p_cfg * h.pose_dim, pp.stream[s]);
+      if (jac) grow(&pp.dJ[s], &pp.cap_J[s], std::max<size_t>((size_t)capn * j_cfg * h.n_out_cols, 16), pp.stream[s]);
+    }
+  }
+
+  auto run_slice = [&](int g) {
+    const int64_t begin = std::min<int64_t>(n, (int64_t)g * per_dev), end = std::min<int64_t>(n, (int64_t)(g + 1) * per_dev);
+    if (begin >= end) return;
+    const int dev = devs[g];
+    ck(cudaSetDevice(dev), "cudaSetDevice");
+    HostPipe &pp = pipes_.find(dev)->second;
+    int64_t k = 0;
+    for (int64_t r0 = begin; r0 < end; ++k) {
+      const int64_t nc = std::min<int64_t>(chunk, end - r0);
+      const int s = (int)(k & 1);
+      cudaStream_t st = pp.stream[s];
+      if (in_row) {
+        NvtxRange r("tfk_solve_fk_host: H2D q");
+        ck(cudaMemcpyAsync(pp.dq[s], qb + (size_t)r0 * in_row, (size_t)nc * in_row, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(q)");
+      }
+      {
+        NvtxRange r("tfk_solve_fk_host: kernel");
+        std::lock_guard<std::mutex> lk(launch_mu_);
+        launch(dev, st, e, spec.precision, pp.dq[s], nc, pp.dP[s], jac ? pp.dJ[s] : nullptr, nc, 0);
+      }
+      // one contiguous run per output column (column-major destination dimensioned for all n): a single strided
+      // copy per array keeps the copy engine busy back to back (16 separate copies per chunk cost ~5-10 % of PCIe time;
+      // letting the kernel store straight into the pinned outputs was measured too and is slower)
+      NvtxRange r("tfk_solve_fk_host: D2H P, J");
+      copy_columns_d2h(dev, Pb + (size_t)r0 * p_cfg, (size_t)n * p_cfg, static_cast<const char *>(pp.dP[s]), (size_t)nc * p_cfg,
+                       (size_t)nc * p_cfg, (size_t)h.pose_dim, st, "device->host copy of P");
+      for (const auto &run : copy_runs)
+        copy_columns_d2h(dev, Jb + (size_t)run.first * n * j_cfg + (size_t)r0 * j_cfg, (size_t)n * j_cfg,
+                         static_cast<const char *>(pp.dJ[s]) + (size_t)run.first * nc * j_cfg, (size_t)nc * j_cfg, (size_t)nc * j_cfg,
+                         (size_t)(run.second - run.first), st, "device->host copy of J");
+      r0 += nc;
+    }
+    ck(cudaStreamSynchronize(pp.stream[0]), "cudaStreamSynchronize");
+    ck(cudaStreamSynchronize(pp.stream[1]), "cudaStreamSynchronize");
+  };
+
+  std::vector<std::exception_ptr> errs(G);
+  if (G == 1) {
+    try {
+      run_slice(0);
+    } catch (...) {
+      errs[0] = std::current_exception();
+    }
+  } else {
+    std::vector<std::thread> workers;
+    for (int g = 0; g < G; ++g)
+      workers.emplace_back([&, g]() {
+        try {
+          run_slice(g);
+        } catch (...) {
+          errs[g] = std::current_exception();
+        }
+      });
+    for (auto &w : workers) w.join();
   }
   cudaSetDevice(cur);
+  for (auto &x : fillers) x.join();
+  fillers.clear();
+  for (int g = 0; g < G; ++g)
+    if (errs[g]) std::rethrow_exception(errs[g]);
 
   // like the reference, the model is left at the LAST configuration (src/wrapper.cpp:85-89)
   std::vector<size_t> ids(spec.joint_ids, spec.joint_ids + spec.n_joint);

@@ -11,6 +11,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <set>
 #include <stdexcept>
 #include <thread>
 #include <string>
@@ -100,6 +101,7 @@ public:
   int64_t jit_threshold;
   void inertia_host(const void *q, int64_t n, const int *joint_ids, int n_joint, int precision, void *out);
   LaunchInfo last_launch;
+  size_t plan_cache_size() const; // signatures held (diagnostics, tests)
 
 private:
   struct SpecKernel { // one per (plan, precision)
@@ -117,7 +119,9 @@ private:
     ~SpecKernel();
   };
   struct PlanEntry {
-    PlanKey key;
+    PlanKey key;                     // the call signature; key.model_version = the model state the blob was built from
+    uint64_t last_used = 0;          // LRU tick
+    std::set<int> launched_on;       // devices that may still run a kernel of this entry (synchronised before it is freed)
     std::vector<unsigned char> blob;
     std::unique_ptr<PlanParams> params; // the kernel-parameter form of the blob (fk_plan.h)
     std::map<int, unsigned char *> on_device; // device ordinal -> uploaded copy
@@ -130,6 +134,7 @@ private:
   struct Workspace { // one per (device, stream): concurrent launches never share records
     void *scratch;
     size_t scratch_bytes;
+    std::vector<void *> outgrown; // grow-only: a captured CUDA graph may still name an older buffer (freed with the engine)
   };
   struct HostPipe { // per device: two slots of staging buffers, one stream each
     cudaStream_t stream[2];
@@ -147,6 +152,15 @@ private:
     double mass_total, vfs, com_diag;
   };
   PlanEntry &plan_for(const SolveSpec &spec);
+  void retire(std::unique_ptr<PlanEntry> &e); // waits for the devices it ran on, frees its tables and its specialised kernels
+  uint64_t plan_tick_ = 0;
+  std::mutex launch_mu_; // Engine::solve_host drives several devices from one thread each; launch() and its caches are shared
+  size_t max_pitch(int device);
+  std::map<int, size_t> max_pitch_;
+  // device -> host copy of `ncols` columns of `width` bytes (column-major source and destination): one strided copy, or one
+  // plain copy per column when a pitch exceeds what cudaMemcpy2D accepts (cudaDevAttrMaxPitch, 2 GiB - 1 on B200)
+  void copy_columns_d2h(int device, char *dst, size_t dst_pitch, const char *src, size_t src_pitch, size_t width, size_t ncols,
+                        cudaStream_t st, const char *what);
   const unsigned char *plan_on_device(PlanEntry &e, int device, cudaStream_t stream);
   Workspace &workspace(int device, cudaStream_t stream, size_t bytes);
   HostPipe &pipe(int device);

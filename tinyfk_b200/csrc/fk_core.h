@@ -705,7 +705,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     sink.stride = stride;
     phase_a_sink(pv, qrow, rec, rec_link, stride, sink);
   }
-  // the same with the caller's link sink (fk_pos_kernel writes link positions straight into P)
+  // the same with the caller's link sink
   template <class LinkSink>
   static TFK_FN void phase_a_sink(const PlanView &pv, const T *qrow, T *rec, T *rec_f, int stride, const LinkSink &sink) {
     const PlanHeader &h = *pv.h;
@@ -740,89 +740,6 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
     bs.stride = STRIDE;
     bs.at = h.off_base;
     emit_link(pv, e, o, rec, STRIDE, h.off_arec, h.off_prec, bs, out);
-  }
-
-  // ---------------------------------------------------------------------------------------------
-  // Position-only queries (RotationType IGNORE, several links: collision-sphere centres and their 3 x n
-  // Jacobians), phase B one OUTPUT ENTRY at a time.  fk_pos_kernel gives every thread one entry of a
-  // Jacobian column -- row r of link o of configuration il -- so that consecutive threads write consecutive
-  // addresses of J with no staging, and walks the columns with it:
-  //   J(r, c) = (axis_c x (p_o - pos_c))_r = a[r1]*d[r2] - a[r2]*d[r1],  r1 = (r+1)%3, r2 = (r+2)%3
-  // which is urdf::cross_product (pose.cpp:90-94) on the operands of src/kinematics.cpp:152-158, component r
-  // (same products, same order: bit-identical to emit_link).  rec_r / rec_r1 / rec_r2: the configuration's
-  // records shifted by r / r1 / r2 elements, so that a vector record `at` is read at rec_rk[at*STRIDE].
-  enum { REC_STRIDE = STRIDE };
-  static TFK_FN T pos_entry(const PlanHeader &h, const PlanCol &pc, const T *rec_r, const T *rec_r1, const T *rec_r2, T p1, T p2) {
-    const int aa = (h.off_arec + 3 * pc.arec) * STRIDE;
-    if (pc.prismatic) return rec_r[aa]; // src/kinematics.cpp:149-151
-    const int pa = (h.off_prec + 3 * pc.prec) * STRIDE;
-    const T a1 = rec_r1[aa], a2 = rec_r2[aa];
-    const T d1 = p1 - rec_r1[pa], d2 = p2 - rec_r2[pa];
-    return a1 * d2 - a2 * d1;
-  }
-  // The base-rotation columns of such a link (roll, pitch, yaw | yaw for PLANER; src/kinematics.cpp:182-232,
-  // position rows): one (configuration, link) per thread, same code as the tail of emit_link for LREC == 3.
-  // `out` must address column n_cols + n_trans first (StagedSink: running column pointer).
-  template <class OutSink> static TFK_FN void emit_base_rot_pos(const PlanView &pv, const V &ep, const T *rec, OutSink &out) {
-    const PlanHeader &h = *pv.h;
-    P e;
-    e.p = ep;
-    e.q = O::qidentity();
-    V erpy;
-    erpy.x = erpy.y = erpy.z = T(0);
-    BaseFromRec bs;
-    bs.rec = rec;
-    bs.stride = STRIDE;
-    bs.at = h.off_base;
-    out.begin();
-    const int n_trans = (h.base_type == 1) ? 2 : 3;
-    if (!ANALYTIC_BASE && h.base_type == 1) {
-      emit_planer_yaw(h, e, erpy, bs, out);
-      return;
-    }
-    const V base_p = bs.base_p();
-    const int k0 = (h.base_type == 1) ? 2 : 0;
-    if (ANALYTIC_BASE) {
-      V d;
-      d.x = e.p.x - base_p.x;
-      d.y = e.p.y - base_p.y;
-      d.z = e.p.z - base_p.z;
-      TFK_NOUNROLL
-      for (int k = k0; k < 3; ++k) {
-        T v[7];
-        const V dpos = O::cross(bs.w(k), d);
-        v[0] = dpos.x;
-        v[1] = dpos.y;
-        v[2] = dpos.z;
-        v[3] = v[4] = v[5] = v[6] = T(0);
-        out.put_J(h.n_cols + n_trans + (k - k0), v);
-      }
-      return;
-    }
-    const typename M::Den deps = M::den_(T(1e-7));
-    V bep; // tf_blink_to_elink, position only (the position rows never read the link rotation)
-    {
-      const P binv = bs.binv();
-      const V r = O::rotate(binv.q, e.p);
-      bep.x = r.x + binv.p.x;
-      bep.y = r.y + binv.p.y;
-      bep.z = r.z + binv.p.z;
-    }
-    TFK_NOUNROLL
-    for (int k = k0; k < 3; ++k) {
-      const V r = O::rotate(bs.bk(k), bep);
-      T v[7];
-      v[0] = (r.x + base_p.x) - e.p.x;
-      v[1] = (r.y + base_p.y) - e.p.y;
-      v[2] = (r.z + base_p.z) - e.p.z;
-      v[3] = v[4] = v[5] = v[6] = T(0);
-      {
-        T num[3] = {v[0], v[1], v[2]};
-        M::divn_(num, deps);
-        v[0] = num[0], v[1] = num[1], v[2] = num[2];
-      }
-      out.put_J(h.n_cols + n_trans + (k - k0), v);
-    }
   }
 
   // ---------------------------------------------------------------------------------------------

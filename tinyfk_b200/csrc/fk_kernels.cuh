@@ -382,183 +382,6 @@ template <class Core, bool SMEM_HOT> __device__ __forceinline__ void fk_twophase
 }
 #endif
 
-// Several links, RotationType IGNORE (collision-sphere centres + 3 x n position Jacobians: the store-bound shape,
-// BASELINE cfg4).
-//   Phase A: thread per configuration, as fk_twophase_kernel, except that link positions are written STRAIGHT INTO P
-//   (they are output anyway; the partial sectors merge in L2) and the joint records into the block's scratch
-//   ([k][TILE + 1]); the thread then copies its joint records into COLUMN ORDER, crec[6c + 0..2] = world axis of
-//   column c's joint, crec[6c + 3..5] = its position (shared memory when three blocks fit, else scratch), which
-//   takes the plan's (axis record, position record) indirection out of phase B.
-//   Phase B, in sub-tiles of `sub` configurations: their rows of P (contiguous) are read back from L2 into shared
-//   memory, then every thread owns one ENTRY of a Jacobian column (configuration il, link o, row r; consecutive
-//   threads = consecutive addresses, plain coalesced streaming stores, no staging strip, no warp barrier) and walks
-//   the columns with it at a constant record stride: four record reads, five FP64 operations, one select and one
-//   store per entry (same products in the same order as FkCore::emit_link).  Only the finite-difference
-//   base-rotation columns (moving base) are produced per (configuration, link) through the staged sink.
-template <class T> struct PosLinkSink { // FkCore::walk's link sink: positions of the link's outputs, into P
-  T *P;            // P + (row of this configuration) * n_out
-  long long ldP;
-  const int *first_out, *next_out; // outputs that name link record l: first_out[l], next_out[o], ... -1
-  template <class Pose> __device__ __forceinline__ void link(int lrec, const Pose &cur) const {
-    for (int o = first_out[lrec]; o >= 0; o = next_out[o]) {
-      P[o] = cur.p.x;
-      P[ldP + o] = cur.p.y;
-      P[2 * ldP + o] = cur.p.z;
-    }
-  }
-};
-
-template <class Core, bool SMEM_CREC>
-__global__ void __launch_bounds__(TFK_TILE, 3) fk_pos_kernel(const KernelArgs a, const __grid_constant__ PlanParams pp) {
-  typedef typename Core::T T;
-  enum { S = Core::REC_STRIDE };
-  static_assert(S == TFK_POS_STRIDE, "fk_pos_kernel wants the [k][TILE + 1] record layout");
-  extern __shared__ __align__(16) unsigned char smem[];
-  for (int i = threadIdx.x * 16; i < a.table_bytes; i += TFK_TILE * 16)
-    *reinterpret_cast<int4 *>(smem + i) = *reinterpret_cast<const int4 *>(a.tables + i);
-  const PlanHeader &h = pp.h;
-  PlanView pv;
-  pv.h = &pp.h;
-  pv.slots = pp.slots;
-  pv.cols = pp.cols;
-  pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
-  pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
-  const int n_out = h.n_out, n_cols = h.n_cols;
-  int *first_out = reinterpret_cast<int *>(smem + ((a.table_bytes + 15) & ~15)), *next_out = first_out + h.n_lrec;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int l = 0; l < h.n_lrec; ++l) first_out[l] = -1;
-    for (int o = n_out - 1; o >= 0; --o) {
-      const int l = pv.lrec_of_out[o];
-      next_out[o] = first_out[l];
-      first_out[l] = o;
-    }
-  }
-  __syncthreads();
-  const int n_crec = h.with_jacobian ? 6 * n_cols : 0;
-  const int sub = a.sub_cfg, lpitch = pos_lpitch(sub, n_out);
-  const SmemLayout L = smem_layout_pos(a.table_bytes, h.n_in, h.n_lrec, n_out, sub, SMEM_CREC ? n_crec : 0, (int)sizeof(T));
-  T *qs = reinterpret_cast<T *>(smem + L.q_off);
-  T *rec = static_cast<T *>(a.scratch) + (size_t)blockIdx.x * S * (h.off_lrec + (SMEM_CREC ? 0 : n_crec));
-  T *crec = SMEM_CREC ? reinterpret_cast<T *>(smem + L.rec_off) : rec + (size_t)S * h.off_lrec;
-  const T *q = static_cast<const T *>(a.q);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n_trans = h.base_type == 0 ? 0 : (h.base_type == 1 ? 2 : 3);
-  const long long ldP = a.ld_cfg * n_out, ldJ = ldP * 3;
-  const unsigned m_out = n_out > 1 ? 0xffffffffu / (unsigned)n_out + 1u : 0u; // x / d == umulhi(x, m) for x*d < 2^32, d > 1
-  unsigned long long prism = 0ull; // columns of prismatic joints (src/kinematics.cpp:149-151): J = axis
-  for (int c = 0; c < n_cols; ++c)
-    if (pp.cols[c].prismatic) prism |= 1ull << c;
-
-  StagedFactory<T, 3> fac;
-  fac.P = static_cast<T *>(a.P);
-  fac.J = static_cast<T *>(a.J) + (long long)(n_cols + n_trans) * ldJ; // first base-rotation column
-  fac.ldP = ldP;
-  fac.stg = qs + warp * TFK_STG; // the q tile is dead during phase B (TILE*q_pitch >= 4*TFK_STG)
-
-  const long long n_tiles = (a.n + TFK_TILE - 1) / TFK_TILE;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long i0 = tile * TFK_TILE;
-    const int nv = (a.n - i0 < TFK_TILE) ? (int)(a.n - i0) : (int)TFK_TILE;
-    const long long hbase = (a.row0 + i0) * n_out;
-    T *Pt = static_cast<T *>(a.P) + hbase;
-    stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
-    prefetch_q_tile(q, i0 + (long long)gridDim.x * TFK_TILE, a.n, h.n_in);
-    __syncthreads();
-    if ((int)threadIdx.x < nv) {
-      T *mine = rec + threadIdx.x;
-      PosLinkSink<T> sink;
-      sink.P = Pt + (long long)threadIdx.x * n_out;
-      sink.ldP = ldP;
-      sink.first_out = first_out;
-      sink.next_out = next_out;
-      Core::phase_a_sink(pv, qs + threadIdx.x * L.q_pitch, mine, mine, S, sink);
-      T *cr = crec + threadIdx.x;
-      TFK_NOUNROLL
-      for (int c = 0; c < n_crec / 6; ++c) { // joint records -> column order (a column no link depends on keeps zeros)
-        const PlanCol &pc = pp.cols[c];
-        T v[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
-        if (pc.arec >= 0) {
-          const T *ar = mine + (h.off_arec + 3 * pc.arec) * S;
-          v[0] = ar[0], v[1] = ar[S], v[2] = ar[2 * S];
-          if (!pc.prismatic) {
-            const T *pr = mine + (h.off_prec + 3 * pc.prec) * S;
-            v[3] = pr[0], v[4] = pr[S], v[5] = pr[2 * S];
-          }
-        }
-#pragma unroll
-        for (int k = 0; k < 6; ++k) cr[(6 * c + k) * S] = v[k];
-      }
-    }
-    if (h.with_jacobian) {
-      const int items = nv * n_out;
-      for (int s0 = 0; s0 < nv; s0 += sub) {
-        const int ns = nv - s0 < sub ? nv - s0 : sub;
-        const int sitems = ns * n_out;
-        __syncthreads(); // phase A's stores are visible; the q tile / the previous sub-tile's positions are dead
-        for (int d = 0; d < 3; ++d) { // the sub-tile's rows of P are contiguous: coalesced copy (L2 hits)
-          const T *src = Pt + d * ldP + (long long)s0 * n_out;
-          for (int k = threadIdx.x; k < sitems; k += TFK_TILE) qs[d * lpitch + k] = src[k];
-        }
-        __syncthreads();
-        T *Jt = static_cast<T *>(a.J) + (hbase + (long long)s0 * n_out) * 3;
-        const int entries = sitems * 3;
-        for (int e = threadIdx.x; e < entries; e += TFK_TILE) {
-          const int item = (int)__umulhi((unsigned)e, 0x55555556u); // e / 3
-          const int r = e - 3 * item;
-          const int il = (int)__umulhi((unsigned)item, m_out);
-          const int o = item - il * n_out;
-          const int r1 = r == 2 ? 0 : r + 1, r2 = r == 0 ? 2 : r - 1;
-          const T p1 = qs[r1 * lpitch + item], p2 = qs[r2 * lpitch + item];
-          const T *cc = crec + s0 + il;
-          const T *c1 = cc + r1 * S, *c2 = cc + r2 * S;
-          const uint32_t *mk = pv.masks + o * h.mask_words;
-          T *pj = Jt + e;
-          for (int cb = 0; cb < n_cols; cb += 32) {
-            const uint32_t m = mk[cb >> 5];
-            const int ce = n_cols - cb < 32 ? n_cols - cb : 32;
-#pragma unroll 8
-            for (int c = 0; c < ce; ++c) {
-              // (axis x (p - pos))_r = a[r1]*d[r2] - a[r2]*d[r1]: urdf::cross_product, pose.cpp:90-94, component r
-              const T a1 = c1[0], a2 = c2[0];
-              const T d1 = p1 - c1[3 * S], d2 = p2 - c2[3 * S];
-              T v = a1 * d2 - a2 * d1;
-              v = ((m >> c) & 1u) ? v : T(0); // the joint does not move this link (include/tinyfk.hpp:31-46)
-              __stcs(pj, v);
-              pj += ldJ;
-              c1 += 6 * S, c2 += 6 * S;
-            }
-          }
-          for (int k = 0; k < n_trans; ++k) { // base translation columns, src/kinematics.cpp:194-196
-            __stcs(pj, r == k ? T(1) : T(0));
-            pj += ldJ;
-          }
-          for (unsigned long long pb = prism; pb; pb &= pb - 1) { // prismatic joints: the column is the axis itself
-            const int c = __ffsll((long long)pb) - 1;
-            const T v = ((mk[c >> 5] >> (c & 31)) & 1u) ? cc[(6 * c + r) * S] : T(0);
-            __stcs(Jt + e + c * ldJ, v);
-          }
-        }
-      }
-      __syncthreads(); // the last sub-tile's positions are dead: the strips below alias them
-      if (h.base_type != 0) { // base rotation columns: one thread per (configuration, link), staged stores
-        for (int it0 = warp * 32; it0 < items; it0 += TFK_TILE) {
-          const int it = it0 + lane;
-          const int itc = it < items ? it : items - 1;
-          const int il = (int)__umulhi((unsigned)itc, m_out);
-          fac.nvalid = items - it0 < 32 ? items - it0 : 32;
-          fac.head0 = hbase + it0;
-          StagedSink<T, 3> out = fac.make();
-          typename Core::V ep;
-          ep.x = Pt[itc], ep.y = Pt[ldP + itc], ep.z = Pt[2 * ldP + itc];
-          Core::emit_base_rot_pos(pv, ep, rec + il, out);
-        }
-      }
-    }
-    __syncthreads();
-  }
-}
-
 // compute_inter_link_squared_dists (src/wrapper.cpp:189-237): phase A as in the two-phase kernel (plan over the
 // union of the pairs' links, positions only), then one thread per (configuration, pair): consecutive threads
 // write consecutive entries of sqdists and of every gradient column -- coalesced without staging.
@@ -816,38 +639,14 @@ template <class Core> cudaError_t occupancy_fk_core(int variant, int smem_bytes,
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fn, TFK_TILE, smem_bytes);
 }
 
-// fk_pos_kernel: RotationType IGNORE only, records in the [k][TILE + 1] layout
-template <class M, bool ANALYTIC_BASE> const void *pos_kernel_fn(int variant) {
-  typedef FkCore<M, ANALYTIC_BASE, 0, TFK_POS_STRIDE> Core;
-  return variant == KV_POS_SMEM ? (const void *)fk_pos_kernel<Core, true> : (const void *)fk_pos_kernel<Core, false>;
-}
-template <class M, bool ANALYTIC_BASE>
-cudaError_t launch_pos(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
-  typedef FkCore<M, ANALYTIC_BASE, 0, TFK_POS_STRIDE> Core;
-  if (variant == KV_POS_SMEM)
-    fk_pos_kernel<Core, true><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
-  else
-    fk_pos_kernel<Core, false><<<grid, TFK_TILE, smem_bytes, stream>>>(a, pp);
-  return cudaGetLastError();
-}
-
 // one instantiation per RotationType (the pose dimension is a compile-time constant of the kernels)
 template <class M, bool ANALYTIC_BASE>
 cudaError_t launch_fk(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes, cudaStream_t stream) {
-  if (variant == KV_POS || variant == KV_POS_SMEM) return launch_pos<M, ANALYTIC_BASE>(a, pp, variant, grid, smem_bytes, stream);
   if (pp.h.rot_type == 0) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 0, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
   if (pp.h.rot_type == 1) return launch_fk_core<FkCore<M, ANALYTIC_BASE, 1, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
   return launch_fk_core<FkCore<M, ANALYTIC_BASE, 2, TFK_TILE>>(a, pp, variant, grid, smem_bytes, stream);
 }
 template <class M, bool ANALYTIC_BASE> cudaError_t occupancy_fk(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
-  if (variant == KV_POS || variant == KV_POS_SMEM) {
-    const void *fn = pos_kernel_fn<M, ANALYTIC_BASE>(variant);
-    if (smem_bytes > 48 * 1024) {
-      cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-      if (e != cudaSuccess) return e;
-    }
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, fn, TFK_TILE, smem_bytes);
-  }
   if (rot_type == 0) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 0, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
   if (rot_type == 1) return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 1, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);
   return occupancy_fk_core<FkCore<M, ANALYTIC_BASE, 2, TFK_TILE>>(variant, smem_bytes, blocks_per_sm);

@@ -28,8 +28,6 @@ enum KernelVariant {
   KV_SQDIST_SMEM = 9,   // KV_SQDIST with [base | arec | prec] in shared memory
   KV_FUSED_SPEC = 7,  // plan-specialised build of the fused kernel, compiled at run time (jit.cpp)
      // total inertia matrix about the centre of mass: phase A (with rotations) -> records -> 3x3 sums
-  KV_POS = 10,       // several links, RotationType IGNORE: phase A -> records -> one thread per OUTPUT ENTRY (fk_pos_kernel)
-  KV_POS_SMEM = 11,  // KV_POS with the column-ordered joint records in shared memory
   KV_TWOPHASE_SPEC = 12, // plan-specialised build of the two-phase kernel (several links), compiled at run time
   KV_FUSED_SMEM5 = 3, // KV_FUSED_SMEM compiled for 5 resident blocks per SM (<= 96 registers), used when the
                       // shared-memory footprint leaves room for the fifth block
@@ -49,8 +47,7 @@ struct KernelArgs {
   int n_pairs;
   // KV_INERTIA: P = out (9, ld_cfg); weights = 7 reals per com link (mass, ixx, ixy, ixz, iyy, iyz, izz); n_com, mass_total
   // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
-  int sub_cfg;         // fk_pos_kernel: configurations per phase-B sub-tile (power of two, <= 32)
-                       // fk_twophase_kernel: configurations per tile (0 = TFK_TILE), twophase_tile_cfgs()
+  int sub_cfg;         // fk_twophase_kernel: configurations per tile (0 = TFK_TILE), twophase_tile_cfgs()
   const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
   int n_com, n_act;
   double mass_total, vfs, com_diag;
@@ -86,11 +83,6 @@ TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem,
   return smem_layout_tile(TFK_TILE, table_bytes, n_in, rec_reals_in_smem, real_bytes);
 }
 
-// fk_pos_kernel: records are [k][TFK_TILE + 1] (odd pitch: a warp reading three consecutive elements of ONE
-// configuration hits three banks, and one element of 32 configurations hits 32)
-enum { TFK_POS_STRIDE = TFK_TILE + 1 };
-// shared memory: [per-output tables | outputs of every link record (first_out[n_lrec], next_out[n_out]) | q tile, later
-// the sub-tile's link positions [3][sub*n_out | 1], later the warps' staging strips | column-ordered joint records (or none)]
 // fk_twophase_kernel: configurations per tile.  When the batch needs more than one wave of resident blocks, the last
 // wave is partly empty (cfg5 FP32: 512 tiles of 128 on 444 resident blocks = two rounds for 68 blocks, one for the
 // rest); half tiles even that out at the price of idle threads in phase A, so they are used only when the busiest
@@ -101,15 +93,6 @@ TFK_HDI int twophase_tile_cfgs(long long n, long long resident_blocks) {
   const int tc = TFK_TILE / 2;
   const long long half = (((n + tc - 1) / tc + resident_blocks - 1) / resident_blocks) * tc;
   return half * 108 < full * 100 ? tc : (int)TFK_TILE;
-}
-TFK_HDI int pos_lpitch(int sub, int n_out) { return (sub * n_out) | 1; }
-TFK_HDI SmemLayout smem_layout_pos(int table_bytes, int n_in, int n_lrec, int n_out, int sub, int rec_reals_in_smem, int real_bytes) {
-  const int tb = ((table_bytes + 15) & ~15) + (((n_lrec + n_out) * 4 + 15) & ~15);
-  SmemLayout L = smem_layout_tile(TFK_TILE, tb, n_in, 0, real_bytes);
-  const int lps = (3 * pos_lpitch(sub, n_out) * real_bytes + 15) & ~15;
-  if (L.rec_off - L.q_off < lps) L.rec_off = L.q_off + lps;
-  L.total = L.rec_off + rec_reals_in_smem * TFK_POS_STRIDE * real_bytes;
-  return L;
 }
 
 #if !defined(__CUDACC_RTC__)

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <limits>
 #include <map>
@@ -383,8 +384,12 @@ std::vector<double> KinematicModel::get_joint_effort_limits(const std::vector<si
 void KinematicModel::set_joint_angles(const std::vector<size_t> &ids, const std::vector<double> &angles) {
   if (ids.size() != angles.size()) throw std::invalid_argument("joint id / angle count mismatch");
   check_joint_ids(ids, joints_.size());
-  for (size_t i = 0; i < ids.size(); ++i) joint_angles_[ids[i]] = angles[i];
-  ++version_;
+  bool changed = false; // an unchanged state keeps the version: plans built from it stay valid (Engine::plan_for)
+  for (size_t i = 0; i < ids.size(); ++i) {
+    changed |= std::memcmp(&joint_angles_[ids[i]], &angles[i], sizeof(double)) != 0;
+    joint_angles_[ids[i]] = angles[i];
+  }
+  if (changed) ++version_;
 }
 
 std::vector<double> KinematicModel::get_joint_angles(const std::vector<size_t> &ids) const {
@@ -400,11 +405,13 @@ void KinematicModel::set_init_angles() {
 }
 
 void KinematicModel::set_base_pose_xyzrpy(const double b[6]) { // src/wrapper.cpp:25-35
-  base_pose_.p.x = b[0];
-  base_pose_.p.y = b[1];
-  base_pose_.p.z = b[2];
-  base_pose_.q = quat_from_rpy(b[3], b[4], b[5]);
-  ++version_;
+  Pose64 nb;
+  nb.p.x = b[0];
+  nb.p.y = b[1];
+  nb.p.z = b[2];
+  nb.q = quat_from_rpy(b[3], b[4], b[5]);
+  if (std::memcmp(&nb, &base_pose_, sizeof nb) != 0) ++version_; // see set_joint_angles
+  base_pose_ = nb;
 }
 
 void KinematicModel::get_base_pose_xyzrpy(double b[6]) const { // src/wrapper.cpp:45-55
