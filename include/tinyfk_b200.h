@@ -24,7 +24,10 @@
  *     with n_dof = n_joint (+3 PLANER: x, y, yaw columns, python/tinyfk/__init__.py:154-158; +6 FLOATING).
  *   - precision: TFK_F64_STRICT computes in double in the reference's operation order (matches the
  *     reference to 1e-12 and the libm-pinned reference bit for bit); TFK_F32 is the opt-in float mode
- *     (arrays are float, tolerance 1e-5).
+ *     (arrays are float, tolerance 1e-5); TFK_F64_FAST is the opt-in double mode with FMA contraction, the CUDA libm,
+ *     reciprocal-multiply quotients and ANALYTIC base-rotation Jacobian columns: poses and analytic Jacobian entries
+ *     within 1e-12 of the reference; its base-rotation columns are the exact derivative, which the reference's
+ *     eps = 1e-7 forward difference (src/kinematics.cpp:201-232) only approximates to ~1e-7 * |f''|.
  */
 #ifndef TINYFK_B200_H
 #define TINYFK_B200_H
@@ -47,7 +50,7 @@ typedef struct tfk_model tfk_model; /* opaque: tinyfk::KinematicModel (include/t
 enum { TFK_OK = 0, TFK_ERR_INVALID = 1, TFK_ERR_RUNTIME = 2, TFK_ERR_CUDA = 3 };
 enum { TFK_ROT_IGNORE = 0, TFK_ROT_RPY = 1, TFK_ROT_XYZW = 2 };
 enum { TFK_BASE_FIXED = 0, TFK_BASE_PLANER = 1, TFK_BASE_FLOATING = 2 };
-enum { TFK_F64_STRICT = 0, TFK_F32 = 1 };
+enum { TFK_F64_STRICT = 0, TFK_F32 = 1, TFK_F64_FAST = 2 };
 enum { TFK_LIBM_PORTABLE = 0, TFK_LIBM_SYSTEM = 1 };
 
 /* message of the last failing call on this thread */

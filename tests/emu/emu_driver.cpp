@@ -300,6 +300,8 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     run<FkCore<MathPortable, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);             \
   else if (mode == 1)                                                                       \
     run<FkCore<MathNative32, true, R, 1>, float>(blob, qs, n, P, Jp, two_phase);               \
+  else if (mode == 3)                                                                       \
+    run<FkCore<MathFast64, true, R, 1>, double>(blob, qs, n, P, Jp, two_phase);                \
   else                                                                                      \
     run<FkCore<MathNative64, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);
     if (rot_type == 0) {

@@ -12,7 +12,7 @@ _dp = ctypes.POINTER(ctypes.c_double)
 _ip = ctypes.POINTER(ctypes.c_int)
 _lib = None
 
-MODE_STRICT64, MODE_F32, MODE_NATIVE64 = 0, 1, 2
+MODE_STRICT64, MODE_F32, MODE_NATIVE64, MODE_FAST64 = 0, 1, 2, 3
 
 
 def _srcs():

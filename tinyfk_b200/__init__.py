@@ -7,7 +7,7 @@ numerics run in hand-written CUDA kernels for sm_100a through the C ABI in
 ``include/tinyfk_b200.h``; there is no CPU compute path -- importing this package without the built
 extension raises ImportError, and solving without a CUDA device raises RuntimeError.
 
-New relative to the reference: ``solve_fk(..., precision="fp64" | "fp32", devices=[...])`` -- an
+New relative to the reference: ``solve_fk(..., precision="fp64" | "fp32" | "fp64_fast", devices=[...])`` -- an
 (N, n_dof) ndarray of configurations is solved in one launch per chunk and sharded over the listed
 GPUs in contiguous slices.
 """
@@ -56,7 +56,7 @@ class RotationType(Enum):  # reference python/tinyfk/__init__.py:35-38
 
 
 _ROT_CODE = {RotationType.IGNORE: 0, RotationType.RPY: 1, RotationType.XYZW: 2}
-_PRECISION = {"fp64": 0, "f64": 0, "double": 0, "strict": 0, "fp32": 1, "f32": 1, "float": 1}
+_PRECISION = {"fp64": 0, "f64": 0, "double": 0, "strict": 0, "fp32": 1, "f32": 1, "float": 1, "fp64_fast": 2, "f64_fast": 2}
 
 
 class KinematicModel:

@@ -226,7 +226,7 @@ void Engine::spec_start(PlanEntry &e, int precision, bool wait) {
 }
 
 SpecInfo Engine::specialize(const SolveSpec &spec, bool wait, bool compile_only) {
-  if (spec.precision != PREC_F64_STRICT && spec.precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
+  if (spec.precision < 0 || spec.precision >= PREC_COUNT) throw std::invalid_argument("unknown precision mode");
   PlanEntry &e = plan_for(spec);
   SpecKernel &sk = e.spec[spec.precision];
   spec_start(e, spec.precision, wait);
@@ -524,7 +524,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   if (n <= 0 || h->n_out == 0) return;
   const bool sqdist = ex && ex->variant == KV_SQDIST, com = ex && (ex->variant == KV_COM || ex->variant == KV_INERTIA);
   const int n_pairs = sqdist ? ex->n_pairs : 0;
-  if (precision != PREC_F64_STRICT && precision != PREC_F32) throw std::invalid_argument("unknown precision mode");
+  if (precision < 0 || precision >= PREC_COUNT) throw std::invalid_argument("unknown precision mode");
   const int rb = (int)real_size(precision);
   // per-output tables of the two-phase kernel: [lrec_of_out | masks], contiguous inside the blob
   const int table_bytes = (h->n_out == 1 && !ex) ? 0 : ((h->off_cols - h->off_outs + 15) & ~15);
@@ -589,8 +589,9 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   int bps = 0;
   if (oit == occupancy_.end()) {
     // also raises the kernel's dynamic shared memory limit on this device when smem > 48 KB
-    ck(precision == PREC_F32 ? occupancy_fk_f32(h->rot_type, variant, smem, &bps)
-                             : occupancy_fk_f64_strict(h->rot_type, variant, smem, &bps),
+    ck(precision == PREC_F32        ? occupancy_fk_f32(h->rot_type, variant, smem, &bps)
+       : precision == PREC_F64_FAST ? occupancy_fk_f64_fast(h->rot_type, variant, smem, &bps)
+                                    : occupancy_fk_f64_strict(h->rot_type, variant, smem, &bps),
        "occupancy query");
     if (bps < 1) throw CudaError("kernel does not fit on an SM");
     occupancy_[okey] = bps;
@@ -625,8 +626,9 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.mass_total = com ? ex->mass_total : 0.0;
   a.vfs = com ? ex->vfs : 0.0;
   a.com_diag = com ? ex->com_diag : 0.0;
-  ck(precision == PREC_F32 ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
-                           : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
+  ck(precision == PREC_F32        ? launch_fk_f32(a, *e.params, variant, grid, smem, stream)
+     : precision == PREC_F64_FAST ? launch_fk_f64_fast(a, *e.params, variant, grid, smem, stream)
+                                  : launch_fk_f64_strict(a, *e.params, variant, grid, smem, stream),
      "kernel launch");
   e.launched_on.insert(device);
   g_launches.fetch_add(1);

@@ -125,7 +125,7 @@ private:
     std::vector<unsigned char> blob;
     std::unique_ptr<PlanParams> params; // the kernel-parameter form of the blob (fk_plan.h)
     std::map<int, unsigned char *> on_device; // device ordinal -> uploaded copy
-    SpecKernel spec[2];                       // by precision
+    SpecKernel spec[PREC_COUNT];              // by precision mode
     int64_t configs_served = 0;
   };
   bool spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *kind, std::string *why) const;

@@ -11,4 +11,12 @@ cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant
 cudaError_t occupancy_fk_f32(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
   return occupancy_fk<MathNative32, true>(rot_type, variant, smem_bytes, blocks_per_sm);
 }
+// opt-in FP64 fast mode (fk_math.h MathFast64): 1e-12 on poses and analytic Jacobian entries, not bit-identical
+cudaError_t launch_fk_f64_fast(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
+    cudaStream_t stream) {
+  return launch_fk<MathFast64, true>(a, pp, variant, grid, smem_bytes, stream);
+}
+cudaError_t occupancy_fk_f64_fast(int rot_type, int variant, int smem_bytes, int *blocks_per_sm) {
+  return occupancy_fk<MathFast64, true>(rot_type, variant, smem_bytes, blocks_per_sm);
+}
 } // namespace tfk

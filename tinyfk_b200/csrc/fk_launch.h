@@ -15,6 +15,9 @@ namespace tfk {
 enum Precision {
   PREC_F64_STRICT = 0, // reference operation order, portable libm, FD base columns, no FMA contraction
   PREC_F32 = 1,        // float arithmetic, libdevice libm, analytic base-rotation columns
+  PREC_F64_FAST = 2,   // double arithmetic with FMA contraction, libdevice libm, reciprocal-multiply quotients, analytic
+                       // base-rotation columns: 1e-12 on poses and analytic columns, not bit-identical
+  PREC_COUNT = 3,
 };
 
 enum KernelVariant {
@@ -102,6 +105,9 @@ cudaError_t occupancy_fk_f64_strict(int rot_type, int variant, int smem_bytes, i
 cudaError_t launch_fk_f32(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
                           cudaStream_t stream);
 cudaError_t occupancy_fk_f32(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
+cudaError_t launch_fk_f64_fast(const KernelArgs &a, const PlanParams &pp, int variant, int grid, int smem_bytes,
+                               cudaStream_t stream);
+cudaError_t occupancy_fk_f64_fast(int rot_type, int variant, int smem_bytes, int *blocks_per_sm);
 #endif
 
 } // namespace tfk

@@ -224,17 +224,74 @@ struct MathNative32 {
   static TFK_FN float atan2_(float y, float x) { return ::atan2f(y, x); }
   static TFK_FN float atan2_rare_(float y, float x) { return ::atan2f(y, x); }
   static TFK_FN float sqrt_(float x) { return ::sqrtf(x); }
+  // Several quotients by one denominator (quaternion / norm, rpy_derivative coefficients / cos): ONE reciprocal --
+  // MUFU.RCP (1 ulp) and one Newton step -- then a multiplication per quotient (relative error < 2^-22, against the 1e-5
+  // contract of this mode).  The IEEE division the compiler emits for `a / b` is ~10 instructions and a slow-path branch
+  // per quotient: in the round-1 capture (profiles/r2_full_cfg2_fp32_v12.txt) 24 % of the kernel's instructions.
   struct Den {
-    float b;
+    float b, y;
   };
   static TFK_FN Den den_(float b) {
     Den d;
     d.b = b;
+#if defined(__CUDA_ARCH__)
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(b));
+    const float y1 = fmaf(y, fmaf(-b, y, 1.0f), y);
+    d.y = (fabsf(y) < 3.0e38f) ? y1 : y; // b == 0 keeps the infinity
+#else
+    d.y = 1.0f / b;
+#endif
     return d;
   }
-  static TFK_FN float div_(float a, const Den &d) { return a / d.b; }
+  static TFK_FN float div_(float a, const Den &d) { return a * d.y; }
   template <int N> static TFK_FN void divn_(float (&a)[N], const Den &d) {
-    for (int i = 0; i < N; ++i) a[i] = a[i] / d.b;
+    TFK_MATH_UNROLL
+    for (int i = 0; i < N; ++i) a[i] = a[i] * d.y;
+  }
+};
+
+// Opt-in FP64 "fast" mode (SURVEY.md section 7 hard part 4): double arithmetic with FMA contraction (the translation
+// unit is built with the default -fmad=true), the platform libm (libdevice), quotients through one correctly rounded
+// reciprocal and a multiplication (1 ulp), base-rotation columns analytic.  Not bit-identical to the reference: the
+// contract is 1e-12 on poses and analytic Jacobian entries.
+struct MathFast64 {
+  typedef double real;
+  static TFK_FN double sin_(double x) { return ::sin(x); }
+  static TFK_FN double cos_(double x) { return ::cos(x); }
+  static TFK_FN void sincos_(double x, double *s, double *c) {
+#if defined(__CUDA_ARCH__)
+    ::sincos(x, s, c);
+#else
+    *s = ::sin(x);
+    *c = ::cos(x);
+#endif
+  }
+  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
+    sincos_(xa, sa, ca);
+    sincos_(xb, sb, cb);
+  }
+  static TFK_FN double asin_(double x) { return ::asin(x); }
+  static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
+  static TFK_FN double atan2_rare_(double y, double x) { return ::atan2(y, x); }
+  static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
+  struct Den {
+    double b, y;
+  };
+  static TFK_FN Den den_(double b) {
+    Den d;
+    d.b = b;
+#if defined(__CUDA_ARCH__)
+    d.y = __drcp_rn(b);
+#else
+    d.y = 1.0 / b;
+#endif
+    return d;
+  }
+  static TFK_FN double div_(double a, const Den &d) { return a * d.y; }
+  template <int N> static TFK_FN void divn_(double (&a)[N], const Den &d) {
+    TFK_MATH_UNROLL
+    for (int i = 0; i < N; ++i) a[i] = a[i] * d.y;
   }
 };
 

@@ -133,14 +133,15 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   } else {
     s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
   }
-  if (o.kind != 0 && !f32) s += "#define TFK_SPEC_ROLLED_WALK 1\n"; // several links, FP64: fk_core.h TFK_WALK_LOOP
+  if (o.kind != 0 && o.precision == PREC_F64_STRICT) s += "#define TFK_SPEC_ROLLED_WALK 1\n"; // several links, FP64: fk_core.h TFK_WALK_LOOP
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;
   s += "#include \"fk_kernels.cuh\"\n";
   s += "extern \"C\" __global__ void __launch_bounds__(tfk::TFK_TILE, " + std::to_string(o.blocks_per_sm) +
        ") tfk_spec_kernel(const tfk::KernelArgs a) {\n";
-  const std::string core = std::string("tfk::FkCore<") + (f32 ? "tfk::MathNative32, true, " : "tfk::MathPortable, false, ") +
+  const std::string core = std::string("tfk::FkCore<") +
+                           (f32 ? "tfk::MathNative32, true, " : (o.precision == PREC_F64_FAST ? "tfk::MathFast64, true, " : "tfk::MathPortable, false, ")) +
                            std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
   if (o.kind == 0)
     s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";

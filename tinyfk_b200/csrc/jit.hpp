@@ -19,7 +19,7 @@
 namespace tfk {
 
 struct SpecOptions {
-  int precision;  // PREC_F64_STRICT | PREC_F32
+  int precision;  // PREC_F64_STRICT | PREC_F32 | PREC_F64_FAST
   int rot_type;   // compile-time RotationType of FkCore
   int tile;       // threads per block == configurations per tile (a multiple of 32)
   int blocks_per_sm;

@@ -122,7 +122,7 @@ public:
   // The new batched overload: qs is an (N, n_dof) ndarray; base_type 0/1/2; returns (P, J) F-ordered
   // exactly like the reference.  J is all zeros (lazily allocated) when with_jacobian is false, as
   // src/wrapper.cpp:81-82 returns it.
-  py::tuple solve_batch(py::array qs_in, const std::vector<size_t> &elink_ids, const std::vector<size_t> &joint_ids,
+  py::tuple solve_batch(py::object qs_in, const std::vector<size_t> &elink_ids, const std::vector<size_t> &joint_ids,
                         int rot_type, int base_type, bool with_jacobian, int precision, const std::vector<int> &devices,
                         bool pinned_output) {
     if (rot_type < 0 || rot_type > 2) throw std::invalid_argument("bad rot_type");
@@ -138,7 +138,7 @@ public:
   }
 
   // The reference's 7-argument entry (src/wrapper.cpp:60-124): with_base means the 6-D floating base.
-  py::tuple solve_forward_kinematics(py::array qs, const std::vector<size_t> &elink_ids,
+  py::tuple solve_forward_kinematics(py::object qs, const std::vector<size_t> &elink_ids,
                                      const std::vector<size_t> &joint_ids, RotationType rot_type, bool with_base,
                                      bool with_jacobian, bool /*use_cache: no cache exists*/) {
     py::array_t<double, py::array::c_style | py::array::forcecast> a =
@@ -152,7 +152,7 @@ public:
 
   // compute_inter_link_squared_dists (src/wrapper.cpp:189-237), batched: returns (sqdists [n*n_check],
   // grads (n*n_check, n_dof) F-ordered; a 1x1 zero matrix when !with_grads, as the reference)
-  py::tuple sqdists_batch(py::array qs_in, const std::vector<size_t> &link_ids1, const std::vector<size_t> &link_ids2,
+  py::tuple sqdists_batch(py::object qs_in, const std::vector<size_t> &link_ids1, const std::vector<size_t> &link_ids2,
                           const std::vector<size_t> &joint_ids, int base_type, bool with_grads, int precision) {
     if (base_type < 0 || base_type > 2) throw std::invalid_argument("bad base_type");
     if (link_ids1.size() != link_ids2.size()) throw std::invalid_argument("link_ids1 and link_ids2 differ in length");
@@ -165,7 +165,7 @@ public:
                           with_grads, precision, n_in);
   }
   // the reference's 7-argument entry: with_base means the 6-D floating base; use_cache has no meaning here
-  py::tuple compute_inter_link_squared_dists(py::array qs, const std::vector<size_t> &link_ids1,
+  py::tuple compute_inter_link_squared_dists(py::object qs, const std::vector<size_t> &link_ids1,
                                              const std::vector<size_t> &link_ids2, const std::vector<size_t> &joint_ids,
                                              bool with_base, bool with_grads, bool /*use_cache*/) {
     return sqdists_batch(qs, link_ids1, link_ids2, joint_ids, with_base ? TFK_BASE_FLOATING : TFK_BASE_FIXED, with_grads,
@@ -175,7 +175,7 @@ public:
   // solve_com_forward_kinematics (src/wrapper.cpp:126-179), batched: returns (coms (n, 3), J (3n, n_dof) F-ordered,
   // all zeros when !with_jacobian as the reference).  base_type PLANER takes (x, y, yaw) rows and returns the six
   // base columns of the padded row, as KinematicModel.solve_com_fk does (python/tinyfk/__init__.py:180-195).
-  py::tuple com_batch(py::array qs_in, const std::vector<size_t> &joint_ids, const std::vector<size_t> &action_link_ids,
+  py::tuple com_batch(py::object qs_in, const std::vector<size_t> &joint_ids, const std::vector<size_t> &action_link_ids,
                       const std::vector<double> &forces, int base_type, bool with_jacobian, int precision) {
     if (base_type < 0 || base_type > 2) throw std::invalid_argument("bad base_type");
     if (action_link_ids.size() != forces.size()) throw std::invalid_argument("action_link_ids and forces differ in length");
@@ -188,7 +188,7 @@ public:
                            with_jacobian, precision, n_in);
   }
   // the reference's 6-argument entry: with_base means the 6-D floating base
-  py::tuple solve_com_forward_kinematics(py::array qs, const std::vector<size_t> &joint_ids,
+  py::tuple solve_com_forward_kinematics(py::object qs, const std::vector<size_t> &joint_ids,
                                          const std::vector<size_t> &action_link_ids, const std::vector<double> &forces,
                                          bool with_base, bool with_jacobian) {
     return com_batch(qs, joint_ids, action_link_ids, forces, with_base ? TFK_BASE_FLOATING : TFK_BASE_FIXED, with_jacobian,
@@ -196,7 +196,7 @@ public:
   }
 
   // compute_total_inertia_matrix (src/wrapper.cpp:181-187): one configuration -> 3x3; the batched form returns (n, 3, 3)
-  py::array inertia_batch(py::array qs_in, const std::vector<size_t> &joint_ids, int precision) {
+  py::array inertia_batch(py::object qs_in, const std::vector<size_t> &joint_ids, int precision) {
     std::vector<int> j = to_int(joint_ids);
     if (precision == TFK_F32)
       return run_inertia<float>(py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(qs_in), j, precision);
