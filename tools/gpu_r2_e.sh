@@ -1,0 +1,22 @@
+# cycle E (2 or 8 GPUs): the engine's own device-list split on real devices, the new bench.py alone and under torchrun,
+# the D2H ceiling per process layout
+NG=${1:-2}
+mkdir -p gpurun_out
+( time python -m pytest tests/test_multi_device.py -x -q -rs ) > gpurun_out/e_t_${NG}.log 2>&1; tail -12 gpurun_out/e_t_${NG}.log
+python bench.py --steps 50 > gpurun_out/e_b1_${NG}.log 2>&1; tail -c 400 gpurun_out/e_b1_${NG}.log
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $NG --steps 50 --warmup 5 > gpurun_out/e_bN_${NG}.log 2>&1
+python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/e_ref_${NG}.log 2>&1
+python tools/d2h_bw.py > gpurun_out/e_d2h_${NG}.log 2>&1
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29512 tools/d2h_bw.py >> gpurun_out/e_d2h_${NG}.log 2>&1
+grep "^{" gpurun_out/e_d2h_${NG}.log
+nvidia-smi topo -m > gpurun_out/e_topo_${NG}.log 2>&1; nproc >> gpurun_out/e_topo_${NG}.log
+python - <<PY
+import json
+for f in ("gpurun_out/e_b1_${NG}.log", "gpurun_out/e_bN_${NG}.log", "gpurun_out/e_ref_${NG}.log"):
+  for l in open(f):
+    if l.startswith("{"):
+        d=json.loads(l); print(d.get("impl","ours"), "N", d["n_gpus"], "%.3e"%d["value"], "%.4f ms"%d["ms_per_step"], "frac", d.get("roofline",{}).get("frac"), "clocks", d.get("clocks"))
+        print("  e2e", d.get("e2e",{}).get("value"), "inproc", d.get("e2e_inprocess",{}).get("value"), "cpu", d.get("cpu_baseline",{}).get("value"))
+        for w in d.get("workloads", []): print("   ", w["workload"][:60], w["scaling"][:12], "%.3e"%w["value"], "%.4f ms"%w["ms_per_step"], "frac %.3f"%w["roofline_frac"], w["kernel"][:24])
+    elif "Error" in l or "error" in l: print(l[:300])
+PY
