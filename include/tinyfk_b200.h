@@ -127,6 +127,29 @@ TFK_API int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const vo
                                 int rot_type, int base_type, int with_jacobian, int precision, void *d_P,
                                 void *d_J, int64_t ld_cfg, int64_t row0);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  tfk_solve_fk_device in
+ * TFK_F64_STRICT (same arguments minus `precision`, same outputs, same bits) computed by the several-link kernel
+ * (fk_twophase_kernel, any n_link >= 1) whose scratch -- the per-configuration records and the plan's per-link tables --
+ * is a file-scope static device array of TFK_NOALLOC_STATIC_BYTES (32 MiB) instead of cudaMalloc'ed memory
+ * (tinyfk_b200/csrc/fk_noalloc.cu).  The call allocates NO device memory: no cudaMalloc, cudaFree or allocating library
+ * routine; it enqueues one small host->device copy (the tables) and one kernel on `stream`.  (The plan of a signature is
+ * built in host memory on its first call and cached.)
+ *   - Limits: n <= TFK_NOALLOC_MAX_CONFIGS (65 536) configurations per call, per-link tables <= 64 KiB, one tile's records
+ *     <= the array; beyond them the call fails with TFK_ERR_INVALID and a message that names the limit.  Requests with
+ *     large records (many links) run with fewer resident blocks, never with more memory.
+ *   - Every GPU on which the entry has been used holds the array until the process exits.  (The first launch of a kernel
+ *     instance on a device lets the driver load its code, as for any kernel; callers that must see no change in free
+ *     memory at all make one call per RotationType at set-up.)
+ *   - Every call shares the array, which keeps the previous call's contents (nothing in it has to start at zero: every
+ *     record is written before it is read, the tables are re-written per call).  Calls that overlap on the GPU -- two
+ *     streams, two host threads, two models on one device -- RACE on it: serialise them (one stream is enough). */
+enum { TFK_NOALLOC_MAX_CONFIGS = 1 << 16, TFK_NOALLOC_STATIC_BYTES = 32 << 20 };
+TFK_API int tfk_solve_fk_device_noalloc(tfk_model *m, int device, void *stream, const void *d_q, int64_t n,
+                                        const int *elink_ids, int n_link, const int *joint_ids, int n_joint,
+                                        int rot_type, int base_type, int with_jacobian, void *d_P, void *d_J,
+                                        int64_t ld_cfg, int64_t row0);
+
 /* ---- inter-link squared distances ------------------------------- */
 /* KinematicsModelPyWrapper::compute_inter_link_squared_dists (src/wrapper.cpp:189-237) + the facade glue of
  * KinematicModel.compute_inter_link_sqdists (python/tinyfk/__init__.py:233-266), batched on the GPU: for every

@@ -21,7 +21,7 @@ SYMBOLS = [
     "tfk_get_joint_ids", "tfk_get_joint_limits", "tfk_get_joint_velocity_limits",
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
-    "tfk_solve_fk_device", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
+    "tfk_solve_fk_device", "tfk_solve_fk_device_noalloc", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_plan_cache_size", "tfk_version",
 ]
 
@@ -63,6 +63,8 @@ def lib():
                                     ctypes.c_int, ctypes.c_int, _ip, ctypes.c_int, _vp, _vp]
     L.tfk_solve_fk_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, _ip, ctypes.c_int,
                                       ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
+    L.tfk_solve_fk_device_noalloc.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, ctypes.c_int, _ip, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, ctypes.c_int, _vp, _vp, _i64, _i64]
     L.tfk_inter_link_sqdists_host.argtypes = [_vp, _vp, _i64, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_int, ctypes.c_int, _vp, _vp]
     L.tfk_inter_link_sqdists_device.argtypes = [_vp, ctypes.c_int, _vp, _vp, _i64, _ip, _ip, ctypes.c_int, _ip, ctypes.c_int,
@@ -345,6 +347,15 @@ class Model:
                                            int(bool(with_jacobian)), int(precision), _vp(d_P),
                                            _vp(d_J) if d_J else None, int(ld_cfg if ld_cfg is not None else n),
                                            int(row0)))
+
+    def solve_fk_device_noalloc(self, device, stream, d_q, n, elink_ids, joint_ids, rot_type, base_type, with_jacobian,
+                                d_P, d_J, ld_cfg=None, row0=0):
+        """tfk_solve_fk_device_noalloc: strict FP64, scratch in a static device array, no device-memory allocation"""
+        l, j = _ints(elink_ids), _ints(joint_ids)
+        _check(self._L.tfk_solve_fk_device_noalloc(self._h, int(device), _vp(stream), _vp(d_q), int(n), l.ctypes.data_as(_ip),
+                                                   l.size, j.ctypes.data_as(_ip), j.size, int(rot_type), int(base_type),
+                                                   int(bool(with_jacobian)), _vp(d_P), _vp(d_J) if d_J else None,
+                                                   int(ld_cfg if ld_cfg is not None else n), int(row0)))
 
     def plan_cache_size(self):
         return int(self._L.tfk_plan_cache_size(self._h))

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "engine.hpp"
+#include "fk_noalloc.h"
 
 using namespace tfk;
 
@@ -227,6 +228,20 @@ int tfk_solve_fk_device(tfk_model *m, int device, void *stream, const void *d_q,
     SolveSpec s = make_spec(elink_ids, n_link, joint_ids, n_joint, rot_type, base_type, with_jacobian, precision);
     std::lock_guard<std::mutex> lk(m->engine.mu);
     m->engine.solve_device(device, static_cast<cudaStream_t>(stream), d_q, n, s, d_P, d_J, ld_cfg, row0);
+  });
+}
+
+// No counterpart in the reference (include/tinyfk_b200.h).
+static_assert(TFK_NOALLOC_MAX_CONFIGS == (int)tfk::TFK_NOALLOC_MAX_CONFIGS_ && TFK_NOALLOC_STATIC_BYTES == (int)tfk::TFK_NOALLOC_SCRATCH_BYTES,
+              "include/tinyfk_b200.h and csrc/fk_noalloc.h disagree on the limits of the allocation-free entry");
+int tfk_solve_fk_device_noalloc(tfk_model *m, int device, void *stream, const void *d_q, int64_t n, const int *elink_ids,
+                                int n_link, const int *joint_ids, int n_joint, int rot_type, int base_type, int with_jacobian,
+                                void *d_P, void *d_J, int64_t ld_cfg, int64_t row0) {
+  return guarded([&] {
+    need(m, "model");
+    SolveSpec s = make_spec(elink_ids, n_link, joint_ids, n_joint, rot_type, base_type, with_jacobian, PREC_F64_STRICT);
+    std::lock_guard<std::mutex> lk(m->engine.mu);
+    m->engine.solve_device_noalloc(device, static_cast<cudaStream_t>(stream), d_q, n, s, d_P, d_J, ld_cfg, row0);
   });
 }
 

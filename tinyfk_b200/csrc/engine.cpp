@@ -1,5 +1,6 @@
 // engine.cpp -- see engine.hpp.
 #include "engine.hpp"
+#include "fk_noalloc.h"
 #include "jit.hpp"
 
 #include <nvtx3/nvToolsExt.h> // header-only NVTX 3: ranges are no-ops unless a profiler is attached
@@ -651,6 +652,70 @@ void Engine::solve_device(int device, cudaStream_t stream, const void *d_q, int6
   if (spec.with_jacobian && !d_J) throw std::invalid_argument("J is null but with_jacobian is set");
   DeviceGuard g(device);
   launch(device, stream, e, spec.precision, d_q, n, d_P, d_J, ld_cfg, row0);
+}
+
+// The allocation-free device entry (tfk_solve_fk_device_noalloc; no counterpart in the reference):
+// fk_twophase_kernel with its record scratch and the plan's per-output tables in the static device
+// array of fk_noalloc.cu.  Calls no cudaMalloc / cudaFree (nor Engine::workspace / plan_on_device, which do); the plan
+// itself is host memory (built on the first call with a signature, then cached).  Strict FP64.  The grid is what the
+// array holds: a request whose records are large runs with fewer resident blocks, not with more memory.
+void Engine::solve_device_noalloc(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec_in,
+                                  void *d_P, void *d_J, int64_t ld_cfg, int64_t row0) {
+  if (n < 0) throw std::invalid_argument("negative batch size");
+  if (n > (int64_t)TFK_NOALLOC_MAX_CONFIGS_)
+    throw std::invalid_argument("tfk_solve_fk_device_noalloc: " + std::to_string(n) + " configurations exceed the maximum of " +
+                                std::to_string((int)TFK_NOALLOC_MAX_CONFIGS_) + " per call (TFK_NOALLOC_MAX_CONFIGS); split the batch "
+                                "or use tfk_solve_fk_device");
+  if (row0 < 0 || row0 + n > ld_cfg) throw std::invalid_argument("rows [row0, row0+n) exceed ld_cfg");
+  SolveSpec spec = spec_in;
+  spec.precision = PREC_F64_STRICT;
+  PlanEntry &e = plan_for(spec);
+  const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
+  if (n == 0 || h->n_out == 0) return;
+  if (!d_q && h->n_in > 0) throw std::invalid_argument("q is null");
+  if (!d_P) throw std::invalid_argument("P is null");
+  if (spec.with_jacobian && !d_J) throw std::invalid_argument("J is null but with_jacobian is set");
+  const int table_bytes = (h->off_cols - h->off_outs + 15) & ~15;
+  if (table_bytes > (int)TFK_NOALLOC_TABLE_BYTES)
+    throw std::invalid_argument("tfk_solve_fk_device_noalloc: the per-link tables of this request (" + std::to_string(table_bytes) +
+                                " bytes) exceed the " + std::to_string((int)TFK_NOALLOC_TABLE_BYTES) + " bytes reserved for them");
+  const size_t per_block = (size_t)TFK_TILE * (size_t)std::max(h->rec_size, 1) * sizeof(double);
+  const size_t room = (size_t)TFK_NOALLOC_SCRATCH_BYTES - TFK_NOALLOC_TABLE_BYTES;
+  if (per_block > room)
+    throw std::invalid_argument("tfk_solve_fk_device_noalloc: one tile of this request needs " + std::to_string(per_block) +
+                                " bytes of records, more than the static scratch holds (" + std::to_string(room) + ")");
+  const SmemLayout L = smem_layout(table_bytes, h->n_in, 0, (int)sizeof(double));
+  if (L.total > 200 * 1024) throw std::invalid_argument("plan too large for shared memory");
+  DeviceGuard g(device);
+  const auto okey = std::make_tuple(device, (int)h->rot_type, L.total);
+  auto oit = occupancy_noalloc_.find(okey);
+  if (oit == occupancy_noalloc_.end()) {
+    int bps = 0;
+    ck(occupancy_fk_noalloc(h->rot_type, L.total, &bps), "occupancy query (allocation-free kernel)");
+    if (bps < 1) throw CudaError("kernel does not fit on an SM");
+    oit = occupancy_noalloc_.insert(std::make_pair(okey, bps)).first;
+  }
+  const int64_t n_tiles = (n + TFK_TILE - 1) / TFK_TILE;
+  const int64_t resident = (int64_t)sm_count(device) * oit->second;
+  const int grid = (int)std::min<int64_t>(std::min<int64_t>(n_tiles, resident), (int64_t)(room / per_block));
+  KernelArgs a = KernelArgs();
+  a.q = d_q;
+  a.n = n;
+  a.row0 = row0;
+  a.ld_cfg = ld_cfg;
+  a.P = d_P;
+  a.J = d_J;
+  a.sub_cfg = 0; // whole tiles of TFK_TILE configurations
+  ck(launch_fk_noalloc(device, a, *e.params, e.blob.data() + h->off_outs, table_bytes, grid, L.total, stream),
+     "launch (allocation-free kernel)");
+  e.launched_on.insert(device);
+  g_launches.fetch_add(1);
+  last_launch.grid = grid;
+  last_launch.block = TFK_TILE;
+  last_launch.smem_bytes = L.total;
+  last_launch.blocks_per_sm = oit->second;
+  last_launch.rec_reals = h->rec_size;
+  last_launch.variant = KV_TWOPHASE;
 }
 
 Engine::HostPipe &Engine::pipe(int device) {

@@ -83,6 +83,10 @@ public:
   void solve_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec, void *d_P,
                     void *d_J, int64_t ld_cfg, int64_t row0);
   void solve_host(const void *q, int64_t n, const SolveSpec &spec, const int *devices, int n_devices, void *P, void *J);
+  // solve_device without any device-memory allocation (fk_noalloc.cu): the several-link kernel with its record scratch and
+  // the plan's per-output tables in a static device array; strict FP64 (spec.precision is ignored), n <= 65 536
+  void solve_device_noalloc(int device, cudaStream_t stream, const void *d_q, int64_t n, const SolveSpec &spec, void *d_P,
+                            void *d_J, int64_t ld_cfg, int64_t row0);
   void sqdists_device(int device, cudaStream_t stream, const void *d_q, int64_t n, const PairSpec &ps, void *d_sq,
                       void *d_G, int64_t ld_cfg, int64_t row0);
   void sqdists_host(const void *q, int64_t n, const PairSpec &ps, void *sq, void *G);
@@ -189,6 +193,7 @@ private:
   std::map<int, HostPipe> pipes_;
   std::map<int, int> sm_counts_;
   std::map<std::tuple<int, int, int, int>, int> occupancy_; // (device, precision, variant, smem bytes) -> blocks per SM
+  std::map<std::tuple<int, int, int>, int> occupancy_noalloc_;   // (device, rot_type, smem bytes) -> blocks per SM
 };
 
 int64_t kernel_launch_count();
