@@ -88,6 +88,9 @@ def test_state_roundtrip_and_errors():
     ("<robot name='r'><link name='a'/><link name='b'/><joint name='j' type='revolute'><parent link='a'/>"
      "<child link='b'/></joint></robot>", ValueError),                             # revolute without <limit>
     ("<robot name='r'><link name='a'><unclosed></link></robot>", ValueError),
+    ("<robot name='r'><link name='a'>" + "<x>" * 100000 + "</x>" * 100000 + "</link></robot>", ValueError),  # nesting bound
+    ("<robot name='r'><link name='a&#0;b'/></robot>", ValueError),          # NUL character reference
+    ("<robot name='r'><link name='a&#x110000;'/></robot>", ValueError),     # beyond the last Unicode scalar value
 ])
 def test_malformed_urdf_raises_instead_of_ub(xml, exc):
     with pytest.raises(exc):

@@ -59,6 +59,35 @@ def test_specialisation_compiles_without_a_gpu_and_is_cached(tmp_path):
         m.specialize(l2, list(range(m.n_joints)), 1, 1, True, 0, wait=True, compile_only=True)
 
 
+@needs_nvrtc
+def test_corrupt_or_foreign_cache_files_are_discarded_and_recompiled(tmp_path):
+    """the disk cache verifies key, length and payload hash: a truncated or foreign file is deleted and the
+    kernel recompiled instead of being handed to the driver; a cache directory others can write to is not used"""
+    d = os.environ["TFK_CACHE_DIR"]
+    m = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0)
+    j, l = list(m.get_joint_ids(W.KUKA_JOINTS)), list(m.get_link_ids(["lbr_iiwa_link_7"]))
+    a = m.specialize(l, j, 2, 0, True, 0, wait=True, compile_only=True)
+    files = [f for f in os.listdir(d) if f.endswith(".cubin")]
+    assert a["from_cache"] == 0 and len(files) == 1
+    path = os.path.join(d, files[0])
+    good = open(path, "rb").read()
+    assert good[:8] == b"TFKCUBN1" and len(good) == a["cubin_bytes"] + 40
+    assert (os.stat(d).st_mode & 0o077) == 0
+    for bad in (good[:len(good) // 2], good[:40] + bytes(len(good) - 40), b"\x7fELF" + good[4:], good[:-1] + bytes([good[-1] ^ 1])):
+        open(path, "wb").write(bad)
+        b = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0).specialize(l, j, 2, 0, True, 0, wait=True, compile_only=True)
+        assert b["from_cache"] == 0 and b["cubin_bytes"] == a["cubin_bytes"]
+        assert open(path, "rb").read() == good  # rewritten
+    b = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0).specialize(l, j, 2, 0, True, 0, wait=True, compile_only=True)
+    assert b["from_cache"] == 1
+    os.chmod(d, 0o777)  # writable by others: not trusted, neither read nor written
+    try:
+        b = capi.Model(W.urdf_text("kuka.urdf"), host_libm=0).specialize(l, j, 2, 0, True, 0, wait=True, compile_only=True)
+        assert b["from_cache"] == 0
+    finally:
+        os.chmod(d, 0o700)
+
+
 MULTI = [  # workload (BASELINE config), base override, jac, precision
     ("cfg4", None, True, 0), ("cfg4", 2, True, 0), ("cfg4", 1, False, 0), ("cfg5", None, True, 1), ("cfg5", 1, True, 1),
     ("cfg4", None, True, 1),
@@ -118,6 +147,39 @@ def test_gpu_specialised_kernel_is_the_generic_kernel_bit_for_bit(urdf, joints, 
         assert np.abs(P0 - P1).max() < 1e-5
         if jac:
             assert np.abs(J0 - J1).max() < 1e-4
+
+
+@pytest.mark.gpu
+@needs_nvrtc
+@pytest.mark.parametrize("urdf,joints,link,rot,base", [c[:5] for c in CASES[:4]])
+def test_gpu_specialised_strict_kernel_redoes_warps_that_meet_rare_inputs(urdf, joints, link, rot, base):
+    """The specialised strict kernel runs a branch-free first pass that only REPORTS rare inputs (csrc/fkmath_flag.h) and
+    redoes a reporting warp through the ordinary code.  Rows that are rare for the libm (huge angles, inf, nan, angles
+    within 2^-40 of a multiple of pi/2, denormals) are scattered over a batch -- alone in a warp, many in a warp, in the
+    ragged tail -- next to rows of exact zeros (a robot at its zero configuration is an ordinary input): every row must equal
+    the generic kernel's bit for bit (NaN where it has NaN)."""
+    m = capi.Model(W.urdf_text(urdf), host_libm=0)
+    j, l = list(m.get_joint_ids(joints)), list(m.get_link_ids([link]))
+    n = 3000 + 17
+    q = W.sample_q(m.get_joint_limits(j), base, n, seed=11, wide_pitch=True)
+    rng = np.random.default_rng(12)
+    rare = [1e7, -3.3e9, np.inf, -np.inf, np.nan, np.pi / 2, -np.pi, 3 * np.pi / 2 * (1 + 2.0 ** -45), 1e-310, 5e-324, 2.0 ** 40, 1647099.5]
+    rows = np.concatenate([rng.choice(n, 60, replace=False), np.arange(1024, 1040), [n - 1, n - 2, 0]])
+    for r in rows:
+        q[r, rng.integers(0, q.shape[1])] = rare[rng.integers(0, len(rare))]
+    q[200:232] = 0.0      # a whole warp at the zero configuration
+    q[500] = 0.0
+    q[777, :len(j)] = 0.0  # zero joints, random base
+    m.set_jit_mode(0)
+    P0, J0 = m.solve_fk(q, l, j, rot, base, True)
+    assert "spec" not in m.last_launch_info()["kernel"]
+    m.set_jit_mode(1)
+    assert m.specialize(l, j, rot, base, True, 0, wait=True)["state"] == 3
+    P1, J1 = m.solve_fk(q, l, j, rot, base, True)
+    assert m.last_launch_info()["kernel"].startswith("tfk_spec_kernel")
+    assert np.array_equal(P0, P1, equal_nan=True) and np.array_equal(J0, J1, equal_nan=True)
+    clean = np.setdiff1d(np.arange(n), rows)
+    assert np.isfinite(P1[clean]).all()
 
 
 @pytest.mark.gpu

@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdio>
 #include <cstring>
 #include <exception>
 
@@ -153,6 +154,18 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
   // thread reads its own input row from global memory at constant offsets).
   // 256-thread blocks, two per SM: the blocks of an SM then walk the long straight-line code close together, which the
   // instruction cache rewards (measured on cfg2: 2 x 256 threads 0.245 ms, 4 x 128 0.258, 3 x 192 0.266, 1 x 512 0.256)
+  if (const char *t = std::getenv("TFK_SPEC_SHAPE")) { // A/B knob for measurements: "threads,blocks" (e.g. "128,5")
+    int tt = 0, bb = 0;
+    if (std::sscanf(t, "%d,%d", &tt, &bb) == 2 && tt >= 32 && tt <= 512 && tt % 32 == 0 && bb >= 1) {
+      const int sm = fused_smem_bytes(tt, h->fz_size, rb);
+      if (bb * (sm + 1024) <= limit || std::getenv("TFK_SPEC_SHAPE_FORCE")) { // (FORCE: compile-only register studies)
+        *tile = tt;
+        *bps = bb;
+        *smem = sm;
+        return true;
+      }
+    }
+  }
   {
     const int sm = fused_smem_bytes(256, h->fz_size, rb);
     int b = precision == PREC_F32 ? 3 : 2;

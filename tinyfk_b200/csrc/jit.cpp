@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <mutex>
 #include <stdexcept>
@@ -92,8 +93,24 @@ std::string cache_dir() {
 
 void mkdirs(const std::string &p) {
   for (size_t i = 1; i <= p.size(); ++i)
-    if (i == p.size() || p[i] == '/') mkdir(p.substr(0, i).c_str(), 0755);
+    if (i == p.size() || p[i] == '/') mkdir(p.substr(0, i).c_str(), 0700);
 }
+
+// only a directory that belongs to this user and that nobody else can write to is trusted as a cubin cache
+bool cache_dir_trusted(const std::string &dir) {
+  struct stat st;
+  if (stat(dir.c_str(), &st) != 0) return false;
+  return S_ISDIR(st.st_mode) && st.st_uid == geteuid() && (st.st_mode & (S_IWGRP | S_IWOTH)) == 0;
+}
+
+// Cache file = header + cubin.  The header carries two independent 64-bit hashes of everything that determines the
+// cubin (source, options, embedded headers, NVRTC version), the payload length and a hash of the payload: a truncated,
+// foreign or colliding file is detected, deleted and recompiled instead of being handed to cudaLibraryLoadData.
+struct CacheHeader {
+  char magic[8]; // "TFKCUBN1"
+  uint64_t key_a, key_b, payload_bytes, payload_hash;
+};
+const char k_cache_magic[8] = {'T', 'F', 'K', 'C', 'U', 'B', 'N', '1'};
 
 std::vector<std::string> compile_options(const SpecOptions &o) {
   std::vector<std::string> v;
@@ -131,7 +148,7 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
       i = j + 1;
     }
   } else {
-    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
+    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n#define TFK_SPEC_FLAG 1\n";
   }
   if (o.kind != 0 && o.precision == PREC_F64_STRICT) s += "#define TFK_SPEC_ROLLED_WALK 1\n"; // several links, FP64: fk_core.h TFK_WALK_LOOP
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
@@ -143,8 +160,16 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   const std::string core = std::string("tfk::FkCore<") +
                            (f32 ? "tfk::MathNative32, true, " : (o.precision == PREC_F64_FAST ? "tfk::MathFast64, true, " : "tfk::MathPortable, false, ")) +
                            std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
-  if (o.kind == 0)
-    s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
+  // strict FP64, one link: first pass through the branch-free arithmetic that flags rare inputs (fkmath_flag.h), a
+  // flagged warp is redone through `core` (TFK_SPEC_FLAG; off: one pass through `core`)
+  const std::string core_flag = std::string("tfk::FkCore<tfk::MathPortableFlag, false, ") + std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
+  if (o.kind == 0 && o.precision == PREC_F64_STRICT) {
+    // (TFK_SPEC_FLAG_ONLY: analysis build without the second pass -- NOT a product configuration)
+    s += "#if defined(TFK_SPEC_FLAG_ONLY)\n  tfk::fk_fused_spec_body<" + core_flag + ", " + core_flag + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n";
+    s += "#elif defined(TFK_SPEC_FLAG)\n  tfk::fk_fused_spec_body<" + core + ", " + core_flag + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n";
+    s += "#else\n  tfk::fk_fused_spec_body<" + core + ", " + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n#endif\n}\n";
+  } else if (o.kind == 0)
+    s += "  tfk::fk_fused_spec_body<" + core + ", " + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
   else
     s += "  tfk::fk_twophase_spec_body<" + core + ", " + (o.kind == 2 ? "true" : "false") + ">(a);\n}\n";
   return s;
@@ -156,22 +181,37 @@ std::vector<char> spec_compile(const std::string &plan_source, const SpecOptions
   if (!n.so) throw std::runtime_error(n.error);
   const std::string src = spec_source(plan_source, o);
   const std::vector<std::string> opts = compile_options(o);
-  // cache key: everything that determines the cubin
-  uint64_t key = fnv1a(src);
-  for (const std::string &x : opts) key = fnv1a(x, key);
-  for (int i = 0; i < k_jit_n_headers; ++i) key = fnv1a(k_jit_header_sources[i], key);
-  key = fnv1a("nvrtc " + std::to_string(n.major) + "." + std::to_string(n.minor), key);
+  // cache key: everything that determines the cubin (two FNV-1a streams with different offsets: 128 bits)
+  uint64_t key = fnv1a(src), key_b = fnv1a(src, 0x9e3779b97f4a7c15ull);
+  for (const std::string &x : opts) key = fnv1a(x, key), key_b = fnv1a(x, key_b);
+  for (int i = 0; i < k_jit_n_headers; ++i) key = fnv1a(k_jit_header_sources[i], key), key_b = fnv1a(k_jit_header_sources[i], key_b);
+  const std::string ver = "nvrtc " + std::to_string(n.major) + "." + std::to_string(n.minor) + " sm_100a";
+  key = fnv1a(ver, key), key_b = fnv1a(ver, key_b);
   char name[64];
   std::snprintf(name, sizeof name, "/spec_%016llx.cubin", (unsigned long long)key);
-  const std::string dir = cache_dir();
+  std::string dir = cache_dir();
+  if (!dir.empty()) {
+    mkdirs(dir);
+    if (!cache_dir_trusted(dir)) dir.clear(); // someone else's (or a writable-by-others) directory: no disk cache
+  }
   if (!dir.empty()) {
     std::ifstream f(dir + name, std::ios::binary);
     if (f) {
-      std::vector<char> cubin((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
-      if (cubin.size() > 64) {
-        if (from_cache) *from_cache = true;
-        return cubin;
+      std::vector<char> file((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+      f.close();
+      CacheHeader hd;
+      bool ok = file.size() > sizeof hd + 64;
+      if (ok) {
+        std::memcpy(&hd, file.data(), sizeof hd);
+        ok = std::memcmp(hd.magic, k_cache_magic, 8) == 0 && hd.key_a == key && hd.key_b == key_b &&
+             hd.payload_bytes == file.size() - sizeof hd &&
+             hd.payload_hash == fnv1a(std::string(file.data() + sizeof hd, file.size() - sizeof hd));
       }
+      if (ok) {
+        if (from_cache) *from_cache = true;
+        return std::vector<char>(file.begin() + sizeof hd, file.end());
+      }
+      std::remove((dir + name).c_str()); // corrupt, truncated, foreign or from an older layout: recompile
     }
   }
   nvrtcProgram prog = nullptr;
@@ -195,10 +235,16 @@ std::vector<char> spec_compile(const std::string &plan_source, const SpecOptions
   n.DestroyProgram(&prog);
   if (rc != 0 || cs == 0) throw std::runtime_error("NVRTC produced no cubin");
   if (!dir.empty()) { // best effort; written through a temporary so that concurrent processes never see a partial file
-    mkdirs(dir);
     const std::string tmp = dir + name + "." + std::to_string((long)getpid()) + ".tmp";
     std::ofstream f(tmp, std::ios::binary);
     if (f) {
+      CacheHeader hd;
+      std::memcpy(hd.magic, k_cache_magic, 8);
+      hd.key_a = key;
+      hd.key_b = key_b;
+      hd.payload_bytes = cubin.size();
+      hd.payload_hash = fnv1a(std::string(cubin.data(), cubin.size()));
+      f.write(reinterpret_cast<const char *>(&hd), sizeof hd);
       f.write(cubin.data(), (std::streamsize)cubin.size());
       f.close();
       if (!f || std::rename(tmp.c_str(), (dir + name).c_str()) != 0) std::remove(tmp.c_str());

@@ -150,6 +150,7 @@ private:
           unsigned long cp = (ent.size() > 1 && (ent[1] == 'x' || ent[1] == 'X'))
                                  ? std::strtoul(ent.c_str() + 2, nullptr, 16)
                                  : std::strtoul(ent.c_str() + 1, nullptr, 10);
+          if (cp == 0 || cp > 0x10FFFF) fail("character reference &" + ent + "; is not a Unicode scalar value");
           append_utf8(out, cp);
         } else {
           out += s_.substr(i_, semi - i_ + 1); // unknown entity: keep literally
@@ -165,8 +166,19 @@ private:
     return out;
   }
 
+  // URDF nests four or five levels deep; a bound keeps a crafted document from overflowing the stack (one frame per level)
+  enum { MAX_DEPTH = 256 };
+  int depth_ = 0;
+  struct DepthGuard {
+    int &d;
+    explicit DepthGuard(int &x) : d(x) { ++d; }
+    ~DepthGuard() { --d; }
+  };
+
   std::unique_ptr<Element> element() {
     // precondition: peek() == '<' and this is a start tag
+    DepthGuard guard(depth_);
+    if (depth_ > MAX_DEPTH) fail("elements nested more than 256 levels deep");
     ++i_;
     std::unique_ptr<Element> e(new Element);
     e->tag = name();
