@@ -242,15 +242,6 @@ TFK_API int tfk_last_launch_variant(const tfk_model *m);
 /* call signatures the engine currently holds a plan for (bounded at 64, least recently used evicted; a signature whose
  * plan constants change with the stored model state is replaced in place).  Diagnostics / tests. */
 TFK_API int tfk_plan_cache_size(const tfk_model *m);
-/* Test hook, no reference equivalent.  The plan-specialised strict FP64 kernels first run a branch-free restatement of
- * the strict arithmetic that REPORTS rare inputs instead of branching on them (tinyfk_b200/csrc/fkmath_flag.h) and redo
- * a warp that reported one through the ordinary code.  This entry evaluates that restatement element by element on the
- * current GPU next to the function it must equal, on HOST arrays of n doubles:
- *   op 0  1/x          vs __drcp_rn(x)             op 3  sin, cos of x   vs tfk_sincos_simt   (out/ref hold 2n: sin | cos)
- *   op 1  x / y        vs the compiler's x / y     op 4  asin(x)         vs tfk_asin_simt
- *   op 2  sqrt(x)      vs the compiler's sqrt(x)   op 5  atan2(x, y)     vs tfk_atan2_simt
- * flags[i] = 1 where the restatement reported a rare input (its out[i] is then unspecified).  y is read by ops 1, 5. */
-TFK_API int tfk_debug_flag_math(int op, int64_t n, const double *x, const double *y, double *out, double *ref, int *flags);
 TFK_API const char *tfk_version(void);
 
 #ifdef __cplusplus

@@ -18,9 +18,6 @@
 using namespace tfk;
 
 static thread_local std::string g_err;
-// mode 4 (MathPortableFlag, csrc/fkmath_flag.h): per configuration, the line of fk_math.h whose call raised the
-// rare-input flag last (0: not raised) -- read back with emu_flags()
-static thread_local std::vector<int> g_flags;
 
 template <class T> struct DirectFactory { // the fused driver builds its sink after the walk
   typedef DirectSink<T> Sink;
@@ -43,10 +40,7 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
   out.ldP = ldP;
   out.ldJ = ldJ;
   out.D = h.pose_dim;
-  g_flags.assign((size_t)n, 0);
   for (long i = 0; i < n; ++i) {
-    tfk_rare_host_flag = 0;
-    tfk_rare_host_line = 0;
     for (int c = 0; c < h.n_in; ++c) qrow[c] = (T)qs[(size_t)i * h.n_in + c];
     if (fused) {
       out.head = i;
@@ -62,7 +56,6 @@ static void run(const std::vector<unsigned char> &blob, const double *qs, long n
         }
       }
     }
-    g_flags[(size_t)i] = tfk_rare_host_flag ? tfk_rare_host_line : 0;
   }
   for (size_t k = 0; k < P.size(); ++k) Pd[k] = (double)P[k];
   if (Jd)
@@ -246,12 +239,6 @@ void emu_div(const double *a, const double *b, double *o, long n) {
   for (long i = 0; i < n; ++i) o[i] = MathPortable::div_(a[i], MathPortable::den_(b[i]));
 }
 const char *emu_last_error() { return g_err.c_str(); }
-// flags of the last emu_solve on this thread (mode 4): out[i] = raising line of fk_math.h for configuration i, or 0
-long emu_flags(int *out, long n) {
-  const long m = (long)g_flags.size() < n ? (long)g_flags.size() : n;
-  for (long i = 0; i < m; ++i) out[i] = g_flags[(size_t)i];
-  return m;
-}
 
 void *emu_create(const char *xml, int system_libm) {
   try {
@@ -293,8 +280,7 @@ void emu_link_info(void *m, int id, int *parent, int *jtype, int *jid, double *a
 int emu_is_relevant(void *m, int l, int j) { return static_cast<KinematicModel *>(m)->is_relevant(l, j) ? 1 : 0; }
 
 // mode 0: FP64 strict (portable libm, FD base columns); 1: FP32 (native libm, analytic base columns);
-// 2: FP64 with the platform libm (FD base columns); 3: FP64 fast; 4: FP64 strict through the branch-free arithmetic that
-// reports rare inputs (MathPortableFlag; emu_flags() tells which configurations did); +16: force the two-phase driver
+// 2: FP64 with the platform libm (FD base columns); +16: force the two-phase driver for a single link
 int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, const int *joints, int n_joint,
               int rot_type, int base_type, int with_jacobian, int mode, double *P, double *J) {
   try {
@@ -316,8 +302,6 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     run<FkCore<MathNative32, true, R, 1>, float>(blob, qs, n, P, Jp, two_phase);               \
   else if (mode == 3)                                                                       \
     run<FkCore<MathFast64, true, R, 1>, double>(blob, qs, n, P, Jp, two_phase);                \
-  else if (mode == 4)                                                                       \
-    run<FkCore<MathPortableFlag, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);         \
   else                                                                                      \
     run<FkCore<MathNative64, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);
     if (rot_type == 0) {

@@ -12,7 +12,7 @@ _dp = ctypes.POINTER(ctypes.c_double)
 _ip = ctypes.POINTER(ctypes.c_int)
 _lib = None
 
-MODE_STRICT64, MODE_F32, MODE_NATIVE64, MODE_FAST64, MODE_STRICT64_FLAG = 0, 1, 2, 3, 4
+MODE_STRICT64, MODE_F32, MODE_NATIVE64, MODE_FAST64 = 0, 1, 2, 3
 
 
 def _srcs():
@@ -133,14 +133,6 @@ class EmuModel:
         if rc:
             raise ValueError(self._L.emu_last_error().decode())
         return P, J
-
-    def last_flags(self, n):
-        """after solve_fk(..., mode=MODE_STRICT64_FLAG): per configuration, the line of csrc/fk_math.h whose call reported
-        a rare input last (0: none did -- the result is then the strict result bit for bit)"""
-        out = np.zeros(n, dtype=np.int32)
-        self._L.emu_flags.restype = ctypes.c_long
-        self._L.emu_flags(out.ctypes.data_as(_ip), ctypes.c_long(n))
-        return out
 
     def inter_link_sqdists(self, qs, link_id_pairs, joint_ids, base_type=0, with_jacobian=False, mode=MODE_STRICT64):
         qs = np.ascontiguousarray(np.atleast_2d(np.asarray(qs, dtype=np.float64)))

@@ -152,12 +152,11 @@ def test_gpu_specialised_kernel_is_the_generic_kernel_bit_for_bit(urdf, joints, 
 @pytest.mark.gpu
 @needs_nvrtc
 @pytest.mark.parametrize("urdf,joints,link,rot,base", [c[:5] for c in CASES[:4]])
-def test_gpu_specialised_strict_kernel_redoes_warps_that_meet_rare_inputs(urdf, joints, link, rot, base):
-    """The specialised strict kernel runs a branch-free first pass that only REPORTS rare inputs (csrc/fkmath_flag.h) and
-    redoes a reporting warp through the ordinary code.  Rows that are rare for the libm (huge angles, inf, nan, angles
-    within 2^-40 of a multiple of pi/2, denormals) are scattered over a batch -- alone in a warp, many in a warp, in the
-    ragged tail -- next to rows of exact zeros (a robot at its zero configuration is an ordinary input): every row must equal
-    the generic kernel's bit for bit (NaN where it has NaN)."""
+def test_gpu_specialised_strict_kernel_on_rare_inputs(urdf, joints, link, rot, base):
+    """Rows that are rare for the portable libm and the shared-reciprocal divisions (huge angles, inf, nan, angles within
+    2^-40 of a multiple of pi/2, denormals) scattered over a batch -- alone in a warp, many in a warp, in the ragged tail --
+    next to rows of exact zeros (a robot at its zero configuration): the specialised kernel's out-of-line rare paths must
+    give the generic kernel's result bit for bit (NaN where it has NaN)."""
     m = capi.Model(W.urdf_text(urdf), host_libm=0)
     j, l = list(m.get_joint_ids(joints)), list(m.get_link_ids([link]))
     n = 3000 + 17

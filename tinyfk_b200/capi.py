@@ -23,7 +23,6 @@ SYMBOLS = [
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
     "tfk_solve_fk_device", "tfk_solve_fk_device_noalloc", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
     "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_plan_cache_size", "tfk_version",
-    "tfk_debug_flag_math",
 ]
 
 _lib = None
@@ -370,23 +369,6 @@ class Model:
         d["kernel"] = {0: "fk_fused_kernel<smem records>", 1: "fk_fused_kernel<global records>",
                        2: "fk_twophase_kernel", 3: "fk_fused_kernel<smem records, 5 blocks/SM>", 4: "fk_sqdist_kernel", 5: "fk_com_kernel", 6: "fk_inertia_kernel", 9: "fk_sqdist_kernel<joint records in shared memory>", 8: "fk_twophase_kernel<joint records in shared memory>", 7: "tfk_spec_kernel (plan-specialised fk_fused_kernel, NVRTC)", 12: "tfk_spec_kernel (plan-specialised fk_twophase_kernel, NVRTC)"}.get(k, "none")
         return d
-
-
-def debug_flag_math(op, x, y=None):
-    """test hook (include/tinyfk_b200.h:tfk_debug_flag_math): returns (out, ref, flags) for the branch-free strict
-    arithmetic of csrc/fkmath_flag.h evaluated on the current GPU"""
-    x = np.ascontiguousarray(x, dtype=np.float64)
-    n = x.shape[0]
-    if y is not None:
-        y = np.ascontiguousarray(y, dtype=np.float64)
-        assert y.shape == x.shape
-    m = 2 * n if op == 3 else n
-    out, ref, flags = np.empty(m), np.empty(m), np.empty(n, dtype=np.int32)
-    L = lib()
-    L.tfk_debug_flag_math.argtypes = [ctypes.c_int, _i64, _vp, _vp, _vp, _vp, _vp]
-    _check(L.tfk_debug_flag_math(op, n, x.ctypes.data, y.ctypes.data if y is not None else None, out.ctypes.data,
-                                 ref.ctypes.data, flags.ctypes.data))
-    return out, ref, flags
 
 
 def kernel_launch_count():

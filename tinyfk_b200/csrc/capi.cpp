@@ -7,7 +7,6 @@
 #include <vector>
 
 #include "engine.hpp"
-#include "fk_debug_math.h"
 #include "fk_noalloc.h"
 
 using namespace tfk;
@@ -387,20 +386,6 @@ int tfk_last_launch_info(const tfk_model *m, int *grid, int *block, int *smem_by
 }
 
 int tfk_last_launch_variant(const tfk_model *m) { return m ? m->engine.last_launch.variant : -1; }
-
-int tfk_debug_flag_math(int op, int64_t n, const double *x, const double *y, double *out, double *ref, int *flags) {
-  return guarded([&] {
-    if (op < 0 || op > 5 || n < 0) throw std::invalid_argument("tfk_debug_flag_math: bad op or n");
-    need(x, "x");
-    need(out, "out");
-    need(ref, "ref");
-    need(flags, "flags");
-    if ((op == 1 || op == 5) && !y) throw std::invalid_argument("tfk_debug_flag_math: op needs y");
-    if (n == 0) return;
-    const cudaError_t e = debug_flag_math(op, (long long)n, x, (op == 1 || op == 5) ? y : nullptr, out, ref, flags);
-    if (e != cudaSuccess) throw CudaError(std::string("tfk_debug_flag_math: ") + cudaGetErrorString(e));
-  });
-}
 
 int tfk_plan_cache_size(const tfk_model *m) { return m ? (int)m->engine.plan_cache_size() : -1; }
 

@@ -111,6 +111,16 @@ Engine::SpecKernel::~SpecKernel() {
   if (lib) cudaLibraryUnload(lib);
 }
 
+// configurations per tile of the two-phase kernels: the rule of fk_launch.h, or TFK_TWOPHASE_TILE_CFGS (32 | 64 | 128:
+// A/B knob for measurements -- smaller tiles touch less of the block-private record scratch)
+static int tile_cfgs_for(long long n, long long resident_blocks) {
+  if (const char *t = std::getenv("TFK_TWOPHASE_TILE_CFGS")) {
+    const int v = std::atoi(t);
+    if (v == 32 || v == 64 || v == (int)TFK_TILE) return v;
+  }
+  return twophase_tile_cfgs(n, resident_blocks);
+}
+
 // ---- plan specialisation (jit.hpp) -------------------------------------------------------------------------------
 bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *kind, std::string *why) const {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
@@ -321,7 +331,7 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
     it = sk.blocks_per_sm.insert(std::make_pair(device, b)).first;
   }
   // two-phase: configurations per tile (fk_launch.h:twophase_tile_cfgs; the two-phase builds use TFK_TILE threads)
-  const int tile_cfgs = sk.kind != 0 ? twophase_tile_cfgs(a.n, (int64_t)sm_count(device) * it->second) : sk.tile;
+  const int tile_cfgs = sk.kind != 0 ? tile_cfgs_for(a.n, (int64_t)sm_count(device) * it->second) : sk.tile;
   const int64_t n_tiles = (a.n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
   KernelArgs args = a;
@@ -614,7 +624,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   }
   const bool twophase = variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM;
   const int64_t resident = (int64_t)sm_count(device) * bps;
-  const int tile_cfgs = twophase ? twophase_tile_cfgs(n, resident) : (int)TFK_TILE;
+  const int tile_cfgs = twophase ? tile_cfgs_for(n, resident) : (int)TFK_TILE;
   const int64_t n_tiles = (n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, resident);
   KernelArgs a;

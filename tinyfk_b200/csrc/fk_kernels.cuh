@@ -227,16 +227,9 @@ __global__ void __launch_bounds__(TFK_TILE, BPS) fk_fused_kernel(const KernelArg
 // plan.cpp:plan_to_source and compiled at run time, jit.cpp), the plan loops are fully unrolled and every test on a
 // plan field is folded, so what is left is the straight-line arithmetic of THIS robot/query.  Same source, same
 // compiler flags, same bits as the generic kernel.
-// CoreFast: the same arithmetic as one basic block that reports rare inputs through the warp's flag instead of branching
-// (FkCore over MathPortableFlag, fkmath_flag.h) -- run first; a warp whose flag is up runs its configurations again
-// through Core, which overwrites what the first pass wrote.  CoreFast == Core: one pass.
-template <class A, class B> struct IsSame { enum { value = 0 }; };
-template <class A> struct IsSame<A, A> { enum { value = 1 }; };
-
-template <class Core, class CoreFast, bool SMEM_REC, int BPS>
+template <class Core, bool SMEM_REC, int BPS>
 __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
   typedef typename Core::T T;
-  enum { REDO = !IsSame<Core, CoreFast>::value };
   extern __shared__ __align__(16) unsigned char smem[];
   PlanView pv;
   pv.h = &spec::k_h;
@@ -253,10 +246,6 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
   rec += threadIdx.x;
   const T *q = static_cast<const T *>(a.q);
   const int warp = threadIdx.x >> 5;
-  if (REDO) {
-    tfk_rare_flag[warp] = 0;
-    __syncwarp();
-  }
 
   StagedFactory<T, Core::D> fac;
   fac.P = static_cast<T *>(a.P);
@@ -275,20 +264,7 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
       const int row = (int)threadIdx.x < nv ? (int)threadIdx.x : nv - 1;
       fac.nvalid = nvalid;
       fac.head0 = a.row0 + i0 + warp * 32;
-      CoreFast::run_fused(pv, q + (i0 + row) * h.n_in, rec, TFK_TILE, fac);
-      if (REDO) {
-        __syncwarp();
-        const int raised = tfk_rare_flag[warp];
-        __syncwarp();
-        if (TFK_UNLIKELY(raised != 0)) { // a lane met a rare input: the warp's 32 configurations once more, the ordinary way
-          tfk_rare_flag[warp] = 0;
-          __syncwarp();
-          Core::run_fused(pv, q + (i0 + row) * h.n_in, rec, TFK_TILE, fac);
-#if defined(TFK_SPEC_FLAG_MARK) // debugging aid, never a product build: the first P entry of a redone warp = the line that reported
-          if ((threadIdx.x & 31) == 0) static_cast<T *>(a.P)[fac.head0] = (T)raised;
-#endif
-        }
-      }
+      Core::run_fused(pv, q + (i0 + row) * h.n_in, rec, TFK_TILE, fac);
     }
     __syncthreads(); // keeps the block's warps together in the straight-line code (instruction cache)
   }

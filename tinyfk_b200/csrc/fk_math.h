@@ -17,7 +17,6 @@
 
 #include "fkmath.h"
 #include "fkmath_simt.h"
-#include "fkmath_flag.h"
 
 #if defined(__CUDACC__)
 #define TFK_FN __host__ __device__ __forceinline__
@@ -57,10 +56,6 @@ template <class T> struct PoseT {
 // Portable libm: identical bits on host and device (fkmath.h).  FP64 only.
 struct MathPortable {
   typedef double real;
-  // BRANCHLESS: the policy's functions never branch on their data (MathPortableFlag below); rare_(c): "c is a rare
-  // condition" -- returned as is here, reported through the warp's flag and answered `false` there
-  enum { BRANCHLESS = 0 };
-  static TFK_FN bool rare_(bool c) { return c; }
   static TFK_FN double sin_(double x) { return tfk_sin(x); }
   static TFK_FN double cos_(double x) { return tfk_cos(x); }
   // fkmath_simt.h: bit-identical to fkmath.h's functions, restructured for warps
@@ -174,78 +169,9 @@ struct MathPortable {
   }
 };
 
-// MathPortable as one basic block (fkmath_flag.h): the same bits for every input that does not raise the warp's rare-input
-// flag; the plan-specialised strict kernels run it first and redo a warp whose flag is up with MathPortable
-// (fk_kernels.cuh:fk_fused_spec_body).  On the host (tests/emu) the same code runs with emulated MUFU seeds.
-struct MathPortableFlag {
-  typedef double real;
-  enum { BRANCHLESS = 1 };
-  static TFK_FN bool rare_(bool c) {
-    tfk_rare_raise(c);
-    return false;
-  }
-  static TFK_FN void sincos_(double x, double *s, double *c) {
-    int bad = 0;
-    const TfkSinCos r = tfk_sincos_flag(x, bad);
-    tfk_rare_raise(bad);
-    *s = r.s;
-    *c = r.c;
-  }
-  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
-    int bad = 0;
-    const TfkSinCos a = tfk_sincos_flag(xa, bad), b = tfk_sincos_flag(xb, bad);
-    tfk_rare_raise(bad);
-    *sa = a.s, *ca = a.c, *sb = b.s, *cb = b.c;
-  }
-  static TFK_FN double asin_(double x) {
-    int bad = 0;
-    const double r = tfk_asin_flag(x, bad);
-    tfk_rare_raise(bad);
-    return r;
-  }
-  static TFK_FN double atan2_(double y, double x) {
-    int bad = 0;
-    const double r = tfk_atan2_flag(y, x, bad);
-    tfk_rare_raise(bad);
-    return r;
-  }
-  static TFK_FN double atan2_rare_(double y, double x) { return atan2_(y, x); }
-  static TFK_FN double sqrt_(double x) {
-    int bad = 0;
-    const double r = tfk_sqrt_flag(x, bad);
-    tfk_rare_raise(bad);
-    return r;
-  }
-  struct Den {
-    double b, y;
-    int bad;
-  };
-  static TFK_FN Den den_(double b) {
-    Den d;
-    d.b = b;
-    d.bad = 0;
-    d.y = tfk_rcp_flag(b, d.bad);
-    return d;
-  }
-  static TFK_FN double div_(double a, const Den &d) {
-    int bad = d.bad;
-    const double q = tfk_div_y_flag(a, d.b, d.y, bad);
-    tfk_rare_raise(bad);
-    return q;
-  }
-  template <int N> static TFK_FN void divn_(double (&a)[N], const Den &d) {
-    int bad = d.bad;
-    TFK_MATH_UNROLL
-    for (int i = 0; i < N; ++i) a[i] = tfk_div_y_flag(a[i], d.b, d.y, bad);
-    tfk_rare_raise(bad);
-  }
-};
-
 // The platform's own libm (glibc on the host, libdevice on the GPU).
 struct MathNative64 {
   typedef double real;
-  enum { BRANCHLESS = 0 };
-  static TFK_FN bool rare_(bool c) { return c; }
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
   static TFK_FN void sincos_(double x, double *s, double *c) {
@@ -280,8 +206,6 @@ struct MathNative64 {
 
 struct MathNative32 {
   typedef float real;
-  enum { BRANCHLESS = 0 };
-  static TFK_FN bool rare_(bool c) { return c; }
   static TFK_FN float sin_(float x) { return ::sinf(x); }
   static TFK_FN float cos_(float x) { return ::cosf(x); }
   static TFK_FN void sincos_(float x, float *s, float *c) {
@@ -333,8 +257,6 @@ struct MathNative32 {
 // contract is 1e-12 on poses and analytic Jacobian entries.
 struct MathFast64 {
   typedef double real;
-  enum { BRANCHLESS = 0 };
-  static TFK_FN bool rare_(bool c) { return c; }
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
   static TFK_FN void sincos_(double x, double *s, double *c) {
@@ -400,7 +322,7 @@ template <class M> struct Ops {
   static TFK_FN Q qget_inverse(const Q &q) {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
     Q r = qidentity();
-    if (TFK_LIKELY(!M::rare_(!(norm > T(0))))) {
+    if (TFK_LIKELY(norm > T(0))) {
       T a[4] = {q.w, -q.x, -q.y, -q.z};
       M::divn_(a, M::den_(norm));
       r.w = a[0];
@@ -547,7 +469,7 @@ template <class M> struct Ops {
   // Rotation::normalize, pose.h:230-250
   static TFK_FN void qnormalize(Q &q) {
     T s = M::sqrt_(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-    if (TFK_UNLIKELY(M::rare_(s == T(0)))) {
+    if (TFK_UNLIKELY(s == T(0))) {
       q = qidentity();
     } else {
       T a[4] = {q.x, q.y, q.z, q.w};
@@ -581,20 +503,6 @@ template <class M> struct Ops {
     T sarg = T(-2) * (q.x * q.z - q.w * q.y);
     const T pi_2 = T(1.57079632679489661923);
     V r;
-    if (M::BRANCHLESS) {
-      // the same three cases with selects: the gimbal rows are ordinary inputs (a few per thousand), not rare ones.
-      // Gimbal: roll = 0, pitch = -+pi/2, yaw = 2 * atan2(+-x, -+y); the unused asin / atan2 get harmless arguments.
-      const bool gm = sarg <= T(-0.99999), gp = sarg >= T(0.99999), g = gm | gp;
-      const T yy = g ? (gm ? q.x : -q.x) : T(2) * (q.x * q.y + q.w * q.z);
-      const T yx = g ? (gm ? -q.y : q.y) : sqw + sqx - sqy - sqz;
-      const T yaw = M::atan2_(yy, yx);
-      const T roll = M::atan2_(g ? T(0) : T(2) * (q.y * q.z + q.w * q.x), g ? T(1) : sqw - sqx - sqy + sqz);
-      const T pitch = M::asin_(g ? T(0) : sarg);
-      r.x = g ? T(0) : roll;
-      r.y = g ? (gm ? -pi_2 : pi_2) : pitch;
-      r.z = g ? T(2) * yaw : yaw;
-      return r;
-    }
     if (TFK_UNLIKELY(sarg <= T(-0.99999))) {
       r.y = -pi_2;
       r.x = T(0);
@@ -689,7 +597,7 @@ template <class M> struct Ops {
     q.z = s;
     q.w = c;
     const T n = M::sqrt_(s * s + c * c); // x*x + y*y + z*z + w*w with x = y = 0
-    if (TFK_UNLIKELY(M::rare_(n == T(0)))) {
+    if (TFK_UNLIKELY(n == T(0))) {
       q.z = T(0);
       q.w = T(1);
     } else {
@@ -708,7 +616,7 @@ template <class M> struct Ops {
     QZ r;
     r.z = T(0);
     r.w = T(1);
-    if (TFK_LIKELY(!M::rare_(!(norm > T(0))))) {
+    if (TFK_LIKELY(norm > T(0))) {
       T a[2] = {q.w, -q.z};
       M::divn_(a, M::den_(norm));
       r.w = a[0];

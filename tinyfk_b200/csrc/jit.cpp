@@ -148,7 +148,7 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
       i = j + 1;
     }
   } else {
-    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n#define TFK_SPEC_FLAG 1\n";
+    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
   }
   if (o.kind != 0 && o.precision == PREC_F64_STRICT) s += "#define TFK_SPEC_ROLLED_WALK 1\n"; // several links, FP64: fk_core.h TFK_WALK_LOOP
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
@@ -160,16 +160,8 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   const std::string core = std::string("tfk::FkCore<") +
                            (f32 ? "tfk::MathNative32, true, " : (o.precision == PREC_F64_FAST ? "tfk::MathFast64, true, " : "tfk::MathPortable, false, ")) +
                            std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
-  // strict FP64, one link: first pass through the branch-free arithmetic that flags rare inputs (fkmath_flag.h), a
-  // flagged warp is redone through `core` (TFK_SPEC_FLAG; off: one pass through `core`)
-  const std::string core_flag = std::string("tfk::FkCore<tfk::MathPortableFlag, false, ") + std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
-  if (o.kind == 0 && o.precision == PREC_F64_STRICT) {
-    // (TFK_SPEC_FLAG_ONLY: analysis build without the second pass -- NOT a product configuration)
-    s += "#if defined(TFK_SPEC_FLAG_ONLY)\n  tfk::fk_fused_spec_body<" + core_flag + ", " + core_flag + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n";
-    s += "#elif defined(TFK_SPEC_FLAG)\n  tfk::fk_fused_spec_body<" + core + ", " + core_flag + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n";
-    s += "#else\n  tfk::fk_fused_spec_body<" + core + ", " + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n#endif\n}\n";
-  } else if (o.kind == 0)
-    s += "  tfk::fk_fused_spec_body<" + core + ", " + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
+  if (o.kind == 0)
+    s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
   else
     s += "  tfk::fk_twophase_spec_body<" + core + ", " + (o.kind == 2 ? "true" : "false") + ">(a);\n}\n";
   return s;
