@@ -113,11 +113,18 @@ Engine::SpecKernel::~SpecKernel() {
 
 // configurations per tile of the two-phase kernels: the rule of fk_launch.h, or TFK_TWOPHASE_TILE_CFGS (32 | 64 | 128:
 // A/B knob for measurements -- smaller tiles touch less of the block-private record scratch)
-static int tile_cfgs_for(long long n, long long resident_blocks) {
+// small_tiles: the plan-specialised FP32 build.  Its phase A (the straight-line walk of THIS tree in FP32) is short, so
+// idle threads there cost little, while a 32-configuration tile touches a quarter of the block-private record scratch
+// (L2 hits instead of HBM round trips) and evens out the last wave: measured on B200 (profiles/README.md round 2) cfg5
+// FP32 0.437 -> 0.416 ms, cfg4 FP32 0.432 -> 0.421 ms.  FP64 builds keep 128 or 64 by the rule of fk_launch.h: a long
+// FP64 phase A with three quarters of the threads idle costs more than the scratch saves (cfg4 strict at 32: 1.27 ms
+// against 0.80 ms, cfg4 FP64-fast 1.32 ms; cfg5 FP64-fast gains 2 % at 64 or 32, within the rule's reach).
+static int tile_cfgs_for(long long n, long long resident_blocks, bool small_tiles) {
   if (const char *t = std::getenv("TFK_TWOPHASE_TILE_CFGS")) {
     const int v = std::atoi(t);
     if (v == 32 || v == 64 || v == (int)TFK_TILE) return v;
   }
+  if (small_tiles) return 32;
   return twophase_tile_cfgs(n, resident_blocks);
 }
 
@@ -331,7 +338,7 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
     it = sk.blocks_per_sm.insert(std::make_pair(device, b)).first;
   }
   // two-phase: configurations per tile (fk_launch.h:twophase_tile_cfgs; the two-phase builds use TFK_TILE threads)
-  const int tile_cfgs = sk.kind != 0 ? tile_cfgs_for(a.n, (int64_t)sm_count(device) * it->second) : sk.tile;
+  const int tile_cfgs = sk.kind != 0 ? tile_cfgs_for(a.n, (int64_t)sm_count(device) * it->second, precision == PREC_F32) : sk.tile;
   const int64_t n_tiles = (a.n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
   KernelArgs args = a;
@@ -624,7 +631,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   }
   const bool twophase = variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM;
   const int64_t resident = (int64_t)sm_count(device) * bps;
-  const int tile_cfgs = twophase ? tile_cfgs_for(n, resident) : (int)TFK_TILE;
+  const int tile_cfgs = twophase ? tile_cfgs_for(n, resident, false) : (int)TFK_TILE;
   const int64_t n_tiles = (n + tile_cfgs - 1) / tile_cfgs;
   const int grid = (int)std::min<int64_t>(n_tiles, resident);
   KernelArgs a;
