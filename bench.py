@@ -212,6 +212,7 @@ class ClockSampler:
 
     def __init__(self, gpu_index):
         self.samples, self.h, self.nv, self.t, self.on = [], None, None, None, False
+        self.in_region, self.n_in_region, self.smax = None, 0, None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -230,13 +231,17 @@ class ClockSampler:
             return
         nv = self.nv
         try:
+            inside = self.in_region is not None and self.in_region()
             sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
-            smax = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            if self.smax is None:
+                self.smax = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            smax = self.smax
             try:
                 r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
             except Exception:
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
             self.samples.append((float(sm), float(smax), int(r)))
+            self.n_in_region += 1 if inside else 0
         except Exception:
             pass
 
@@ -264,7 +269,10 @@ class ClockSampler:
         # nvml.h: SwPowerCap 0x4, HwSlowdown 0x8, SwThermalSlowdown 0x20, HwThermalSlowdown 0x40
         names = [("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "reasons": sorted(n for n, b in names if bits & b), "samples": len(sm)}
+                "reasons": sorted(n for n, b in names if bits & b), "samples": len(sm),
+                "samples_in_timed_region": self.n_in_region,
+                "note": "NVML polled back to back while the timed steps and an untimed tail of identical steps run (>= 60 ms of "
+                        "the same load in all): an NVML query takes longer than a step"}
 
 
 def measured_peaks():
@@ -344,22 +352,32 @@ def measure_device_resident(ctx, cfg, precision, n, steps, warmup, jit=True, see
         model.solve_fk_device(local_rank, stream.cuda_stream, d_q[i % n_rot].data_ptr(), n, lids, jids, rot, base,
                               True, prec, d_P.data_ptr(), d_J.data_ptr(), n, 0)
 
+    wev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    wev[0].record(stream)
     for i in range(max(warmup, 3)):
         step(i)
+    wev[1].record(stream)
     ctx["barrier"]()
+    est_ms = max(wev[0].elapsed_time(wev[1]) / max(warmup, 3), 1e-3)
     launches0 = capi.kernel_launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
     if clocks is not None:
+        clocks.in_region = lambda: not ev[-1].query()
         clocks.start()
     ev[0].record(stream)
     for i in range(steps):
         step(i)
         ev[i + 1].record(stream)
+    launches = capi.kernel_launch_count() - launches0
     if clocks is not None:
-        clocks.sample()  # the launches above are asynchronous: the GPU is inside the timed region now
+        # The timed region is a few milliseconds and an NVML query takes about one: keep the GPU under the SAME load (the
+        # same step, untimed, after the last event) until the sampler has seen >= 60 ms of it.  The events above are not
+        # affected; `samples_in_timed_region` counts the samples taken before the last timed step finished.
+        clocks.sample()
+        for i in range(int(min(4000, max(0.0, 60.0 / est_ms - steps)))):
+            step(steps + i)
     ctx["barrier"]()
     clk = clocks.stop() if clocks is not None else None
-    launches = capi.kernel_launch_count() - launches0
     total_ms = ev[0].elapsed_time(ev[-1])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
     max_ms = ctx["max_over_ranks"](total_ms)

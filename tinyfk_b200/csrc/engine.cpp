@@ -128,6 +128,13 @@ static int tile_cfgs_for(long long n, long long resident_blocks, bool small_tile
   return twophase_tile_cfgs(n, resident_blocks);
 }
 
+// shared memory (reals per thread) of the per-warp staging area of the two-phase kernel whose joint records stay in the
+// scratch: fk_launch.h:twophase_stage_reals; TFK_NO_STAGE=1 turns it off (A/B knob for measurements)
+static int twophase_stage_for(const PlanHeader &h) {
+  if (std::getenv("TFK_NO_STAGE")) return 0;
+  return twophase_stage_reals(h.n_out, h.off_base, h.off_frame);
+}
+
 // ---- plan specialisation (jit.hpp) -------------------------------------------------------------------------------
 bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bps, int *smem, int *kind, std::string *why) const {
   const PlanHeader *h = reinterpret_cast<const PlanHeader *>(e.blob.data());
@@ -150,7 +157,7 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
     const int table_bytes = (h->off_cols - h->off_outs + 15) & ~15;
     const SmemLayout Lh = smem_layout(table_bytes, h->n_in, h->off_frame, rb);
     const bool hot = 3 * (Lh.total + 1024) <= 227 * 1024 && !std::getenv("TFK_NO_SMEM_HOT");
-    const SmemLayout L = hot ? Lh : smem_layout(table_bytes, h->n_in, 0, rb);
+    const SmemLayout L = hot ? Lh : smem_layout(table_bytes, h->n_in, twophase_stage_for(*h), rb);
     if (L.total > 200 * 1024) {
       if (why) *why = "plan too large for shared memory";
       return false;
@@ -343,6 +350,7 @@ bool Engine::spec_launch(int device, cudaStream_t stream, PlanEntry &e, int prec
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)sm_count(device) * it->second);
   KernelArgs args = a;
   if (sk.kind != 0) args.sub_cfg = tile_cfgs;
+  args.stage = (sk.kind == 1 && twophase_stage_for(*reinterpret_cast<const PlanHeader *>(e.blob.data())) > 0) ? 1 : 0;
   const PlanHeader *ph = reinterpret_cast<const PlanHeader *>(e.blob.data());
   int rec_reals = ph->fz_size;
   if (sk.kind != 0) { // two-phase: per-output tables and the block-private record scratch, sized for THIS grid
@@ -562,7 +570,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   const int plan_bytes = table_bytes;
   // kernel variant (fk_kernels.cuh): one requested link -> fused walk + emit with thread-private records
   // in shared memory; several links -> two-phase through block-private scratch
-  int variant, rec_reals;
+  int variant, rec_reals, stage_reals = 0;
   SmemLayout L;
   if (sqdist) {
     rec_reals = h->rec_size;
@@ -600,6 +608,8 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
       L = Lh;
       variant = KV_TWOPHASE_SMEM;
       rec_reals = h->rec_size - h->off_frame;
+    } else if ((stage_reals = twophase_stage_for(*h)) > 0) {
+      L = smem_layout(plan_bytes, h->n_in, stage_reals, rb); // per-warp staging of the joint records (fk_launch.h)
     }
   }
   if ((variant == KV_FUSED_SMEM || variant == KV_FUSED_SMEM5 || variant == KV_TWOPHASE || variant == KV_TWOPHASE_SMEM) && !ex &&
@@ -651,6 +661,7 @@ void Engine::launch(int device, cudaStream_t stream, PlanEntry &e, int precision
   a.pairs = sqdist ? ex->d_pairs : nullptr;
   a.n_pairs = n_pairs;
   a.sub_cfg = twophase ? tile_cfgs : 0;
+  a.stage = (variant == KV_TWOPHASE && stage_reals > 0) ? 1 : 0;
   a.weights = com ? ex->d_weights : nullptr;
   a.n_com = com ? ex->n_com : 0;
   a.n_act = com ? ex->n_act : 0;

@@ -102,6 +102,10 @@ template <class T> struct DirectSink {
 // `stride` arguments below must equal it.
 template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   enum { D = ROT == 0 ? 3 : (ROT == 1 ? 6 : 7), LREC = ROT == 0 ? 3 : 7 };
+  // the same core over records laid out with another stride (the warp-private staged copy of fk_twophase_kernel)
+  template <int STRIDE2> struct Restride {
+    typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE2> type;
+  };
   typedef typename M::real T;
   typedef Ops<M> O;
   typedef Vec3<T> V;

@@ -287,7 +287,12 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
   PlanView pv = pv0;
   pv.lrec_of_out = reinterpret_cast<const int32_t *>(smem);
   pv.masks = reinterpret_cast<const uint32_t *>(smem + (h.off_masks - h.off_outs));
-  const SmemLayout L = smem_layout(a.table_bytes, h.n_in, SMEM_HOT ? h.off_frame : 0, (int)sizeof(T));
+  // without SMEM_HOT the record area of the layout is the warps' staging area for [base | axes | positions] (fk_launch.h:
+  // twophase_stage_reals), when the launch reserved it
+  const bool stage = !SMEM_HOT && a.stage != 0;
+  const int hot = h.off_frame - h.off_base;
+  const SmemLayout L = smem_layout(a.table_bytes, h.n_in,
+                                   SMEM_HOT ? h.off_frame : (stage ? twophase_stage_reals(h.n_out, h.off_base, h.off_frame) : 0), (int)sizeof(T));
   T *qs = reinterpret_cast<T *>(smem + L.q_off);
   // frames and link records: element k of configuration i at rec_link[(h.off_frame + k) * TILE + i] (biased when the hot part is
   // not in the scratch, so that the plan's absolute offsets apply to both arrays)
@@ -349,7 +354,23 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
       fac.nvalid = items - it0 < 32 ? items - it0 : 32;
       fac.head0 = hbase + it0;
       StagedSink<T, Core::D> out = fac.make();
-      Core::phase_b(pv, rec + il_c, e_c, o_c, out);
+      if (!SMEM_HOT && stage) {
+        // the (at most two) configurations of this warp's 32 items: their joint records into the warp's staging area,
+        // element k of configuration c0 + s at wst[2 * k + s]; every load is in flight before the first one is used
+        typedef typename Core::template Restride<2>::type CoreS;
+        T *wst = reinterpret_cast<T *>(smem + L.rec_off) + warp * 2 * hot;
+        const int last = it0 + 31 < items ? it0 + 31 : items - 1;
+        const int c0 = it0 / h.n_out, nc = last / h.n_out - c0 + 1;
+        __syncwarp();
+        for (int idx = lane; idx < 2 * hot; idx += 32) {
+          const int k = idx >> 1, s = idx & 1;
+          if (s < nc) wst[idx] = rec[(h.off_base + k) * TFK_TILE + c0 + s];
+        }
+        __syncwarp();
+        CoreS::phase_b(pv, wst - 2 * h.off_base + (il_c - c0), e_c, o_c, out);
+      } else {
+        Core::phase_b(pv, rec + il_c, e_c, o_c, out);
+      }
     }
     __syncthreads();
   }

@@ -51,6 +51,8 @@ struct KernelArgs {
   // KV_INERTIA: P = out (9, ld_cfg); weights = 7 reals per com link (mass, ixx, ixy, ixz, iyy, iyz, izz); n_com, mass_total
   // KV_COM only: P = com (3, ld_cfg), J = column-major (3*ld_cfg) x n_dof (or null)
   int sub_cfg;         // fk_twophase_kernel: configurations per tile (0 = TFK_TILE), twophase_tile_cfgs()
+  int stage = 0;       // fk_twophase_kernel without SMEM_HOT: 1 = the launch reserved the per-warp staging area of
+                       // twophase_stage_reals() and phase B reads [base | axes | positions] through it
   const void *weights; // device: n_com masses then n_act forces/total_mass, in the kernel's real type
   int n_com, n_act;
   double mass_total, vfs, com_diag;
@@ -84,6 +86,17 @@ TFK_HDI SmemLayout smem_layout_tile(int tile, int table_bytes, int n_in, int rec
 }
 TFK_HDI SmemLayout smem_layout(int table_bytes, int n_in, int rec_reals_in_smem, int real_bytes) {
   return smem_layout_tile(TFK_TILE, table_bytes, n_in, rec_reals_in_smem, real_bytes);
+}
+
+// Two-phase kernel whose joint records do not fit in shared memory for the whole tile (cfg5: 107 reals x 128 configurations):
+// a warp of phase B works on 32 consecutive (configuration, link) items, i.e. on at most TWO configurations when at least
+// 32 links are requested.  Their [base | axes | positions] records are copied from the block-private scratch into a
+// warp-private shared-memory area once per 32 items -- all loads in flight together, one L2 round trip -- instead of one
+// dependent round trip per Jacobian column and item.  Returns the area's size expressed in reals per thread of the block
+// (what smem_layout() takes), 0 when the request has fewer than 32 links.
+TFK_HDI int twophase_stage_reals(int n_out, int off_base, int off_frame) {
+  if (n_out < 32) return 0;
+  return ((TFK_TILE / 32) * 2 * (off_frame - off_base) + TFK_TILE - 1) / TFK_TILE;
 }
 
 // fk_twophase_kernel: configurations per tile.  When the batch needs more than one wave of resident blocks, the last
