@@ -149,7 +149,7 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
     // measured (B200, profiles/README.md v10): FP32 gains 28 % (cfg4) with everything unrolled; strict FP64 gains 5 % on
     // position-only requests (cfg4, walk kept rolled) and LOSES 12 % with orientation rows (cfg5: the unrolled RPY /
     // finite-difference columns of 21 columns outgrow the instruction cache) -- those stay with the generic kernel
-    if (precision == PREC_F64_STRICT && h->rot_type != 0) {
+    if (precision == PREC_F64_STRICT && h->rot_type != 0 && !std::getenv("TFK_SPEC_STRICT_ORIENT")) { // (env: A/B knob)
       if (why) *why = "several links with orientation rows in strict FP64: the generic two-phase kernel is faster";
       return false;
     }
