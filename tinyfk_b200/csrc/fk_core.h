@@ -93,6 +93,12 @@ template <class T> struct DirectSink {
   }
 };
 
+template <class T> struct RecPair;
+#if defined(__CUDACC__)
+template <> struct RecPair<double> { typedef double2 type; };
+template <> struct RecPair<float> { typedef float2 type; };
+#endif
+
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
 // instead of the reference's forward difference (FP32 mode: eps = 1e-7 is below one FP32 ulp).
 // ROT: the call's RotationType (0 IGNORE, 1 RPY, 2 XYZW) as a compile-time constant -- it fixes the
@@ -112,57 +118,120 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   typedef Quat<T> Q;
   typedef PoseT<T> P;
 
-  static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
+  // ---- record layout ------------------------------------------------------------------------------
+  // Element k of a configuration's records lives at rec[ix(k)], `rec` being the configuration's base pointer.
+  //   default        rec = array + i,          ix(k) = k * STRIDE                  ([k][STRIDE])
+  //   TFK_REC_PAIRS  rec = array + 2 * i,      ix(k) = (k / 2) * 2 * STRIDE + k % 2   ([k / 2][STRIDE][2])
+  // The pair layout (plan-specialised device builds) keeps elements 2m and 2m + 1 of one configuration adjacent and
+  // 16-byte aligned, so a 3-vector is TWO 128-bit loads instead of three 64-bit ones: phase B of the several-link
+  // kernels waits on exactly those shared-memory loads (profiles/r2_full_cfg4_fp64.txt: short scoreboard 3.1 + MIO
+  // throttle 1.6 cycles per issue).  STRIDE = 1 (CPU harness) makes both layouts the plain array.
+#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
+  enum { TB = 2 }; // distance between the base pointers of consecutive configurations
+  static TFK_FN int ix(int k) { return (k >> 1) * (2 * STRIDE) + (k & 1); }
+#else
+  enum { TB = 1 };
+  static TFK_FN int ix(int k) { return k * STRIDE; }
+#endif
+
+  // N consecutive elements at .. at + N - 1.  Pair layout: whole pairs as one 128-bit (FP64) access, the odd element at
+  // either end alone; `at & 1` is a constant of the plan in unrolled code and a uniform value in the rolled walk.
+  template <int N> static TFK_FN void ldn(const T *rec, int at, T (&v)[N]) {
+#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
+    typedef typename RecPair<T>::type T2;
+    const T *r_ = rec + ix(at & ~1); // the pair that holds element `at`
+    if (at & 1) {
+      v[0] = r_[1];
+      TFK_UNROLL
+      for (int m = 1; 2 * m <= N - 1; ++m) {
+        const T2 p = *reinterpret_cast<const T2 *>(r_ + m * (2 * STRIDE));
+        v[2 * m - 1] = p.x, v[2 * m] = p.y;
+      }
+      if ((N & 1) == 0) v[N - 1] = r_[(N / 2) * (2 * STRIDE)];
+    } else {
+      TFK_UNROLL
+      for (int m = 0; 2 * m + 1 <= N - 1; ++m) {
+        const T2 p = *reinterpret_cast<const T2 *>(r_ + m * (2 * STRIDE));
+        v[2 * m] = p.x, v[2 * m + 1] = p.y;
+      }
+      if (N & 1) v[N - 1] = r_[((N - 1) / 2) * (2 * STRIDE)];
+    }
+#else
+    const T *r_ = rec + at * STRIDE; // one address, constant offsets
+    TFK_UNROLL
+    for (int k = 0; k < N; ++k) v[k] = r_[k * STRIDE];
+#endif
+  }
+  template <int N> static TFK_FN void stn(T *rec, int at, const T (&v)[N]) {
+#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
+    typedef typename RecPair<T>::type T2;
+    T *r_ = rec + ix(at & ~1);
+    if (at & 1) {
+      r_[1] = v[0];
+      TFK_UNROLL
+      for (int m = 1; 2 * m <= N - 1; ++m) {
+        T2 p;
+        p.x = v[2 * m - 1], p.y = v[2 * m];
+        *reinterpret_cast<T2 *>(r_ + m * (2 * STRIDE)) = p;
+      }
+      if ((N & 1) == 0) r_[(N / 2) * (2 * STRIDE)] = v[N - 1];
+    } else {
+      TFK_UNROLL
+      for (int m = 0; 2 * m + 1 <= N - 1; ++m) {
+        T2 p;
+        p.x = v[2 * m], p.y = v[2 * m + 1];
+        *reinterpret_cast<T2 *>(r_ + m * (2 * STRIDE)) = p;
+      }
+      if (N & 1) r_[((N - 1) / 2) * (2 * STRIDE)] = v[N - 1];
+    }
+#else
     T *r_ = rec + at * STRIDE; // one address, constant offsets
-    r_[0 * STRIDE] = a.p.x;
-    r_[1 * STRIDE] = a.p.y;
-    r_[2 * STRIDE] = a.p.z;
-    r_[3 * STRIDE] = a.q.x;
-    r_[4 * STRIDE] = a.q.y;
-    r_[5 * STRIDE] = a.q.z;
-    r_[6 * STRIDE] = a.q.w;
+    TFK_UNROLL
+    for (int k = 0; k < N; ++k) r_[k * STRIDE] = v[k];
+#endif
+  }
+
+  static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {
+    const T v[7] = {a.p.x, a.p.y, a.p.z, a.q.x, a.q.y, a.q.z, a.q.w};
+    stn(rec, at, v);
   }
   static TFK_FN P get_pose(const T *rec, int stride, int at) {
-    const T *r_ = rec + at * STRIDE; // one address, constant offsets
+    T v[7];
+    ldn(rec, at, v);
     P a;
-    a.p.x = r_[0 * STRIDE];
-    a.p.y = r_[1 * STRIDE];
-    a.p.z = r_[2 * STRIDE];
-    a.q.x = r_[3 * STRIDE];
-    a.q.y = r_[4 * STRIDE];
-    a.q.z = r_[5 * STRIDE];
-    a.q.w = r_[6 * STRIDE];
+    a.p.x = v[0], a.p.y = v[1], a.p.z = v[2];
+    a.q.x = v[3], a.q.y = v[4], a.q.z = v[5], a.q.w = v[6];
     return a;
   }
   static TFK_FN V get_vec(const T *rec, int stride, int at) {
-    const T *r_ = rec + at * STRIDE; // one address, constant offsets
+    T v[3];
+    ldn(rec, at, v);
     V a;
-    a.x = r_[0 * STRIDE];
-    a.y = r_[1 * STRIDE];
-    a.z = r_[2 * STRIDE];
+    a.x = v[0], a.y = v[1], a.z = v[2];
     return a;
   }
   static TFK_FN void put_vec(T *rec, int stride, int at, const V &a) {
-    T *r_ = rec + at * STRIDE; // one address, constant offsets
-    r_[0 * STRIDE] = a.x;
-    r_[1 * STRIDE] = a.y;
-    r_[2 * STRIDE] = a.z;
+    const T v[3] = {a.x, a.y, a.z};
+    stn(rec, at, v);
   }
   static TFK_FN Q get_quat(const T *rec, int stride, int at) {
-    const T *r_ = rec + at * STRIDE; // one address, constant offsets
+    T v[4];
+    ldn(rec, at, v);
     Q a;
-    a.x = r_[0 * STRIDE];
-    a.y = r_[1 * STRIDE];
-    a.z = r_[2 * STRIDE];
-    a.w = r_[3 * STRIDE];
+    a.x = v[0], a.y = v[1], a.z = v[2], a.w = v[3];
     return a;
   }
   static TFK_FN void put_quat(T *rec, int stride, int at, const Q &a) {
-    T *r_ = rec + at * STRIDE; // one address, constant offsets
-    r_[0 * STRIDE] = a.x;
-    r_[1 * STRIDE] = a.y;
-    r_[2 * STRIDE] = a.z;
-    r_[3 * STRIDE] = a.w;
+    const T v[4] = {a.x, a.y, a.z, a.w};
+    stn(rec, at, v);
+  }
+  // per-lane record offsets (phase B reads the link record of ITS output: `at` differs from lane to lane): element-wise
+  static TFK_FN P get_pose_lane(const T *rec, int at, bool with_q) {
+    P a;
+    a.p.x = rec[ix(at)], a.p.y = rec[ix(at + 1)], a.p.z = rec[ix(at + 2)];
+    a.q = O::qidentity();
+    if (with_q) a.q.x = rec[ix(at + 3)], a.q.y = rec[ix(at + 4)], a.q.z = rec[ix(at + 5)], a.q.w = rec[ix(at + 6)];
+    return a;
   }
 
   // ---------------------------------------------------------------------------------------------
@@ -280,10 +349,10 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       PlanerCtx c;
       c.base_p = get_vec(rec, stride, at);
       c.binv.p = get_vec(rec, stride, at + 7);
-      c.binv.q.z = rec[(at + 12) * STRIDE];
-      c.binv.q.w = rec[(at + 13) * STRIDE];
-      c.bk.z = rec[(at + 24) * STRIDE];
-      c.bk.w = rec[(at + 25) * STRIDE];
+      c.binv.q.z = rec[ix(at + 12)];
+      c.binv.q.w = rec[ix(at + 13)];
+      c.bk.z = rec[ix(at + 24)];
+      c.bk.w = rec[ix(at + 25)];
       return c;
     }
   };
@@ -731,11 +800,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
   // the pose phase A recorded for output o (the kernel loads the NEXT item's while it works on the current one)
   static TFK_FN P load_link(const PlanView &pv, const T *rec_link, int o) {
     const int lat = pv.h->off_lrec + pv.lrec_of_out[o] * LREC;
-    P e;
-    e.p = get_vec(rec_link, STRIDE, lat);
-    e.q = O::qidentity();
-    if (LREC == 7) e.q = get_quat(rec_link, STRIDE, lat + 3);
-    return e;
+    return get_pose_lane(rec_link, lat, LREC == 7);
   }
   template <class OutSink> static TFK_FN void phase_b(const PlanView &pv, const T *rec, const P &e, int o, OutSink &out) {
     const PlanHeader &h = *pv.h;

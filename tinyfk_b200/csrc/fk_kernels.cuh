@@ -243,7 +243,7 @@ __device__ __forceinline__ void fk_fused_spec_body(const KernelArgs &a) {
   // records, which lets more warps stay resident
   T *stg0 = reinterpret_cast<T *>(smem);
   T *rec = stg0 + fused_strip_reals(TFK_TILE);
-  rec += threadIdx.x;
+  rec += Core::TB * threadIdx.x; // fk_core.h "record layout"
   const T *q = static_cast<const T *>(a.q);
   const int warp = threadIdx.x >> 5;
 
@@ -318,7 +318,8 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
     stage_q_tile(qs, L.q_pitch, q, i0, nv, h.n_in);
     prefetch_q_tile(q, i0 + (long long)gridDim.x * tc, a.n, h.n_in);
     __syncthreads();
-    if ((int)threadIdx.x < nv) Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + threadIdx.x, rec_link + threadIdx.x, TFK_TILE);
+    if ((int)threadIdx.x < nv)
+      Core::phase_a(pv, qs + threadIdx.x * L.q_pitch, rec + Core::TB * threadIdx.x, rec_link + Core::TB * threadIdx.x, TFK_TILE);
     __syncthreads();
     const int items = nv * h.n_out;
     const long long hbase = (a.row0 + i0) * h.n_out;
@@ -334,14 +335,14 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
       const int itc = warp * 32 + lane < items ? warp * 32 + lane : items - 1;
       il = itc / h.n_out;
       o = itc - il * h.n_out;
-      e = Core::load_link(pv, rec_link + il, o);
+      e = Core::load_link(pv, rec_link + Core::TB * il, o);
     }
     for (int it0 = warp * 32; it0 < items; it0 += TFK_TILE) {
       if (!PREFETCH) {
         const int itc = it0 + lane < items ? it0 + lane : items - 1;
         il = itc / h.n_out;
         o = itc - il * h.n_out;
-        e = Core::load_link(pv, rec_link + il, o);
+        e = Core::load_link(pv, rec_link + Core::TB * il, o);
       }
       const int il_c = il, o_c = o;
       const typename Core::P e_c = e;
@@ -349,7 +350,7 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
         const int itn = it0 + TFK_TILE + lane < items ? it0 + TFK_TILE + lane : items - 1;
         il = itn / h.n_out;
         o = itn - il * h.n_out;
-        e = Core::load_link(pv, rec_link + il, o);
+        e = Core::load_link(pv, rec_link + Core::TB * il, o);
       }
       fac.nvalid = items - it0 < 32 ? items - it0 : 32;
       fac.head0 = hbase + it0;
@@ -364,12 +365,12 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
         __syncwarp();
         for (int idx = lane; idx < 2 * hot; idx += 32) {
           const int k = idx >> 1, s = idx & 1;
-          if (s < nc) wst[idx] = rec[(h.off_base + k) * TFK_TILE + c0 + s];
+          if (s < nc) wst[CoreS::ix(k) + CoreS::TB * s] = rec[Core::ix(h.off_base + k) + Core::TB * (c0 + s)];
         }
         __syncwarp();
-        CoreS::phase_b(pv, wst - 2 * h.off_base + (il_c - c0), e_c, o_c, out);
+        CoreS::phase_b(pv, wst - CoreS::ix(h.off_base) + CoreS::TB * (il_c - c0), e_c, o_c, out);
       } else {
-        Core::phase_b(pv, rec + il_c, e_c, o_c, out);
+        Core::phase_b(pv, rec + Core::TB * il_c, e_c, o_c, out);
       }
     }
     __syncthreads();

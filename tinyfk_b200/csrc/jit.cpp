@@ -153,6 +153,10 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   // several links, FP64 (strict and fast): one rolled copy of the walk, fk_core.h TFK_WALK_LOOP (FP64-fast cfg4: 0.873 ->
   // 0.811 ms with the walk rolled, cfg5 0.880 -> 0.872 ms; FP32 code is half the size and keeps the unrolled walk)
   if (o.kind != 0 && o.precision != PREC_F32) s += "#define TFK_SPEC_ROLLED_WALK 1\n";
+  // several links: records in the pair layout of fk_core.h ("record layout"): 128-bit record loads in phase B (cfg5 FP32
+  // 0.414 -> 0.363 ms, cfg4 FP32 0.423 -> 0.394 ms, cfg5 FP64-fast 0.864 -> 0.785 ms, cfg4 strict 0.811 -> 0.790 ms; the
+  // single-link kernels neither gain nor lose and keep the plain layout).  TFK_NO_REC_PAIRS=1: A/B knob
+  if (o.kind != 0 && !std::getenv("TFK_NO_REC_PAIRS")) s += "#define TFK_REC_PAIRS 1\n";
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;

@@ -266,14 +266,16 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.off_prec = h.off_arec + 3 * n_arec;
   // [base | arec | prec] are what every (configuration, link) item re-reads (small: shared memory when it fits);
   // branch-point frames and link records come last (block-private scratch in L2)
-  h.off_frame = h.off_prec + 3 * n_prec;
+  // (off_frame, rec_size and fz_size are even: the pair layout of the plan-specialised kernels, fk_core.h "record layout",
+  // splits the records between shared memory and the scratch at a pair boundary)
+  h.off_frame = (h.off_prec + 3 * n_prec + 1) & ~1;
   h.off_lrec = h.off_frame + 7 * b.frames_max;
-  h.rec_size = h.off_lrec + h.lrec_size * n_lrec;
+  h.rec_size = (h.off_lrec + h.lrec_size * n_lrec + 1) & ~1;
   // fused single-link kernel: the link pose and the base context stay in registers
   h.fz_arec = (jac && key.base_type != BASE_FIXED) ? 7 : 0; // base pose, re-read for the base columns
   h.fz_prec = h.fz_arec + 3 * n_arec;
   h.fz_frame = h.fz_prec + 3 * n_prec;
-  h.fz_size = h.fz_frame + 7 * b.frames_max;
+  h.fz_size = (h.fz_frame + 7 * b.frames_max + 1) & ~1;
   h.root_lrec = root_lrec;
   h.mask_words = mask_words;
   h.n_frames = b.frames_max;
