@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtinyfk_b200.so")
+LIB_PATH = os.environ.get("TFK_B200_LIB") or os.path.join(_HERE, "libtinyfk_b200.so")  # (env: A/B builds of the library)
 
 _vp = ctypes.c_void_p
 _ip = ctypes.POINTER(ctypes.c_int)

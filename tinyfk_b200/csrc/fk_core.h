@@ -93,11 +93,12 @@ template <class T> struct DirectSink {
   }
 };
 
-template <class T> struct RecPair;
-#if defined(__CUDACC__)
-template <> struct RecPair<double> { typedef double2 type; };
-template <> struct RecPair<float> { typedef float2 type; };
-#endif
+// two adjacent record elements moved as one (pair layout of FkCore, below)
+template <class T> struct RecPair {
+  struct alignas(2 * sizeof(T)) type {
+    T x, y;
+  };
+};
 
 // M: math policy (fk_math.h).  ANALYTIC_BASE: base-rotation Jacobian columns from the closed form
 // instead of the reference's forward difference (FP32 mode: eps = 1e-7 is below one FP32 ulp).
@@ -106,12 +107,15 @@ template <> struct RecPair<float> { typedef float2 type; };
 // STRIDE: distance in reals between consecutive record elements of one configuration ([k][STRIDE] layout:
 // TFK_TILE in the kernels, 1 in the CPU harness) -- compile-time, so record addresses are immediates; the
 // `stride` arguments below must equal it.
-template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
+template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE, bool PAIRS = false> struct FkCore {
   enum { D = ROT == 0 ? 3 : (ROT == 1 ? 6 : 7), LREC = ROT == 0 ? 3 : 7 };
   // the same core over records laid out with another stride (the warp-private staged copy of fk_twophase_kernel)
   template <int STRIDE2> struct Restride {
-    typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE2> type;
+    typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE2, PAIRS> type;
   };
+  // the same core over the pair layout / the plain layout of the records (below)
+  typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE, true> Paired;
+  typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE, false> Plain;
   typedef typename M::real T;
   typedef Ops<M> O;
   typedef Vec3<T> V;
@@ -120,24 +124,21 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
 
   // ---- record layout ------------------------------------------------------------------------------
   // Element k of a configuration's records lives at rec[ix(k)], `rec` being the configuration's base pointer.
-  //   default        rec = array + i,          ix(k) = k * STRIDE                  ([k][STRIDE])
-  //   TFK_REC_PAIRS  rec = array + 2 * i,      ix(k) = (k / 2) * 2 * STRIDE + k % 2   ([k / 2][STRIDE][2])
-  // The pair layout (plan-specialised device builds) keeps elements 2m and 2m + 1 of one configuration adjacent and
-  // 16-byte aligned, so a 3-vector is TWO 128-bit loads instead of three 64-bit ones: phase B of the several-link
-  // kernels waits on exactly those shared-memory loads (profiles/r2_full_cfg4_fp64.txt: short scoreboard 3.1 + MIO
-  // throttle 1.6 cycles per issue).  STRIDE = 1 (CPU harness) makes both layouts the plain array.
-#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
-  enum { TB = 2 }; // distance between the base pointers of consecutive configurations
-  static TFK_FN int ix(int k) { return (k >> 1) * (2 * STRIDE) + (k & 1); }
-#else
-  enum { TB = 1 };
-  static TFK_FN int ix(int k) { return k * STRIDE; }
-#endif
+  //   PAIRS = false  rec = array + i,          ix(k) = k * STRIDE                     ([k][STRIDE])
+  //   PAIRS = true   rec = array + 2 * i,      ix(k) = (k / 2) * 2 * STRIDE + k % 2   ([k / 2][STRIDE][2])
+  // The pair layout (the several-link device kernels) keeps elements 2m and 2m + 1 of one configuration adjacent and
+  // 16-byte aligned (FP64), so a run of N elements is moved as whole pairs -- a 3-vector is one 128-bit and one 64-bit
+  // access instead of three 64-bit ones, a pose four instead of seven: phase B of the several-link kernels waits on
+  // exactly those shared-memory loads (profiles/r2_full_cfg4_fp64.txt before: short scoreboard 3.1 + MIO throttle 1.6
+  // cycles per issue).  The plan keeps off_frame, rec_size and fz_size even (plan.cpp), so the split of the records
+  // between shared memory and the scratch falls on a pair boundary.
+  enum { TB = PAIRS ? 2 : 1 }; // distance between the base pointers of consecutive configurations
+  static TFK_FN int ix(int k) { return PAIRS ? (k >> 1) * (2 * STRIDE) + (k & 1) : k * STRIDE; }
 
   // N consecutive elements at .. at + N - 1.  Pair layout: whole pairs as one 128-bit (FP64) access, the odd element at
   // either end alone; `at & 1` is a constant of the plan in unrolled code and a uniform value in the rolled walk.
   template <int N> static TFK_FN void ldn(const T *rec, int at, T (&v)[N]) {
-#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
+    if (PAIRS) {
     typedef typename RecPair<T>::type T2;
     const T *r_ = rec + ix(at & ~1); // the pair that holds element `at`
     if (at & 1) {
@@ -156,14 +157,14 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       }
       if (N & 1) v[N - 1] = r_[((N - 1) / 2) * (2 * STRIDE)];
     }
-#else
+    return;
+    }
     const T *r_ = rec + at * STRIDE; // one address, constant offsets
     TFK_UNROLL
     for (int k = 0; k < N; ++k) v[k] = r_[k * STRIDE];
-#endif
   }
   template <int N> static TFK_FN void stn(T *rec, int at, const T (&v)[N]) {
-#if defined(TFK_REC_PAIRS) && defined(__CUDA_ARCH__)
+    if (PAIRS) {
     typedef typename RecPair<T>::type T2;
     T *r_ = rec + ix(at & ~1);
     if (at & 1) {
@@ -184,11 +185,11 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE> struct FkCore {
       }
       if (N & 1) r_[((N - 1) / 2) * (2 * STRIDE)] = v[N - 1];
     }
-#else
+    return;
+    }
     T *r_ = rec + at * STRIDE; // one address, constant offsets
     TFK_UNROLL
     for (int k = 0; k < N; ++k) r_[k * STRIDE] = v[k];
-#endif
   }
 
   static TFK_FN void put_pose(T *rec, int stride, int at, const P &a) {

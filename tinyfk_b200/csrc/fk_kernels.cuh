@@ -385,7 +385,11 @@ __global__ void __launch_bounds__(TFK_TILE, 4) fk_twophase_kernel(const KernelAr
   pv.cols = pp.cols;
   pv.lrec_of_out = nullptr; // set by the body (shared memory)
   pv.masks = nullptr;
+#if defined(TFK_GENERIC_PLAIN_RECORDS) // A/B build: the generic kernel on the plain record layout
   fk_twophase_body<Core, SMEM_HOT>(a, pv);
+#else
+  fk_twophase_body<typename Core::Paired, SMEM_HOT>(a, pv); // records in the pair layout (fk_core.h "record layout")
+#endif
 }
 
 #if defined(TFK_SPEC_PLAN)

@@ -153,10 +153,6 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
   // several links, FP64 (strict and fast): one rolled copy of the walk, fk_core.h TFK_WALK_LOOP (FP64-fast cfg4: 0.873 ->
   // 0.811 ms with the walk rolled, cfg5 0.880 -> 0.872 ms; FP32 code is half the size and keeps the unrolled walk)
   if (o.kind != 0 && o.precision != PREC_F32) s += "#define TFK_SPEC_ROLLED_WALK 1\n";
-  // several links: records in the pair layout of fk_core.h ("record layout"): 128-bit record loads in phase B (cfg5 FP32
-  // 0.414 -> 0.363 ms, cfg4 FP32 0.423 -> 0.394 ms, cfg5 FP64-fast 0.864 -> 0.785 ms, cfg4 strict 0.811 -> 0.790 ms; the
-  // single-link kernels neither gain nor lose and keep the plain layout).  TFK_NO_REC_PAIRS=1: A/B knob
-  if (o.kind != 0 && !std::getenv("TFK_NO_REC_PAIRS")) s += "#define TFK_REC_PAIRS 1\n";
   s += "#define TFK_TILE_CFG " + std::to_string(o.tile) + "\n";
   s += "#include \"fk_plan.h\"\n";
   s += plan_source;
@@ -165,7 +161,12 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
        ") tfk_spec_kernel(const tfk::KernelArgs a) {\n";
   const std::string core = std::string("tfk::FkCore<") +
                            (f32 ? "tfk::MathNative32, true, " : (o.precision == PREC_F64_FAST ? "tfk::MathFast64, true, " : "tfk::MathPortable, false, ")) +
-                           std::to_string(o.rot_type) + ", tfk::TFK_TILE>";
+                           std::to_string(o.rot_type) + ", tfk::TFK_TILE" +
+                           // several links: records in the pair layout of fk_core.h ("record layout"): every record access moves
+                           // whole pairs (cfg4 strict 0.808 -> 0.742 ms, cfg4 FP32 0.421 -> 0.340 ms, cfg5 FP32 0.411 -> 0.348 ms,
+                           // cfg5 FP64-fast 0.862 -> 0.788 ms; the single-link kernels neither gain nor lose and keep the plain
+                           // layout).  TFK_NO_REC_PAIRS=1: A/B knob
+                           (((o.kind != 0 || std::getenv("TFK_REC_PAIRS_FUSED")) && !std::getenv("TFK_NO_REC_PAIRS")) ? ", true>" : ">");
   if (o.kind == 0)
     s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
   else
