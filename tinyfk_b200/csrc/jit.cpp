@@ -164,9 +164,9 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
                            std::to_string(o.rot_type) + ", tfk::TFK_TILE" +
                            // several links: records in the pair layout of fk_core.h ("record layout"): every record access moves
                            // whole pairs (cfg4 strict 0.808 -> 0.742 ms, cfg4 FP32 0.421 -> 0.340 ms, cfg5 FP32 0.411 -> 0.348 ms,
-                           // cfg5 FP64-fast 0.862 -> 0.788 ms; the single-link kernels neither gain nor lose and keep the plain
-                           // layout).  TFK_NO_REC_PAIRS=1: A/B knob
-                           (((o.kind != 0 || std::getenv("TFK_REC_PAIRS_FUSED")) && !std::getenv("TFK_NO_REC_PAIRS")) ? ", true>" : ">");
+                           // cfg5 FP64-fast 0.862 -> 0.788 ms).  Single-link kernels: FP32 gains 1 % (cfg2 0.0681 -> 0.0674 ms, cfg3
+                           // 0.1111 -> 0.1097 ms) and takes it, FP64 loses 1 % and keeps the plain layout.  TFK_NO_REC_PAIRS=1: A/B knob
+                           (((o.kind != 0 || f32) && !std::getenv("TFK_NO_REC_PAIRS")) ? ", true>" : ">");
   if (o.kind == 0)
     s += "  tfk::fk_fused_spec_body<" + core + ", true, " + std::to_string(o.blocks_per_sm) + ">(a);\n}\n";
   else
