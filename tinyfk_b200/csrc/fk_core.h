@@ -109,6 +109,7 @@ template <class T> struct RecPair {
 // `stride` arguments below must equal it.
 template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE, bool PAIRS = false> struct FkCore {
   enum { D = ROT == 0 ? 3 : (ROT == 1 ? 6 : 7), LREC = ROT == 0 ? 3 : 7 };
+  enum { SPARE = M::SPARE_REGS }; // the mode's arithmetic leaves registers for software prefetch (fk_twophase_kernel)
   // the same core over records laid out with another stride (the warp-private staged copy of fk_twophase_kernel)
   template <int STRIDE2> struct Restride {
     typedef FkCore<M, ANALYTIC_BASE, ROT, STRIDE2, PAIRS> type;

@@ -323,10 +323,11 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
     __syncthreads();
     const int items = nv * h.n_out;
     const long long hbase = (a.row0 + i0) * h.n_out;
-    // one (configuration, link) item per lane.  Position-only records (3 reals): the NEXT item's record is requested
-    // from the scratch (L2) before the current item is worked on, so its latency hides behind a whole item instead of
-    // stalling the item's first arithmetic; 7-real records are loaded where they are used (no registers to spare).
-    enum { PREFETCH = Core::LREC == 3 };
+    // one (configuration, link) item per lane.  The NEXT item's link record is requested from the scratch (L2) before the
+    // current item is worked on, so its latency hides behind a whole item instead of stalling the item's first arithmetic:
+    // always for position-only records (3 reals), for 7-real records where the arithmetic leaves registers (Core::SPARE:
+    // the FP32 mode, cfg5 0.348 -> 0.340 ms; the FP64 kernels sit at or near their register cap and do not gain).
+    enum { PREFETCH = Core::LREC == 3 || Core::SPARE };
     int il = 0, o = 0;
     typename Core::P e;
     e.p.x = e.p.y = e.p.z = T(0);
@@ -357,7 +358,9 @@ __device__ __forceinline__ void fk_twophase_body(const KernelArgs &a, const Plan
       StagedSink<T, Core::D> out = fac.make();
       if (!SMEM_HOT && stage) {
         // the (at most two) configurations of this warp's 32 items: their joint records into the warp's staging area,
-        // element k of configuration c0 + s at wst[2 * k + s]; every load is in flight before the first one is used
+        // element k of configuration c0 + s at wst[CoreS::ix(k) + TB * s]; every load is in flight before the first one
+        // is used.  (Issuing the NEXT batch's loads before this batch is worked on -- eight more registers per lane --
+        // measured slower in the one mode that would need it: FP64-fast cfg5 0.840 vs 0.788 ms.)
         typedef typename Core::template Restride<2>::type CoreS;
         T *wst = reinterpret_cast<T *>(smem + L.rec_off) + warp * 2 * hot;
         const int last = it0 + 31 < items ? it0 + 31 : items - 1;

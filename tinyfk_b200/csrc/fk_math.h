@@ -56,6 +56,9 @@ template <class T> struct PoseT {
 // Portable libm: identical bits on host and device (fkmath.h).  FP64 only.
 struct MathPortable {
   typedef double real;
+  // registers to spare for prefetching the next item's 7-real link record in the several-link kernels
+  // (fk_kernels.cuh:fk_twophase_body)?  Strict FP64 sits at its register cap.
+  enum { SPARE_REGS = 0 };
   static TFK_FN double sin_(double x) { return tfk_sin(x); }
   static TFK_FN double cos_(double x) { return tfk_cos(x); }
   // fkmath_simt.h: bit-identical to fkmath.h's functions, restructured for warps
@@ -172,6 +175,7 @@ struct MathPortable {
 // The platform's own libm (glibc on the host, libdevice on the GPU).
 struct MathNative64 {
   typedef double real;
+  enum { SPARE_REGS = 0 };
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
   static TFK_FN void sincos_(double x, double *s, double *c) {
@@ -206,6 +210,7 @@ struct MathNative64 {
 
 struct MathNative32 {
   typedef float real;
+  enum { SPARE_REGS = 1 }; // see MathPortable (cfg5 FP32 0.348 -> 0.340 ms)
   static TFK_FN float sin_(float x) { return ::sinf(x); }
   static TFK_FN float cos_(float x) { return ::cosf(x); }
   static TFK_FN void sincos_(float x, float *s, float *c) {
@@ -257,6 +262,7 @@ struct MathNative32 {
 // contract is 1e-12 on poses and analytic Jacobian entries.
 struct MathFast64 {
   typedef double real;
+  enum { SPARE_REGS = 0 }; // see MathPortable (measured: no gain on cfg4 / cfg5)
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
   static TFK_FN void sincos_(double x, double *s, double *c) {
