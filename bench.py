@@ -225,6 +225,11 @@ class ClockSampler:
                 self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
         except Exception:
             self.h = None
+        # the first NVML queries of a process can take tens of milliseconds (lazy initialisation): pay for them here,
+        # not inside the timed region
+        for _ in range(3):
+            self.sample()
+        self.samples, self.n_in_region = [], 0
 
     def sample(self):
         if self.h is None:
