@@ -280,7 +280,8 @@ void emu_link_info(void *m, int id, int *parent, int *jtype, int *jid, double *a
 int emu_is_relevant(void *m, int l, int j) { return static_cast<KinematicModel *>(m)->is_relevant(l, j) ? 1 : 0; }
 
 // mode 0: FP64 strict (portable libm, FD base columns); 1: FP32 (native libm, analytic base columns);
-// 2: FP64 with the platform libm (FD base columns); +16: force the two-phase driver for a single link
+// 2: FP64 with the platform libm (FD base columns); 3: FP64 fast; +16: force the two-phase driver for a single link;
+// +32 (modes 0 and 1): the core over the pair layout of the records
 int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, const int *joints, int n_joint,
               int rot_type, int base_type, int with_jacobian, int mode, double *P, double *J) {
   try {
@@ -293,10 +294,15 @@ int emu_solve(void *m, const double *qs, long n, const int *elinks, int n_link, 
     key.model_version = static_cast<KinematicModel *>(m)->version();
     std::vector<unsigned char> blob = build_plan(*static_cast<KinematicModel *>(m), key);
     const bool two_phase = (mode & 16) != 0;
+    const bool paired = (mode & 32) != 0; // the record accessors of the pair layout (fk_core.h "record layout"; stride 1 here)
     mode &= 15;
     double *Jp = with_jacobian ? J : nullptr;
 #define TFK_EMU_RUN(R)                                                                      \
-  if (mode == 0)                                                                            \
+  if (mode == 0 && paired)                                                                  \
+    run<FkCore<MathPortable, false, R, 1, true>, double>(blob, qs, n, P, Jp, two_phase);       \
+  else if (mode == 1 && paired)                                                             \
+    run<FkCore<MathNative32, true, R, 1, true>, float>(blob, qs, n, P, Jp, two_phase);         \
+  else if (mode == 0)                                                                       \
     run<FkCore<MathPortable, false, R, 1>, double>(blob, qs, n, P, Jp, two_phase);             \
   else if (mode == 1)                                                                       \
     run<FkCore<MathNative32, true, R, 1>, float>(blob, qs, n, P, Jp, two_phase);               \

@@ -77,3 +77,24 @@ def test_core_fp32_and_native64_modes_are_close():
     assert np.abs(P - Pr).max() < 1e-13 and np.abs(J - Jr)[:, :10].max() < 1e-13 and np.abs(J - Jr).max() < 1e-6
     P, J = e.solve_fk(q, lids, jids, 2, 2, True, mode=emuapi.MODE_F32)
     assert np.abs(P - Pr).max() < 1e-5 and np.abs(J - Jr).max() < 1e-5
+
+
+@pytest.mark.parametrize("cfg,n", [("cfg2", 64), ("cfg3", 64), ("cfg4", 12), ("cfg5", 6)])
+@pytest.mark.parametrize("two_phase", [False, True])
+def test_pair_layout_accessors_equal_the_plain_layout(cfg, n, two_phase):
+    """FkCore<..., PAIRS = true> (the record layout of the several-link device kernels: whole 16-byte pairs per access,
+    csrc/fk_core.h "record layout") run on the CPU with stride 1: every run of 3, 4 and 7 record elements starting on an
+    even or an odd offset goes through the pair accessors and must give the plain layout's bits."""
+    from emuapi import MODE_F32, MODE_STRICT64, EmuModel
+    from tinyfk_b200 import capi
+    emu = EmuModel(W.urdf_text(W.CONFIGS[cfg][0]))
+    j, l, rot, base = W.setup(emu, cfg)
+    prod = capi.Model(W.urdf_text(W.CONFIGS[cfg][0]), host_libm=0)
+    jp, _, _, _ = W.setup(prod, cfg)
+    q = W.sample_q(prod.get_joint_limits(jp), base, n, seed=31, wide_pitch=True)
+    tp = 16 if two_phase else 0
+    for mode in (MODE_STRICT64, MODE_F32):
+        for jac in (True, False):
+            P0, J0 = emu.solve_fk(q, l, j, rot, base, jac, mode=mode | tp)
+            P1, J1 = emu.solve_fk(q, l, j, rot, base, jac, mode=mode | tp | 32)
+            assert np.array_equal(P0, P1) and np.array_equal(J0, J1), (cfg, mode, jac)
