@@ -57,8 +57,14 @@ def test_cpp_calls_equal_the_python_facade_bit_for_bit(exe):
     for k in range(4):
         assert np.array_equal(_vals(lines[2 * k]), P[k, :3]) and np.array_equal(_vals(lines[2 * k + 1]), P[k, 3:])
     assert lines[8].split() == ["jac", "6", "13"]
-    _, J = m.solve_fk(q, [l[0]], j, W.ROT_RPY, W.BASE_FLOATING, True)
+    # get_jacobian(with_base) evaluates the STORED base pose: the header reads it back as (xyz, rpy) -- rpy recomputed from
+    # the stored quaternion, equal to what was set to within rounding -- and sends it as the row's base part
+    m.set_base_pose(base)
+    stored = list(m.get_base_pose())
+    assert np.abs(np.array(stored) - np.array(base)).max() < 1e-15
+    _, J = m.solve_fk(np.array([ang + stored]), [l[0]], j, W.ROT_RPY, W.BASE_FLOATING, True)
     assert np.array_equal(_vals(lines[9]), J.T.ravel())     # column-major 6 x 13
+    # (both sides now hold the base pose that call wrote back; the FIXED-base Jacobian below is evaluated at it)
     _, J2 = m.solve_fk(np.array([ang]), [new], j, W.ROT_IGNORE, W.BASE_FIXED, True)
     assert np.array_equal(_vals(lines[10]), J2.T.ravel())
     qs = np.array([[0.1 * (c + 1) - 0.37 * i for c in range(10)] for i in range(3)])
