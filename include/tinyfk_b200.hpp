@@ -18,8 +18,8 @@
 // reference does) by sending a one-row batch through tfk_solve_fk_host: one kernel launch per call -- they exist so that
 // existing C++ call sites keep working; throughput comes from solve_fk().  get_jacobian(.., with_base = true) hands the
 // stored base pose to the batch entry as (xyz, rpy) read back from the stored quaternion: equal to the stored pose to
-// within rounding (1e-16), which the reference's eps = 1e-7 finite-difference base columns amplify to ~1e-9.  Errors become exceptions
-// (std::invalid_argument / std::runtime_error), as in the reference.  Link with -ltinyfk_b200.
+// within rounding (1e-16), which the reference's eps = 1e-7 finite-difference base columns amplify to ~1e-9.
+// Errors become exceptions (std::invalid_argument / std::runtime_error), as in the reference.  Link with -ltinyfk_b200.
 #ifndef TINYFK_B200_HPP
 #define TINYFK_B200_HPP
 
