@@ -360,14 +360,33 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE, bool PAIRS = false> 
   };
   // fused: one link per configuration, so everything is computed where it is used; only the base pose
   // itself is re-read from the record (it exists only for a Jacobian with a moving base)
+  // the base record of the fused driver: a PLANER pose is (x, y, 0) and (0, 0, z, w) -- four reals
+  static TFK_FN void put_base_fused(const PlanHeader &h, T *rec, const P &base) {
+    if (h.base_type == 1) {
+      const T v[4] = {base.p.x, base.p.y, base.q.z, base.q.w};
+      stn(rec, 0, v);
+    } else {
+      put_pose(rec, STRIDE, 0, base);
+    }
+  }
+  static TFK_FN P get_base_fused(const PlanHeader &h, const T *rec) {
+    if (h.base_type != 1) return get_pose(rec, STRIDE, 0);
+    T v[4];
+    ldn(rec, 0, v);
+    P b;
+    b.p.x = v[0], b.p.y = v[1], b.p.z = T(0);
+    b.q.x = T(0), b.q.y = T(0), b.q.z = v[2], b.q.w = v[3];
+    return b;
+  }
   struct BaseComputed {
     const T *rec;
     int stride;
+    const PlanHeader *h;
     P b;
     V rpy_b;
     V wk[3];
     TFK_FN void prepare() {
-      b = get_pose(rec, stride, 0);
+      b = get_base_fused(*h, rec);
       rpy_b = O::to_rpy(b.q);
       if (ANALYTIC_BASE) analytic_axes(rpy_b, wk);
     }
@@ -375,7 +394,7 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE, bool PAIRS = false> 
     TFK_FN P binv() const { return O::inverse(b); }
     TFK_FN Q bk(int k) const { return tweaked_rotation(rpy_b, k); }
     TFK_FN V w(int k) const { return (k == 0) ? wk[0] : ((k == 1) ? wk[1] : wk[2]); }
-    TFK_FN PlanerCtx planer() const { return planer_ctx(get_pose(rec, stride, 0)); }
+    TFK_FN PlanerCtx planer() const { return planer_ctx(get_base_fused(*h, rec)); }
   };
 
   // ---------------------------------------------------------------------------------------------
@@ -1097,11 +1116,12 @@ template <class M, bool ANALYTIC_BASE, int ROT, int STRIDE, bool PAIRS = false> 
   static TFK_FN void run_fused(const PlanView &pv, const T *qrow, T *rec, int stride, const OutFactory &make_out) {
     const PlanHeader &h = *pv.h;
     const P base = base_pose_of(h, qrow);
-    if (h.fz_arec > 0) put_pose(rec, stride, 0, base); // Jacobian with a moving base: re-read for the base columns
+    if (h.fz_arec > 0) put_base_fused(h, rec, base); // Jacobian with a moving base: re-read for the base columns
     const P e = walk<false>(pv, qrow, rec, rec, stride, 0, h.fz_arec, h.fz_prec, h.fz_frame, base, NoLinks());
     BaseComputed bs;
     bs.rec = rec;
     bs.stride = stride;
+    bs.h = &h;
     typename OutFactory::Sink out = make_out.make();
     emit_link(pv, e, 0, rec, stride, h.fz_arec, h.fz_prec, bs, out);
   }

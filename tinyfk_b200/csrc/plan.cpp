@@ -272,7 +272,8 @@ std::vector<unsigned char> build_plan(const KinematicModel &model, const PlanKey
   h.off_lrec = h.off_frame + 7 * b.frames_max;
   h.rec_size = (h.off_lrec + h.lrec_size * n_lrec + 1) & ~1;
   // fused single-link kernel: the link pose and the base context stay in registers
-  h.fz_arec = (jac && key.base_type != BASE_FIXED) ? 7 : 0; // base pose, re-read for the base columns
+  // base pose, re-read for the base columns: 7 reals, or the 4 that a PLANER pose has (x, y, sin, cos of yaw / 2)
+  h.fz_arec = (jac && key.base_type != BASE_FIXED) ? (key.base_type == BASE_PLANER ? 4 : 7) : 0;
   h.fz_prec = h.fz_arec + 3 * n_arec;
   h.fz_frame = h.fz_prec + 3 * n_prec;
   h.fz_size = (h.fz_frame + 7 * b.frames_max + 1) & ~1;
