@@ -24,6 +24,9 @@ CASES = [  # cfg, links kept (None = all), rot override, base override, precisio
     ("cfg4", 3, 2, 1, 1, 2, 148 * 5 * 32 + 32 * 9 + 7),  # FP32: 32-configuration tiles, more than one wave
     ("cfg5", 7, None, None, 0, 0, 130),              # RPY + FLOATING, generic, records in the L2 scratch
     ("cfg5", 7, None, None, 1, 2, 130),
+    ("cfg5", None, None, None, 0, 0, 128 + 67),      # 50 links: joint records staged per warp (generic, strict)
+    ("cfg5", None, None, None, 2, 2, 128 + 67),      # the same through the specialised FP64-fast kernel
+    ("cfg5", 40, 2, 1, 1, 2, 100),                   # FP32, 40 links, XYZW, PLANER: records resident, link-record prefetch
 ]
 
 
