@@ -10,8 +10,13 @@
  * arguments, so this header provides ONE implementation used by
  *   - the sm_100a kernels (nvcc, strict translation unit built with -fmad=false), and
  *   - the host model code and the "strict" oracle (gcc, -ffp-contract=off).
- * It uses only IEEE-754 binary64  + - * / sqrt, comparisons and integer bit moves, so the two
- * sides round identically.
+ * It uses only IEEE-754 binary64  + - * / sqrt and fusedMultiplyAdd (TFK_FMA: one correctly rounded
+ * operation on both sides -- `__fma_rn` on the device, `fma()` on the host, which glibc evaluates exactly
+ * with or without FMA hardware), comparisons and integer bit moves, so the two sides round identically.
+ * The explicit fused operations are part of the DEFINITION of these functions (they do not depend on
+ * -fmad / -ffp-contract): every Horner step and every "product minus correction" of the kernels is one
+ * of them, which halves the FP64 instruction count of the polynomials on the GPU (DESIGN.md section 3,
+ * "libm with explicit fused operations") and does not hurt accuracy.
  *
  * Algorithms: classic table-free ones (Cody-Waite three-stage pi/2 reduction; odd / even
  * polynomial kernels on [-pi/4, pi/4]; rational kernel for asin with the sqrt identity above 0.5;
@@ -58,6 +63,13 @@ typedef unsigned long long uint64_t;
 
 #include "fkmath_consts.inc"
 
+/* a*b + c with ONE rounding, identical on host and device */
+#if defined(__CUDA_ARCH__)
+#define TFK_FMA(a, b, c) __fma_rn((a), (b), (c))
+#else
+#define TFK_FMA(a, b, c) __builtin_fma((a), (b), (c))
+#endif
+
 TFK_HD int32_t tfk_hi32(double x) {
 #if defined(__CUDA_ARCH__)
   return __double2hiint(x);
@@ -86,8 +98,9 @@ TFK_HD double tfk_ksin(double x, double y) {
   if (fabs(x) < 7.450580596923828125e-9) return x; /* 2^-27 */
   double z = x * x;
   double v = z * x;
-  double r = TFK_S2 + z * (TFK_S3 + z * (TFK_S4 + z * (TFK_S5 + z * TFK_S6)));
-  return x - ((z * (0.5 * y - v * r) - y) - v * TFK_S1);
+  double r = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_S6, TFK_S5), TFK_S4), TFK_S3), TFK_S2);
+  /* x - ((z*(y/2 - v*r) - y) - v*S1) */
+  return x - TFK_FMA(-v, TFK_S1, TFK_FMA(z, TFK_FMA(-v, r, 0.5 * y), -y));
 }
 
 /* cos on [-pi/4, pi/4] */
@@ -95,13 +108,14 @@ TFK_HD double tfk_kcos(double x, double y) {
   double ax = fabs(x);
   if (ax < 7.450580596923828125e-9) return 1.0;
   double z = x * x;
-  double r = z * (TFK_C1 + z * (TFK_C2 + z * (TFK_C3 + z * (TFK_C4 + z * (TFK_C5 + z * TFK_C6)))));
-  if (ax < 0.3) return 1.0 - (0.5 * z - (z * r - x * y));
+  double r = z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_C6, TFK_C5), TFK_C4), TFK_C3), TFK_C2), TFK_C1);
+  double e = TFK_FMA(z, r, -(x * y)); /* z*r - x*y */
+  if (ax < 0.3) return 1.0 - (0.5 * z - e);
   /* 1 - z/2 would lose a bit here: peel off qx ~ |x|/4 so that (1 - qx) is exact */
   double qx = (ax > 0.78125) ? 0.28125 : tfk_from_hi32((tfk_hi32(ax)) - 0x00200000);
-  double hz = 0.5 * z - qx;
+  double hz = TFK_FMA(0.5, z, -qx);
   double a = 1.0 - qx;
-  return a - (hz - (z * r - x * y));
+  return a - (hz - e);
 }
 
 /* x = n*(pi/2) + (y0 + y1), |y0 + y1| <= pi/4.  Precondition: |x| > pi/4, finite. */
@@ -133,9 +147,9 @@ TFK_HD int tfk_rem_pio2(double x, double *y0, double *y1) {
     a0 = t;
     a1 = 0.0;
   } else {
-    n = (int)(t * TFK_INVPIO2 + 0.5);
+    n = (int)TFK_FMA(t, TFK_INVPIO2, 0.5);
     double fn = (double)n;
-    double r = t - fn * TFK_PIO2_1;
+    double r = TFK_FMA(-fn, TFK_PIO2_1, t); /* the product is exact (33-bit piece) */
     double w = fn * TFK_PIO2_1T;
     a0 = r - w;
     int j = (tfk_hi32(t) >> 20) & 0x7ff;
@@ -243,8 +257,8 @@ TFK_HD_CALL void tfk_sincos(double x, double *s, double *c) {
 }
 
 TFK_HD double tfk_asin_pq(double z, double *q) {
-  *q = 1.0 + z * (TFK_AQ1 + z * (TFK_AQ2 + z * (TFK_AQ3 + z * TFK_AQ4)));
-  return z * (TFK_AP0 + z * (TFK_AP1 + z * (TFK_AP2 + z * (TFK_AP3 + z * (TFK_AP4 + z * TFK_AP5)))));
+  *q = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_AQ4, TFK_AQ3), TFK_AQ2), TFK_AQ1), 1.0);
+  return z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_AP5, TFK_AP4), TFK_AP3), TFK_AP2), TFK_AP1), TFK_AP0);
 }
 
 TFK_HD_CALL double tfk_asin(double x) {
@@ -257,7 +271,7 @@ TFK_HD_CALL double tfk_asin(double x) {
   if (ax < 0.5) {
     if (ax < 7.450580596923828125e-9) return x;
     p = tfk_asin_pq(x * x, &q);
-    return x + x * (p / q);
+    return TFK_FMA(x, p / q, x);
   }
   double w = 1.0 - ax;
   double t = w * 0.5;
@@ -265,14 +279,14 @@ TFK_HD_CALL double tfk_asin(double x) {
   double s = sqrt(t);
   if (ax >= 0.975) {
     w = p / q;
-    t = TFK_PIO2_HI - (2.0 * (s + s * w) - TFK_PIO2_LO);
+    t = TFK_PIO2_HI - TFK_FMA(2.0, TFK_FMA(s, w, s), -TFK_PIO2_LO);
   } else {
     /* s = w + c with w the top half of s: keeps pi/4 - 2w exact */
     w = tfk_from_hi32(tfk_hi32(s));
-    double c = (t - w * w) / (s + w);
+    double c = TFK_FMA(-w, w, t) / (s + w);
     double r = p / q;
-    p = 2.0 * s * r - (TFK_PIO2_LO - 2.0 * c);
-    q = TFK_PIO4_HI - 2.0 * w;
+    p = TFK_FMA(2.0 * s, r, -TFK_FMA(-2.0, c, TFK_PIO2_LO));
+    q = TFK_FMA(-2.0, w, TFK_PIO4_HI);
     t = TFK_PIO4_HI - (p - q);
   }
   return (x > 0.0) ? t : -t;
@@ -292,7 +306,7 @@ TFK_HD double tfk_atan(double x) {
     t = x;
   } else if (ax < 0.6875) {
     id = 0;
-    t = (2.0 * ax - 1.0) / (2.0 + ax);
+    t = TFK_FMA(2.0, ax, -1.0) / (ax + 2.0);
     hi = TFK_ATANHI0;
     lo = TFK_ATANLO0;
   } else if (ax < 1.1875) {
@@ -302,7 +316,7 @@ TFK_HD double tfk_atan(double x) {
     lo = TFK_ATANLO1;
   } else if (ax < 2.4375) {
     id = 2;
-    t = (ax - 1.5) / (1.0 + 1.5 * ax);
+    t = (ax - 1.5) / TFK_FMA(1.5, ax, 1.0);
     hi = TFK_ATANHI2;
     lo = TFK_ATANLO2;
   } else {
@@ -312,17 +326,20 @@ TFK_HD double tfk_atan(double x) {
     lo = TFK_ATANLO3;
   }
   double z = t * t;
-  double s =
-      z * (TFK_AT0 +
-           z * (TFK_AT1 +
-                z * (TFK_AT2 +
-                     z * (TFK_AT3 +
-                          z * (TFK_AT4 +
-                               z * (TFK_AT5 +
-                                    z * (TFK_AT6 +
-                                         z * (TFK_AT7 + z * (TFK_AT8 + z * (TFK_AT9 + z * TFK_AT10))))))))));
+  double s = TFK_AT10;
+  s = TFK_FMA(z, s, TFK_AT9);
+  s = TFK_FMA(z, s, TFK_AT8);
+  s = TFK_FMA(z, s, TFK_AT7);
+  s = TFK_FMA(z, s, TFK_AT6);
+  s = TFK_FMA(z, s, TFK_AT5);
+  s = TFK_FMA(z, s, TFK_AT4);
+  s = TFK_FMA(z, s, TFK_AT3);
+  s = TFK_FMA(z, s, TFK_AT2);
+  s = TFK_FMA(z, s, TFK_AT1);
+  s = TFK_FMA(z, s, TFK_AT0);
+  s = z * s;
   if (id < 0) return t - t * s;
-  double r = hi - ((t * s - lo) - t);
+  double r = hi - (TFK_FMA(t, s, -lo) - t);
   return (x < 0.0) ? -r : r;
 }
 

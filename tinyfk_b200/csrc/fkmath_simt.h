@@ -89,9 +89,9 @@ TFK_HD uint64_t tfk_abs_bits(double x) {
 TFK_HD double tfk_ksin_simt(double x, double y) {
   double z = x * x;
   double v = z * x;
-  double r = TFK_KC(s2, TFK_S2) +
-             z * (TFK_KC(s3, TFK_S3) + z * (TFK_KC(s4, TFK_S4) + z * (TFK_KC(s5, TFK_S5) + z * TFK_KC(s6, TFK_S6))));
-  double p = x - ((z * (0.5 * y - v * r) - y) - v * TFK_KC(s1, TFK_S1));
+  double r = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(s6, TFK_S6), TFK_KC(s5, TFK_S5)), TFK_KC(s4, TFK_S4)), TFK_KC(s3, TFK_S3)),
+                     TFK_KC(s2, TFK_S2));
+  double p = x - TFK_FMA(-v, TFK_KC(s1, TFK_S1), TFK_FMA(z, TFK_FMA(-v, r, 0.5 * y), -y));
   /* |x| < 2^-27 <=> high word (sign cleared) < 0x3e400000 (the threshold's low word is zero) */
   return ((tfk_hi32(x) & 0x7fffffff) < 0x3e400000) ? x : p;
 }
@@ -99,19 +99,20 @@ TFK_HD double tfk_ksin_simt(double x, double y) {
 TFK_HD double tfk_kcos_simt(double x, double y) {
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
   double z = x * x;
-  double r = z * (TFK_KC(c1, TFK_C1) +
-                  z * (TFK_KC(c2, TFK_C2) +
-                       z * (TFK_KC(c3, TFK_C3) + z * (TFK_KC(c4, TFK_C4) + z * (TFK_KC(c5, TFK_C5) + z * TFK_KC(c6, TFK_C6))))));
-  /* ax < 0.3: qx = 0 gives hz = 0.5*z - 0 = 0.5*z and a = 1 - 0 = 1, i.e. fkmath.h's first form.
+  double r = z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(c6, TFK_C6), TFK_KC(c5, TFK_C5)), TFK_KC(c4, TFK_C4)), TFK_KC(c3, TFK_C3)),
+                                 TFK_KC(c2, TFK_C2)),
+                         TFK_KC(c1, TFK_C1));
+  /* ax < 0.3: qx = 0 gives hz = fma(0.5, z, -0) = 0.5*z and a = 1 - 0 = 1, i.e. fkmath.h's first form.
      (0.3 has a non-zero low word: keep the FP64 compare.)  0.78125 = 0x3fe90000_00000000. */
   const uint64_t ux = tfk_abs_bits(x);
   double qx = tfk_from_hi32(hx - 0x00200000);
   qx = (ux > 0x3fe9000000000000ull) ? 0.28125 : qx; /* ax > 0.78125 */
   qx = (ux < 0x3fd3333333333333ull) ? 0.0 : qx;     /* ax < 0.3 = 0x3fd33333_33333333 */
-  double hz = 0.5 * z - qx;
+  double hz = TFK_FMA(0.5, z, -qx);
   double a = 1.0 - qx;
-  double p = a - (hz - (z * r - x * y));
-  return (hx < 0x3e400000) ? 1.0 : p;
+  /* fkmath.h returns 1.0 below 2^-27: there qx = 0 and |0.5*z - (z*r - x*y)| < 2^-55, a quarter of the spacing below 1.0, so
+     the expression itself rounds to 1.0 -- no select needed */
+  return a - (hz - TFK_FMA(z, r, -(x * y)));
 }
 
 typedef struct {
@@ -129,9 +130,9 @@ TFK_HD TfkSinCos tfk_sincos_simt(double x) {
   const double t = fabs(x);
   const int small = tfk_abs_bits(x) <= 0x3fe921fb54442d18ull; /* |x| <= TFK_PIO4_HI */
   /* first reduction stage for every lane (harmless when small) */
-  int n = (int)(t * TFK_KC(invpio2, TFK_INVPIO2) + 0.5);
+  int n = (int)TFK_FMA(t, TFK_KC(invpio2, TFK_INVPIO2), 0.5);
   const double fn = (double)n;
-  double r = t - fn * TFK_KC(pio2_1, TFK_PIO2_1);
+  double r = TFK_FMA(-fn, TFK_KC(pio2_1, TFK_PIO2_1), t);
   double w = fn * TFK_KC(pio2_1t, TFK_PIO2_1T);
   double a0 = r - w;
   if (!small) {
@@ -194,9 +195,9 @@ TFK_HD TfkSinCos2 tfk_sincos2_simt(double xa, double xb) {
   }
   const double ta = fabs(xa), tb = fabs(xb);
   const int smalla = tfk_abs_bits(xa) <= 0x3fe921fb54442d18ull, smallb = tfk_abs_bits(xb) <= 0x3fe921fb54442d18ull;
-  int na = (int)(ta * TFK_KC(invpio2, TFK_INVPIO2) + 0.5), nb = (int)(tb * TFK_KC(invpio2, TFK_INVPIO2) + 0.5);
+  int na = (int)TFK_FMA(ta, TFK_KC(invpio2, TFK_INVPIO2), 0.5), nb = (int)TFK_FMA(tb, TFK_KC(invpio2, TFK_INVPIO2), 0.5);
   const double fna = (double)na, fnb = (double)nb;
-  const double ra = ta - fna * TFK_KC(pio2_1, TFK_PIO2_1), rb = tb - fnb * TFK_KC(pio2_1, TFK_PIO2_1);
+  const double ra = TFK_FMA(-fna, TFK_KC(pio2_1, TFK_PIO2_1), ta), rb = TFK_FMA(-fnb, TFK_KC(pio2_1, TFK_PIO2_1), tb);
   const double wa = fna * TFK_KC(pio2_1t, TFK_PIO2_1T), wb = fnb * TFK_KC(pio2_1t, TFK_PIO2_1T);
   double a0a = ra - wa, a0b = rb - wb;
   {
@@ -236,10 +237,10 @@ TFK_HD TfkSinCos2 tfk_sincos2_simt(double xa, double xb) {
 }
 
 TFK_HD double tfk_asin_pq_simt(double z, double *q) {
-  *q = 1.0 + z * (TFK_KC(aq1, TFK_AQ1) + z * (TFK_KC(aq2, TFK_AQ2) + z * (TFK_KC(aq3, TFK_AQ3) + z * TFK_KC(aq4, TFK_AQ4))));
-  return z * (TFK_KC(ap0, TFK_AP0) +
-              z * (TFK_KC(ap1, TFK_AP1) +
-                   z * (TFK_KC(ap2, TFK_AP2) + z * (TFK_KC(ap3, TFK_AP3) + z * (TFK_KC(ap4, TFK_AP4) + z * TFK_KC(ap5, TFK_AP5))))));
+  *q = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(aq4, TFK_AQ4), TFK_KC(aq3, TFK_AQ3)), TFK_KC(aq2, TFK_AQ2)), TFK_KC(aq1, TFK_AQ1)), 1.0);
+  return z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(ap5, TFK_AP5), TFK_KC(ap4, TFK_AP4)), TFK_KC(ap3, TFK_AP3)), TFK_KC(ap2, TFK_AP2)),
+                                TFK_KC(ap1, TFK_AP1)),
+                     TFK_KC(ap0, TFK_AP0));
 }
 
 /* bit-identical to tfk_asin (fkmath.h): one rational kernel + one division for both ranges */
@@ -253,16 +254,16 @@ TFK_HD double tfk_asin_simt(double x) {
   double q;
   const double p = tfk_asin_pq_simt(big ? t : x * x, &q);
   const double rr = p / q;
-  if (!big) return x + x * rr;
+  if (!big) return TFK_FMA(x, rr, x);
   const double s = sqrt(t);
   double res;
   if (tfk_abs_bits(x) >= 0x3fef333333333333ull) { /* ax >= 0.975 */
-    res = TFK_PIO2_HI - (2.0 * (s + s * rr) - TFK_PIO2_LO);
+    res = TFK_PIO2_HI - TFK_FMA(2.0, TFK_FMA(s, rr, s), -TFK_PIO2_LO);
   } else {
     const double w = tfk_from_hi32(tfk_hi32(s));
-    const double c = (t - w * w) / (s + w);
-    const double pp = 2.0 * s * rr - (TFK_PIO2_LO - 2.0 * c);
-    const double qq = TFK_PIO4_HI - 2.0 * w;
+    const double c = TFK_FMA(-w, w, t) / (s + w);
+    const double pp = TFK_FMA(2.0 * s, rr, -TFK_FMA(-2.0, c, TFK_PIO2_LO));
+    const double qq = TFK_FMA(-2.0, w, TFK_PIO4_HI);
     res = TFK_PIO4_HI - (pp - qq);
   }
   return tfk_xor_sign(res, tfk_hi32(x)); /* x > 0 ? res : -res (x is neither 0 nor NaN here) */
@@ -272,11 +273,12 @@ TFK_HD double tfk_asin_simt(double x) {
    interval id from the high word (all four thresholds have a zero low word), its six constants from a
    table, ONE division:  t = (na*ax + nb) / (da*ax + db)
      id -1: (1*ax + 0) / (0*ax + 1) = ax / 1 = ax            fkmath.h: t = x
-     id  0: (2*ax - 1) / (1*ax + 2)                          (2.0*ax - 1.0) / (2.0 + ax)
+     id  0: (2*ax - 1) / (1*ax + 2)                          fma(2.0, ax, -1.0) / (ax + 2.0)
      id  1: (1*ax - 1) / (1*ax + 1)                          (ax - 1.0) / (ax + 1.0)
-     id  2: (1*ax - 1.5) / (1.5*ax + 1)                      (ax - 1.5) / (1.0 + 1.5*ax)
+     id  2: (1*ax - 1.5) / (1.5*ax + 1)                      (ax - 1.5) / fma(1.5, ax, 1.0)
      id  3: (0*ax - 1) / (1*ax + 0) = -1 / ax                -1.0 / ax
-   and hi - ((t*s - lo) - t) with hi = lo = 0 for id -1 equals -(t*s - t) = t - t*s. */
+   (numerator and denominator are ONE fused operation each: exact products with 0, 1 and 2 make them equal to the
+   plain forms) and hi - (fma(t, s, -lo) - t) with hi = lo = 0 for id -1 equals -(t*s - t) = t - t*s. */
 TFK_HD double tfk_atan_pos_simt(double ax) {
   const int32_t hx = tfk_hi32(ax);
   const int id = (hx >= 0x3fdc0000) + (hx >= 0x3fe60000) + (hx >= 0x3ff30000) + (hx >= 0x40038000);
@@ -291,21 +293,21 @@ TFK_HD double tfk_atan_pos_simt(double ax) {
                                    {0.0, -1.0, 1.0, 0.0, TFK_ATANHI3, TFK_ATANLO3}};
   const double na = tab[id][0], nb = tab[id][1], da = tab[id][2], db = tab[id][3], hi = tab[id][4], lo = tab[id][5];
 #endif
-  const double t = (na * ax + nb) / (da * ax + db);
+  const double t = TFK_FMA(na, ax, nb) / TFK_FMA(da, ax, db);
   const double z = t * t;
   double s = TFK_KC(at[10], TFK_AT10);
-  s = TFK_KC(at[9], TFK_AT9) + z * s;
-  s = TFK_KC(at[8], TFK_AT8) + z * s;
-  s = TFK_KC(at[7], TFK_AT7) + z * s;
-  s = TFK_KC(at[6], TFK_AT6) + z * s;
-  s = TFK_KC(at[5], TFK_AT5) + z * s;
-  s = TFK_KC(at[4], TFK_AT4) + z * s;
-  s = TFK_KC(at[3], TFK_AT3) + z * s;
-  s = TFK_KC(at[2], TFK_AT2) + z * s;
-  s = TFK_KC(at[1], TFK_AT1) + z * s;
-  s = TFK_KC(at[0], TFK_AT0) + z * s;
+  s = TFK_FMA(z, s, TFK_KC(at[9], TFK_AT9));
+  s = TFK_FMA(z, s, TFK_KC(at[8], TFK_AT8));
+  s = TFK_FMA(z, s, TFK_KC(at[7], TFK_AT7));
+  s = TFK_FMA(z, s, TFK_KC(at[6], TFK_AT6));
+  s = TFK_FMA(z, s, TFK_KC(at[5], TFK_AT5));
+  s = TFK_FMA(z, s, TFK_KC(at[4], TFK_AT4));
+  s = TFK_FMA(z, s, TFK_KC(at[3], TFK_AT3));
+  s = TFK_FMA(z, s, TFK_KC(at[2], TFK_AT2));
+  s = TFK_FMA(z, s, TFK_KC(at[1], TFK_AT1));
+  s = TFK_FMA(z, s, TFK_KC(at[0], TFK_AT0));
   s = z * s;
-  return hi - ((t * s - lo) - t);
+  return hi - (TFK_FMA(t, s, -lo) - t);
 }
 
 /* bit-identical to tfk_atan2 (fkmath.h) */
