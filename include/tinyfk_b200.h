@@ -242,6 +242,11 @@ TFK_API int tfk_last_launch_variant(const tfk_model *m);
 /* call signatures the engine currently holds a plan for (bounded at 64, least recently used evicted; a signature whose
  * plan constants change with the stored model state is replaced in place).  Diagnostics / tests. */
 TFK_API int tfk_plan_cache_size(const tfk_model *m);
+/* 1 when tfk_model_create took the link / joint tables of this URDF text from the disk cache (TFK_CACHE_DIR, default
+ * ~/.cache/tinyfk_b200; TFK_TABLE_CACHE=0 disables it) instead of reading the XML, else 0.  The cache is SURVEY.md section
+ * 8(f) rank 4 ("URDF -> flat-table cache on disk"); it replaces the per-process work of src/tinyfk.cpp:16-114 +
+ * urdf_parser/src/model.cpp:91-270.  Diagnostics / tests. */
+TFK_API int tfk_model_tables_from_cache(const tfk_model *m);
 TFK_API const char *tfk_version(void);
 
 #ifdef __cplusplus

@@ -22,7 +22,7 @@ SYMBOLS = [
     "tfk_get_joint_effort_limits", "tfk_link_info", "tfk_is_relevant", "tfk_set_joint_angles", "tfk_get_joint_angles",
     "tfk_set_base_pose", "tfk_get_base_pose", "tfk_add_new_link", "tfk_solve_fk_host",
     "tfk_solve_fk_device", "tfk_solve_fk_device_noalloc", "tfk_inter_link_sqdists_host", "tfk_inter_link_sqdists_device", "tfk_solve_com_fk_host", "tfk_solve_com_fk_device", "tfk_total_inertia_matrix_host", "tfk_total_inertia_matrix_device", "tfk_specialize", "tfk_set_jit_mode", "tfk_get_jit_mode", "tfk_device_count", "tfk_host_alloc", "tfk_host_free",
-    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_plan_cache_size", "tfk_version",
+    "tfk_kernel_launch_count", "tfk_last_launch_info", "tfk_last_launch_variant", "tfk_plan_cache_size", "tfk_model_tables_from_cache", "tfk_version",
 ]
 
 _lib = None
@@ -85,6 +85,7 @@ def lib():
     L.tfk_kernel_launch_count.restype = _i64
     L.tfk_last_launch_info.argtypes = [_vp, _ip, _ip, _ip, _ip, _ip]
     L.tfk_plan_cache_size.argtypes = [_vp]
+    L.tfk_model_tables_from_cache.argtypes = [_vp]
     _lib = L
     return L
 
@@ -359,6 +360,9 @@ class Model:
 
     def plan_cache_size(self):
         return int(self._L.tfk_plan_cache_size(self._h))
+
+    def tables_from_cache(self):
+        return bool(self._L.tfk_model_tables_from_cache(self._h))
 
     def last_launch_info(self):
         v = [ctypes.c_int() for _ in range(5)]

@@ -389,6 +389,8 @@ int tfk_last_launch_variant(const tfk_model *m) { return m ? m->engine.last_laun
 
 int tfk_plan_cache_size(const tfk_model *m) { return m ? (int)m->engine.plan_cache_size() : -1; }
 
+int tfk_model_tables_from_cache(const tfk_model *m) { return m ? (m->engine.model.tables_from_cache() ? 1 : 0) : -1; }
+
 int tfk_specialize(tfk_model *m, const int *elink_ids, int n_link, const int *joint_ids, int n_joint, int rot_type,
                    int base_type, int with_jacobian, int precision, int flags, int64_t *info) {
   return guarded([&] {

@@ -63,6 +63,9 @@ typedef unsigned long long uint64_t;
 
 #include "fkmath_consts.inc"
 
+/* changes whenever a result of this header may change in any bit (keys the caches of values derived from it) */
+#define TFK_FKMATH_VERSION "fkmath 2 (explicit fma)"
+
 /* a*b + c with ONE rounding, identical on host and device */
 #if defined(__CUDA_ARCH__)
 #define TFK_FMA(a, b, c) __fma_rn((a), (b), (c))

@@ -2,8 +2,6 @@
 #include "jit.hpp"
 
 #include <dlfcn.h>
-#include <sys/stat.h>
-#include <unistd.h>
 
 #include <cstdint>
 #include <cstdio>
@@ -13,6 +11,7 @@
 #include <mutex>
 #include <stdexcept>
 
+#include "disk_cache.hpp"
 #include "fk_launch.h"
 #include "jit_headers.inc" // build/: k_jit_header_names / k_jit_header_sources / k_jit_n_headers
 
@@ -76,40 +75,7 @@ Nvrtc &nvrtc() {
   return n;
 }
 
-// ---- disk cache ------------------------------------------------------------------------------------------------
-uint64_t fnv1a(const std::string &s, uint64_t h = 1469598103934665603ull) {
-  for (unsigned char c : s) {
-    h ^= c;
-    h *= 1099511628211ull;
-  }
-  return h;
-}
-
-std::string cache_dir() {
-  if (const char *d = std::getenv("TFK_CACHE_DIR")) return *d ? std::string(d) : std::string();
-  if (const char *h = std::getenv("HOME")) return std::string(h) + "/.cache/tinyfk_b200";
-  return std::string();
-}
-
-void mkdirs(const std::string &p) {
-  for (size_t i = 1; i <= p.size(); ++i)
-    if (i == p.size() || p[i] == '/') mkdir(p.substr(0, i).c_str(), 0700);
-}
-
-// only a directory that belongs to this user and that nobody else can write to is trusted as a cubin cache
-bool cache_dir_trusted(const std::string &dir) {
-  struct stat st;
-  if (stat(dir.c_str(), &st) != 0) return false;
-  return S_ISDIR(st.st_mode) && st.st_uid == geteuid() && (st.st_mode & (S_IWGRP | S_IWOTH)) == 0;
-}
-
-// Cache file = header + cubin.  The header carries two independent 64-bit hashes of everything that determines the
-// cubin (source, options, embedded headers, NVRTC version), the payload length and a hash of the payload: a truncated,
-// foreign or colliding file is detected, deleted and recompiled instead of being handed to cudaLibraryLoadData.
-struct CacheHeader {
-  char magic[8]; // "TFKCUBN1"
-  uint64_t key_a, key_b, payload_bytes, payload_hash;
-};
+// ---- disk cache: disk_cache.hpp (header with 128 bits of key, payload length and payload hash; private directory) ------
 const char k_cache_magic[8] = {'T', 'F', 'K', 'C', 'U', 'B', 'N', '1'};
 
 std::vector<std::string> compile_options(const SpecOptions &o) {
@@ -181,36 +147,19 @@ std::vector<char> spec_compile(const std::string &plan_source, const SpecOptions
   const std::string src = spec_source(plan_source, o);
   const std::vector<std::string> opts = compile_options(o);
   // cache key: everything that determines the cubin (two FNV-1a streams with different offsets: 128 bits)
-  uint64_t key = fnv1a(src), key_b = fnv1a(src, 0x9e3779b97f4a7c15ull);
+  using diskcache::fnv1a;
+  uint64_t key = fnv1a(src), key_b = fnv1a(src, diskcache::k_second_offset);
   for (const std::string &x : opts) key = fnv1a(x, key), key_b = fnv1a(x, key_b);
   for (int i = 0; i < k_jit_n_headers; ++i) key = fnv1a(k_jit_header_sources[i], key), key_b = fnv1a(k_jit_header_sources[i], key_b);
   const std::string ver = "nvrtc " + std::to_string(n.major) + "." + std::to_string(n.minor) + " sm_100a";
   key = fnv1a(ver, key), key_b = fnv1a(ver, key_b);
   char name[64];
-  std::snprintf(name, sizeof name, "/spec_%016llx.cubin", (unsigned long long)key);
-  std::string dir = cache_dir();
-  if (!dir.empty()) {
-    mkdirs(dir);
-    if (!cache_dir_trusted(dir)) dir.clear(); // someone else's (or a writable-by-others) directory: no disk cache
-  }
-  if (!dir.empty()) {
-    std::ifstream f(dir + name, std::ios::binary);
-    if (f) {
-      std::vector<char> file((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
-      f.close();
-      CacheHeader hd;
-      bool ok = file.size() > sizeof hd + 64;
-      if (ok) {
-        std::memcpy(&hd, file.data(), sizeof hd);
-        ok = std::memcmp(hd.magic, k_cache_magic, 8) == 0 && hd.key_a == key && hd.key_b == key_b &&
-             hd.payload_bytes == file.size() - sizeof hd &&
-             hd.payload_hash == fnv1a(std::string(file.data() + sizeof hd, file.size() - sizeof hd));
-      }
-      if (ok) {
-        if (from_cache) *from_cache = true;
-        return std::vector<char>(file.begin() + sizeof hd, file.end());
-      }
-      std::remove((dir + name).c_str()); // corrupt, truncated, foreign or from an older layout: recompile
+  std::snprintf(name, sizeof name, "spec_%016llx.cubin", (unsigned long long)key);
+  {
+    std::vector<char> cached;
+    if (diskcache::read(name, k_cache_magic, key, key_b, cached, 65)) {
+      if (from_cache) *from_cache = true;
+      return cached;
     }
   }
   nvrtcProgram prog = nullptr;
@@ -233,22 +182,7 @@ std::vector<char> spec_compile(const std::string &plan_source, const SpecOptions
   if (rc == 0 && cs) rc = n.GetCUBIN(prog, cubin.data());
   n.DestroyProgram(&prog);
   if (rc != 0 || cs == 0) throw std::runtime_error("NVRTC produced no cubin");
-  if (!dir.empty()) { // best effort; written through a temporary so that concurrent processes never see a partial file
-    const std::string tmp = dir + name + "." + std::to_string((long)getpid()) + ".tmp";
-    std::ofstream f(tmp, std::ios::binary);
-    if (f) {
-      CacheHeader hd;
-      std::memcpy(hd.magic, k_cache_magic, 8);
-      hd.key_a = key;
-      hd.key_b = key_b;
-      hd.payload_bytes = cubin.size();
-      hd.payload_hash = fnv1a(std::string(cubin.data(), cubin.size()));
-      f.write(reinterpret_cast<const char *>(&hd), sizeof hd);
-      f.write(cubin.data(), (std::streamsize)cubin.size());
-      f.close();
-      if (!f || std::rename(tmp.c_str(), (dir + name).c_str()) != 0) std::remove(tmp.c_str());
-    }
-  }
+  diskcache::write(name, k_cache_magic, key, key_b, cubin.data(), cubin.size()); // best effort
   return cubin;
 }
 

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -11,6 +12,9 @@
 #include <sstream>
 #include <stdexcept>
 
+#include <gnu/libc-version.h>
+
+#include "disk_cache.hpp"
 #include "xml_lite.hpp"
 
 namespace tfk {
@@ -185,9 +189,185 @@ Pose64 KinematicModel::local_transform(const LinkRec &l, double angle) const {
 }
 
 // ---- construction (reference src/tinyfk.cpp:16-114) ---------------------------------------------
+// ---- flat tables on disk ("URDF -> flat-table cache on disk") -------------------
+// What the constructor derives from the XML -- link / joint records with their ids, origins as quaternions, the
+// "<name>_com" links, root and total mass -- is a pure function of (URDF text, host libm).  It is stored under the
+// library's disk cache (disk_cache.hpp: private directory, header with 128 bits of key, payload length and hash) and
+// a later process with the same text skips the XML reader and the table building.  The blob is still treated as
+// input: every count, index and string length is bounds-checked and the tree checks of the parsing path are repeated;
+// anything odd means "parse the XML".  TFK_TABLE_CACHE=0 turns it off.
+namespace {
+const char k_table_magic[8] = {'T', 'F', 'K', 'T', 'A', 'B', 'L', '1'};
+
+struct BlobWriter {
+  std::vector<char> b;
+  void raw(const void *p, size_t n) { b.insert(b.end(), static_cast<const char *>(p), static_cast<const char *>(p) + n); }
+  void i32(int32_t v) { raw(&v, sizeof v); }
+  void f64(double v) { raw(&v, sizeof v); }
+  void str(const std::string &v) {
+    i32((int32_t)v.size());
+    raw(v.data(), v.size());
+  }
+};
+struct BlobReader {
+  const char *p, *end;
+  bool ok = true;
+  bool raw(void *out, size_t n) {
+    if (!ok || (size_t)(end - p) < n) return ok = false;
+    std::memcpy(out, p, n);
+    p += n;
+    return true;
+  }
+  int32_t i32() {
+    int32_t v = 0;
+    raw(&v, sizeof v);
+    return v;
+  }
+  double f64() {
+    double v = 0;
+    raw(&v, sizeof v);
+    return v;
+  }
+  std::string str() {
+    const int32_t n = i32();
+    if (!ok || n < 0 || (size_t)(end - p) < (size_t)n) {
+      ok = false;
+      return std::string();
+    }
+    std::string v(p, (size_t)n);
+    p += n;
+    return v;
+  }
+};
+
+bool table_cache_enabled() {
+  const char *e = std::getenv("TFK_TABLE_CACHE");
+  return !(e && e[0] == '0');
+}
+} // namespace
+
+std::vector<char> KinematicModel::save_tables(size_t n_urdf_links) const {
+  BlobWriter w;
+  w.i32((int32_t)n_urdf_links);
+  w.i32((int32_t)links_.size());
+  w.i32((int32_t)joints_.size());
+  w.i32(root_);
+  w.f64(total_mass_);
+  for (const LinkRec &l : links_) {
+    w.str(l.name);
+    w.i32(l.parent);
+    w.i32(l.jtype);
+    w.i32(l.jid);
+    w.raw(&l.axis, sizeof l.axis);
+    w.raw(&l.origin, sizeof l.origin);
+    w.i32(l.has_inertial ? 1 : 0);
+    w.f64(l.mass);
+    w.raw(l.inertia, sizeof l.inertia);
+  }
+  for (const JointRec &j : joints_) {
+    w.str(j.name);
+    w.i32(j.type);
+    w.i32(j.child_link);
+    w.i32(j.has_limits ? 1 : 0);
+    w.f64(j.lower);
+    w.f64(j.upper);
+    w.f64(j.velocity);
+    w.f64(j.effort);
+  }
+  return w.b;
+}
+
+bool KinematicModel::load_tables(const std::vector<char> &blob) {
+  BlobReader r{blob.data(), blob.data() + blob.size()};
+  const int32_t n_urdf = r.i32(), n_links = r.i32(), n_joints = r.i32(), root = r.i32();
+  const double mass = r.f64();
+  if (!r.ok || n_urdf <= 0 || n_links < n_urdf || n_links > (1 << 20) || n_joints < 0 || n_joints > n_urdf ||
+      root < 0 || root >= n_urdf)
+    return false;
+  std::vector<LinkRec> links((size_t)n_links);
+  std::vector<JointRec> joints((size_t)n_joints);
+  for (LinkRec &l : links) {
+    l.name = r.str();
+    l.parent = r.i32();
+    l.jtype = r.i32();
+    l.jid = r.i32();
+    r.raw(&l.axis, sizeof l.axis);
+    r.raw(&l.origin, sizeof l.origin);
+    l.has_inertial = r.i32() != 0;
+    l.mass = r.f64();
+    r.raw(l.inertia, sizeof l.inertia);
+    if (!r.ok || l.parent < -1 || l.parent >= n_links || l.jid < -1 || l.jid >= n_joints || l.jtype < 0 || l.jtype > JT_FIXED)
+      return false;
+  }
+  for (JointRec &j : joints) {
+    j.name = r.str();
+    j.type = r.i32();
+    j.child_link = r.i32();
+    j.has_limits = r.i32() != 0;
+    j.lower = r.f64();
+    j.upper = r.f64();
+    j.velocity = r.f64();
+    j.effort = r.f64();
+    if (!r.ok || j.child_link < 0 || j.child_link >= n_urdf || links[(size_t)j.child_link].jid != (int)(&j - joints.data()))
+      return false;
+  }
+  if (r.p != r.end) return false;
+  // the same tree checks as the parsing path: one root, every link reaches it
+  for (int32_t i = 0; i < n_links; ++i) {
+    if ((links[(size_t)i].parent < 0) != (i == root)) return false;
+    int32_t hops = 0;
+    for (int l = i; l >= 0; l = links[(size_t)l].parent)
+      if (++hops > n_links) return false;
+  }
+  std::unordered_map<std::string, int> link_ids, joint_ids;
+  for (int32_t i = 0; i < n_links; ++i) {
+    if (!link_ids.emplace(links[(size_t)i].name, i).second) return false;
+    if (links[(size_t)i].parent >= 0) links[(size_t)links[(size_t)i].parent].children.push_back(i); // id order, as built
+  }
+  for (int32_t i = 0; i < n_joints; ++i)
+    if (!joint_ids.emplace(joints[(size_t)i].name, i).second) return false;
+  links_.swap(links);
+  joints_.swap(joints);
+  link_ids_.swap(link_ids);
+  joint_ids_.swap(joint_ids);
+  com_links_.clear();
+  for (int32_t i = n_urdf; i < n_links; ++i) com_links_.push_back(i);
+  root_ = root;
+  total_mass_ = mass;
+  joint_angles_.assign(joints_.size(), 0.0);
+  base_pose_.p.x = base_pose_.p.y = base_pose_.p.z = 0.0;
+  base_pose_.q = OpsP::qidentity();
+  return true;
+}
+
 KinematicModel::KinematicModel(const std::string &xml_text, HostLibm libm)
-    : root_(-1), total_mass_(0.0), libm_(libm), version_(1) {
+    : root_(-1), total_mass_(0.0), libm_(libm), version_(1), tables_from_cache_(false) {
   if (xml_text.empty()) throw std::runtime_error("xml string is empty"); // src/tinyfk.cpp:17-19
+  const bool cache = table_cache_enabled();
+  uint64_t key_a = 0, key_b = 0;
+  char file[64] = "";
+  if (cache) {
+    // the origin quaternions come from the host libm: its identity is part of the key
+    // ... and so is this translation unit's build (a rebuilt library never trusts tables written by another build)
+    const std::string what = std::string("tables v1 built " __DATE__ " " __TIME__ " libm ") +
+                             (libm == LIBM_PORTABLE ? std::string("portable " TFK_FKMATH_VERSION) : std::string("system glibc ") + gnu_get_libc_version());
+    key_a = diskcache::fnv1a(xml_text, diskcache::fnv1a(what));
+    key_b = diskcache::fnv1a(xml_text, diskcache::fnv1a(what, diskcache::k_second_offset));
+    std::snprintf(file, sizeof file, "tables_%016llx.tfkt", (unsigned long long)key_a);
+    std::vector<char> blob;
+    if (diskcache::read(file, k_table_magic, key_a, key_b, blob, 32) && load_tables(blob)) {
+      tables_from_cache_ = true;
+      return;
+    }
+  }
+  const size_t n_urdf_links = build_from_xml(xml_text);
+  if (cache) {
+    const std::vector<char> blob = save_tables(n_urdf_links);
+    diskcache::write(file, k_table_magic, key_a, key_b, blob.data(), blob.size()); // best effort
+  }
+}
+
+size_t KinematicModel::build_from_xml(const std::string &xml_text) {
   std::unique_ptr<xml::Element> doc = xml::parse(xml_text);
   if (doc->tag != "robot") throw std::invalid_argument("urdf: could not find the 'robot' element");
   if (!doc->attr("name")) throw std::invalid_argument("urdf: no name given for the robot");
@@ -302,6 +482,7 @@ KinematicModel::KinematicModel(const std::string &xml_text, HostLibm libm)
     for (int k = 0; k < 6; ++k) links_[id].inertia[k] = links_[i].inertia[k]; // the dummy link shares the parent's inertial
     com_links_.push_back(id);
   }
+  return n_urdf_links;
 }
 
 // ---- ids / names --------------------------------------------------------------------------------

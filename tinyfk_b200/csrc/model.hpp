@@ -100,6 +100,8 @@ public:
   HostLibm libm() const { return libm_; }
   // bumps whenever structure or stored state changes; plan caches key on it
   uint64_t version() const { return version_; }
+  // true when the constructor took the link / joint tables from the disk cache instead of reading the XML
+  bool tables_from_cache() const { return tables_from_cache_; }
 
   // host-libm dispatch used by everything that builds constants
   Quat<double> quat_from_rpy(double r, double p, double y) const;
@@ -109,6 +111,9 @@ public:
 
 private:
   int add_link_pose(const std::string &name, size_t parent_id, const Pose64 &pose);
+  size_t build_from_xml(const std::string &xml_text); // returns the number of URDF links (the "_com" links follow)
+  std::vector<char> save_tables(size_t n_urdf_links) const;
+  bool load_tables(const std::vector<char> &blob);
 
   std::vector<LinkRec> links_;
   std::vector<JointRec> joints_;
@@ -120,6 +125,7 @@ private:
   double total_mass_;
   HostLibm libm_;
   uint64_t version_;
+  bool tables_from_cache_;
 };
 
 std::string load_urdf(const std::string &path); // src/tinyfk.cpp:285-295
