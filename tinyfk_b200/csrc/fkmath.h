@@ -64,7 +64,7 @@ typedef unsigned long long uint64_t;
 #include "fkmath_consts.inc"
 
 /* changes whenever a result of this header may change in any bit (keys the caches of values derived from it) */
-#define TFK_FKMATH_VERSION "fkmath 2 (explicit fma)"
+#define TFK_FKMATH_VERSION "fkmath 3 (fma, one-division atan2, tail-free sincos)"
 
 /* a*b + c with ONE rounding, identical on host and device */
 #if defined(__CUDA_ARCH__)
@@ -96,167 +96,120 @@ TFK_HD double tfk_from_hi32(int32_t hi) { /* low word = 0 */
 
 TFK_HD int tfk_signbit(double x) { return (int)(((uint32_t)tfk_hi32(x)) >> 31); }
 
-/* sin on [-pi/4, pi/4]; (x + y) is the reduced argument, |y| << |x| */
-TFK_HD double tfk_ksin(double x, double y) {
-  if (fabs(x) < 7.450580596923828125e-9) return x; /* 2^-27 */
-  double z = x * x;
-  double v = z * x;
-  double r = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_S6, TFK_S5), TFK_S4), TFK_S3), TFK_S2);
-  /* x - ((z*(y/2 - v*r) - y) - v*S1) */
-  return x - TFK_FMA(-v, TFK_S1, TFK_FMA(z, TFK_FMA(-v, r, 0.5 * y), -y));
+/* ---- sin / cos ------------------------------------------------------------------------------------------------
+ * One reduction for every argument below 2^20 * pi/2 (no "small argument" case: n = 0 reduces x to itself), three
+ * fused steps x - n*(P1 + P1T + P1TT) with 33 + 53 + 53 bits of pi/2 (the first is exact, the second is the one rounding of
+ * the reduced argument, the third only acts right next to a multiple of pi/2, where the second leaves few bits), and
+ * plain Horner kernels on the reduced argument.  No tail word, no data-dependent branch: 26 FP64 operations for sin and
+ * cos together.  Accuracy (tests/test_fkmath.py, mpmath): below 1.5 ulp. */
+#define TFK_RND_MAGIC (6755399441055744.0) /* 1.5 * 2^52: adding it rounds to the nearest integer (ties to even) */
+
+/* sin(x), |x| <= pi/4 (+ rounding): x + x^3 * S(x^2) */
+TFK_HD double tfk_ksin(double x) {
+  const double z = x * x;
+  const double v = z * x;
+  const double r = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_S6, TFK_S5), TFK_S4), TFK_S3), TFK_S2);
+  return TFK_FMA(v, TFK_FMA(z, r, TFK_S1), x);
 }
 
-/* cos on [-pi/4, pi/4] */
-TFK_HD double tfk_kcos(double x, double y) {
-  double ax = fabs(x);
-  if (ax < 7.450580596923828125e-9) return 1.0;
-  double z = x * x;
-  double r = z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_C6, TFK_C5), TFK_C4), TFK_C3), TFK_C2), TFK_C1);
-  double e = TFK_FMA(z, r, -(x * y)); /* z*r - x*y */
-  if (ax < 0.3) return 1.0 - (0.5 * z - e);
-  /* 1 - z/2 would lose a bit here: peel off qx ~ |x|/4 so that (1 - qx) is exact */
-  double qx = (ax > 0.78125) ? 0.28125 : tfk_from_hi32((tfk_hi32(ax)) - 0x00200000);
-  double hz = TFK_FMA(0.5, z, -qx);
-  double a = 1.0 - qx;
-  return a - (hz - e);
+/* cos(x), |x| <= pi/4 (+ rounding): 1 + z * (-1/2 + z * C(z)) */
+TFK_HD double tfk_kcos(double x) {
+  const double z = x * x;
+  const double q =
+      TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_C6, TFK_C5), TFK_C4), TFK_C3), TFK_C2), TFK_C1), -0.5);
+  return TFK_FMA(z, q, 1.0);
 }
 
-/* x = n*(pi/2) + (y0 + y1), |y0 + y1| <= pi/4.  Precondition: |x| > pi/4, finite. */
-TFK_HD int tfk_rem_pio2(double x, double *y0, double *y1) {
-  double t = fabs(x);
-  double tl = 0.0; /* tail carried over from the big-argument pre-reduction */
-  if (t >= 1647099.0) { /* ~ 2^20 * pi/2: first strip a quadrant-neutral multiple of 4 quadrants */
-    if (t >= 274877906944.0) { /* 2^38: crude, documented */
-      double k = floor(t / (4.0 * TFK_PIO2_HI));
-      t = t - k * (4.0 * TFK_PIO2_HI);
-      if (t < 0.0) t = 0.0;
-    } else {
-      /* remove a multiple of 2^18 quadrants (<= 20 significant bits => products with the
-         33-bit pieces are exact); keep the rounding error of the second subtraction */
-      double fq = floor(t * TFK_INVPIO2 * (1.0 / 262144.0)) * 262144.0;
-      double t1 = t - fq * TFK_PIO2_1; /* exact */
-      double w = fq * TFK_PIO2_2;      /* exact */
-      t = t1 - w;
-      tl = ((t1 - t) - w) - fq * TFK_PIO2_2T;
-      if (t < 0.0) {
-        t = 0.0;
-        tl = 0.0;
-      }
-    }
-  }
-  int n = 0;
-  double a0, a1;
-  if (t <= TFK_PIO4_HI) {
-    a0 = t;
-    a1 = 0.0;
-  } else {
-    n = (int)TFK_FMA(t, TFK_INVPIO2, 0.5);
-    double fn = (double)n;
-    double r = TFK_FMA(-fn, TFK_PIO2_1, t); /* the product is exact (33-bit piece) */
-    double w = fn * TFK_PIO2_1T;
-    a0 = r - w;
-    int j = (tfk_hi32(t) >> 20) & 0x7ff;
-    int i = j - ((tfk_hi32(a0) >> 20) & 0x7ff);
-    if (i > 16) { /* cancellation: bring in the second piece */
-      double t2 = r;
-      w = fn * TFK_PIO2_2;
-      r = t2 - w;
-      w = fn * TFK_PIO2_2T - ((t2 - r) - w);
-      a0 = r - w;
-      i = j - ((tfk_hi32(a0) >> 20) & 0x7ff);
-      if (i > 49) { /* and the third */
-        t2 = r;
-        w = fn * TFK_PIO2_3;
-        r = t2 - w;
-        w = fn * TFK_PIO2_3T - ((t2 - r) - w);
-        a0 = r - w;
-      }
-    }
-    a1 = (r - a0) - w;
-  }
-  if (tl != 0.0) {
-    a1 = a1 + tl;
-    double h = a0 + a1;
-    a1 = (a0 - h) + a1;
-    a0 = h;
-  }
-  if (x < 0.0) {
-    *y0 = -a0;
-    *y1 = -a1;
-    return -n;
-  }
-  *y0 = a0;
-  *y1 = a1;
-  return n;
+/* t = n*(pi/2) + a0 for 0 <= t < 2^20 * pi/2; *n gets the quadrant count */
+TFK_HD double tfk_reduce(double t, int32_t *n) {
+  const double m = TFK_FMA(t, TFK_INVPIO2, TFK_RND_MAGIC);
+  const double fn = m - TFK_RND_MAGIC;
+#if defined(__CUDA_ARCH__)
+  *n = __double2loint(m);
+#else
+  uint64_t u;
+  memcpy(&u, &m, sizeof u);
+  *n = (int32_t)(uint32_t)u;
+#endif
+  const double r = TFK_FMA(-fn, TFK_PIO2_1, t); /* exact: 33-bit piece times an integer below 2^21 */
+  const double a = TFK_FMA(-fn, TFK_PIO2_1T, r);  /* the one rounding that matters */
+  return TFK_FMA(-fn, TFK_PIO2_1TT, a);           /* changes a only next to a multiple of pi/2, where a is nearly exact */
 }
 
-TFK_HD double tfk_sin(double x) {
-  if (fabs(x) <= TFK_PIO4_HI) return tfk_ksin(x, 0.0);
-  if (!(fabs(x) <= 1.7976931348623157e308)) return x - x; /* inf, nan */
-  double y0, y1;
-  int n = tfk_rem_pio2(x, &y0, &y1);
-  switch (n & 3) {
-  case 0:
-    return tfk_ksin(y0, y1);
-  case 1:
-    return tfk_kcos(y0, y1);
-  case 2:
-    return -tfk_ksin(y0, y1);
-  default:
-    return -tfk_kcos(y0, y1);
-  }
+/* (sin, cos) from the kernels' values on the reduced argument of |x|: quadrant n, sign of x (bit 31 of hx) */
+TFK_HD void tfk_sincos_place(double ks, double kc, int32_t n, int32_t hx, double *s, double *c) {
+  /* n&3: 0 (ks, kc)  1 (kc, -ks)  2 (-ks, -kc)  3 (-kc, ks);  sin is odd in x */
+  double ss = (n & 1) ? kc : ks;
+  double cc = (n & 1) ? ks : kc;
+  const int32_t ms = (int32_t)((uint32_t)n << 30) ^ hx;  /* (n & 2) xor sign(x) -> bit 31 */
+  const int32_t mc = (int32_t)((uint32_t)(n + 1) << 30); /* (n + 1) & 2 -> bit 31 */
+#if defined(__CUDA_ARCH__)
+  *s = __hiloint2double(__double2hiint(ss) ^ (ms & (int32_t)0x80000000), __double2loint(ss));
+  *c = __hiloint2double(__double2hiint(cc) ^ (mc & (int32_t)0x80000000), __double2loint(cc));
+#else
+  uint64_t u;
+  memcpy(&u, &ss, sizeof u);
+  u ^= ((uint64_t)((uint32_t)ms & 0x80000000u)) << 32;
+  memcpy(s, &u, sizeof u);
+  memcpy(&u, &cc, sizeof u);
+  u ^= ((uint64_t)((uint32_t)mc & 0x80000000u)) << 32;
+  memcpy(c, &u, sizeof u);
+#endif
 }
 
-TFK_HD double tfk_cos(double x) {
-  if (fabs(x) <= TFK_PIO4_HI) return tfk_kcos(x, 0.0);
-  if (!(fabs(x) <= 1.7976931348623157e308)) return x - x;
-  double y0, y1;
-  int n = tfk_rem_pio2(x, &y0, &y1);
-  switch (n & 3) {
-  case 0:
-    return tfk_kcos(y0, y1);
-  case 1:
-    return -tfk_ksin(y0, y1);
-  case 2:
-    return -tfk_kcos(y0, y1);
-  default:
-    return tfk_ksin(y0, y1);
-  }
+/* the whole evaluation for |x| < 2^20 * pi/2 (1647099.0): straight-line code */
+TFK_HD void tfk_sincos_core(double x, double *s, double *c) {
+  int32_t n;
+  const double a0 = tfk_reduce(fabs(x), &n);
+  tfk_sincos_place(tfk_ksin(a0), tfk_kcos(a0), n, tfk_hi32(x), s, c);
 }
 
-/* sin and cos of the same argument with one reduction; results are bit-identical to the two
-   separate calls (same kernels on the same reduced argument). */
+/* sin and cos of the same argument.  tfk_sin / tfk_cos are its two halves, so the reference's separate sin() and
+   cos() calls and a compiler-fused sincos() give the same bits. */
 TFK_HD_CALL void tfk_sincos(double x, double *s, double *c) {
-  if (fabs(x) <= TFK_PIO4_HI) {
-    *s = tfk_ksin(x, 0.0);
-    *c = tfk_kcos(x, 0.0);
+  double t = fabs(x);
+  if (TFK_LIKELY(t < 1647099.0)) { /* ~ 2^20 * pi/2 */
+    tfk_sincos_core(x, s, c);
     return;
   }
-  if (!(fabs(x) <= 1.7976931348623157e308)) {
+  if (!(t <= 1.7976931348623157e308)) { /* inf, nan */
     *s = *c = x - x;
     return;
   }
-  double y0, y1;
-  int n = tfk_rem_pio2(x, &y0, &y1);
-  double ks = tfk_ksin(y0, y1), kc = tfk_kcos(y0, y1);
-  switch (n & 3) {
-  case 0:
-    *s = ks;
-    *c = kc;
-    break;
-  case 1:
-    *s = kc;
-    *c = -ks;
-    break;
-  case 2:
-    *s = -ks;
-    *c = -kc;
-    break;
-  default:
-    *s = -kc;
-    *c = ks;
-    break;
+  /* big arguments: first strip a quadrant-neutral multiple of 4 quadrants, keep the rounding error as a tail */
+  double tl = 0.0;
+  if (t >= 274877906944.0) { /* 2^38: crude, documented */
+    double k = floor(t / (4.0 * TFK_PIO2_HI));
+    t = t - k * (4.0 * TFK_PIO2_HI);
+    if (t < 0.0) t = 0.0;
+  } else {
+    /* remove a multiple of 2^18 quadrants (<= 20 significant bits => products with the
+       33-bit pieces are exact); keep the rounding error of the second subtraction */
+    double fq = floor(t * TFK_INVPIO2 * (1.0 / 262144.0)) * 262144.0;
+    double t1 = t - fq * TFK_PIO2_1; /* exact */
+    double w = fq * TFK_PIO2_2;      /* exact */
+    t = t1 - w;
+    tl = ((t1 - t) - w) - fq * TFK_PIO2_2T;
+    if (t < 0.0) {
+      t = 0.0;
+      tl = 0.0;
+    }
   }
+  int32_t n;
+  const double a0 = tfk_reduce(t, &n) + tl;
+  tfk_sincos_place(tfk_ksin(a0), tfk_kcos(a0), n, tfk_hi32(x), s, c);
+}
+
+TFK_HD double tfk_sin(double x) {
+  double s, c;
+  tfk_sincos(x, &s, &c);
+  return s;
+}
+
+TFK_HD double tfk_cos(double x) {
+  double s, c;
+  tfk_sincos(x, &s, &c);
+  return c;
 }
 
 TFK_HD double tfk_asin_pq(double z, double *q) {
@@ -329,7 +282,8 @@ TFK_HD double tfk_atan(double x) {
     lo = TFK_ATANLO3;
   }
   double z = t * t;
-  double s = TFK_AT10;
+  double s = TFK_AT11;
+  s = TFK_FMA(z, s, TFK_AT10);
   s = TFK_FMA(z, s, TFK_AT9);
   s = TFK_FMA(z, s, TFK_AT8);
   s = TFK_FMA(z, s, TFK_AT7);
@@ -346,9 +300,68 @@ TFK_HD double tfk_atan(double x) {
   return (x < 0.0) ? -r : r;
 }
 
+/* ---- atan2 ----------------------------------------------------------------------------------------------------
+ * ONE division: with mx = max(|x|, |y|), mn = min(|x|, |y|) the angle of (mx, mn) is atan(mn / mx) in [0, pi/4];
+ * from mn / mx = 1/2 on it is pi/4 + atan((mn - mx) / (mn + mx)), so numerator and denominator are chosen BEFORE
+ * dividing and the quotient t lies in [-1/3, 1/2], inside the range of the atan polynomial (|t| <= 1/2); with the split
+ * at 1/2 the difference mn - mx is exact (Sterbenz), which keeps the error below 2 ulp where pi/4 + atan(t) is smallest.  Undoing the
+ * swap (pi/2 - .), the reflection for x < 0 (pi - .) and the pi/4 offset all add a multiple of pi/4 and possibly flip the
+ * sign of atan(t):  theta = k * pi/4 + sigma * atan(t), k in 0..4, evaluated as hi_k - ((sigma t * s - lo_k) - sigma t)
+ * (the form tfk_atan uses); the result takes the sign of y.  Straight-line code with selects.
+ * Preconditions (tfk_atan2 establishes them): x, y finite, max(|x|, |y|) in [2^-900, 2^1022). */
+
+TFK_HD double tfk_atan_poly(double z) { /* atan(t) = t - t * (z * A(z)), z = t^2; returns z * A(z) */
+  double s = TFK_AT11;
+  s = TFK_FMA(z, s, TFK_AT10);
+  s = TFK_FMA(z, s, TFK_AT9);
+  s = TFK_FMA(z, s, TFK_AT8);
+  s = TFK_FMA(z, s, TFK_AT7);
+  s = TFK_FMA(z, s, TFK_AT6);
+  s = TFK_FMA(z, s, TFK_AT5);
+  s = TFK_FMA(z, s, TFK_AT4);
+  s = TFK_FMA(z, s, TFK_AT3);
+  s = TFK_FMA(z, s, TFK_AT2);
+  s = TFK_FMA(z, s, TFK_AT1);
+  s = TFK_FMA(z, s, TFK_AT0);
+  return z * s;
+}
+
+#if !defined(TFK_ATAN2_TABLE)
+/* k * pi/4 as hi + lo, k = 0..4 (fkmath_simt.h replaces the lookup by a constant-bank table on the device) */
+#define TFK_ATAN2_TABLE(k, hi, lo)                                                                                    \
+  do {                                                                                                                \
+    const double tfk_hi_[5] = {0.0, TFK_PIO4_HI, TFK_PIO2_HI, TFK_3PIO4_HI, TFK_PI};                                  \
+    const double tfk_lo_[5] = {0.0, TFK_PIO4_LO, TFK_PIO2_LO, TFK_3PIO4_LO, TFK_PI_LO};                               \
+    (hi) = tfk_hi_[k];                                                                                                \
+    (lo) = tfk_lo_[k];                                                                                                \
+  } while (0)
+#endif
+
+#ifndef TFK_QUOT
+#define TFK_QUOT(a, b) ((a) / (b))
+#endif
+
+TFK_HD double tfk_atan2_core(double y, double x) {
+  const double ax = fabs(x), ay = fabs(y);
+  const int swap = ay > ax;
+  const double mx = swap ? ay : ax, mn = swap ? ax : ay;
+  const int big = mn >= 0.5 * mx;
+  const double num = big ? mn - mx : mn;
+  const double den = big ? mn + mx : mx;
+  const double t = TFK_QUOT(num, den);
+  const double s = tfk_atan_poly(t * t);
+  const int xneg = tfk_hi32(x) < 0;
+  const int flip = swap ^ xneg; /* sigma = -1 */
+  const int k = (swap ? 2 : (xneg ? 4 : 0)) + (flip ? -big : big);
+  double hi, lo;
+  TFK_ATAN2_TABLE(k, hi, lo);
+  const double tv = flip ? -t : t;
+  const double th = hi - (TFK_FMA(tv, s, -lo) - tv);
+  return (tfk_hi32(y) < 0) ? -th : th;
+}
+
 TFK_HD_CALL double tfk_atan2(double y, double x) {
   if (x != x || y != y) return x + y;
-  if (x == 1.0) return tfk_atan(y);
   int m = tfk_signbit(y) | (tfk_signbit(x) << 1);
   if (y == 0.0) {
     switch (m) {
@@ -389,26 +402,17 @@ TFK_HD_CALL double tfk_atan2(double y, double x) {
     }
   }
   if (ay > inf) return (m & 1) ? -TFK_PIO2_HI : TFK_PIO2_HI;
-  int k = ((tfk_hi32(ay) >> 20) & 0x7ff) - ((tfk_hi32(ax) >> 20) & 0x7ff);
-  double z;
-  if (k > 60) {
-    z = TFK_PIO2_HI + 0.5 * TFK_PI_LO;
-    m &= 1;
-  } else if ((m & 2) && k < -60) {
-    z = 0.0;
-  } else {
-    z = tfk_atan(fabs(y / x));
+  /* bring the larger magnitude into the core's range; powers of two, so the quotient does not change (a smaller
+     operand that leaves the normal range on the way belongs to a quotient far below one ulp of the result) */
+  const double mxv = (ay > ax) ? ay : ax;
+  if (mxv >= 4.49423283715579e307) { /* 2^1022 */
+    x *= 0.0625;
+    y *= 0.0625;
+  } else if (mxv < 1.1830521861667747e-271) { /* 2^-900 */
+    x *= 1.157920892373162e77; /* 2^256 */
+    y *= 1.157920892373162e77;
   }
-  switch (m) {
-  case 0:
-    return z;
-  case 1:
-    return -z;
-  case 2:
-    return TFK_PI - (z - TFK_PI_LO);
-  default:
-    return (z - TFK_PI_LO) - TFK_PI;
-  }
+  return tfk_atan2_core(y, x);
 }
 
 #endif /* TFK_FKMATH_H */
