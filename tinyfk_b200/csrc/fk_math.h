@@ -15,11 +15,6 @@
 #ifndef TFK_FK_MATH_H
 #define TFK_FK_MATH_H
 
-#if defined(TFK_FAST_PORTABLE_LIBM) && defined(__CUDACC__)
-// FP64 fast mode only (a translation unit that never holds strict code): quotients inside asin / atan / atan2 as one
-// correctly rounded reciprocal times the numerator
-#define TFK_QUOT(a, b) ((a) * __drcp_rn(b))
-#endif
 #include "fkmath.h"
 #include "fkmath_simt.h"
 
@@ -82,7 +77,7 @@ struct MathPortable {
   }
 #endif
   // two arguments at once (fkmath_simt.h: the two evaluations interleave; same bits as two sincos_ calls)
-#if defined(__CUDACC__)
+#if defined(__CUDACC__) // (inlined it costs registers: cfg2 strict 0.265 against 0.198 ms)
   static __host__ __device__ __noinline__ TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
 #else
   static inline TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
@@ -270,25 +265,6 @@ struct MathFast64 {
   enum { SPARE_REGS = 0 }; // see MathPortable (measured: no gain on cfg4 / cfg5)
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
-#if defined(TFK_FAST_PORTABLE_LIBM) && defined(__CUDA_ARCH__)
-  // fkmath_simt.h (explicit fused operations, coefficients as constant-bank operands, select-based control flow) with
-  // its quotients as reciprocal-multiplies (TFK_QUOT): fewer instructions than libdevice, which builds every polynomial
-  // coefficient from immediates
-  static __device__ __noinline__ TfkSinCos sincos_call_(double x) { return tfk_sincos_simt(x); }
-  static TFK_FN void sincos_(double x, double *s, double *c) {
-    const TfkSinCos r = sincos_call_(x);
-    *s = r.s;
-    *c = r.c;
-  }
-  static __device__ __noinline__ TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
-  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
-    const TfkSinCos2 r = sincos2_call_(xa, xb);
-    *sa = r.a.s, *ca = r.a.c, *sb = r.b.s, *cb = r.b.c;
-  }
-  static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
-  static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
-  static TFK_FN double atan2_rare_(double y, double x) { return tfk_atan2(y, x); }
-#else
   static TFK_FN void sincos_(double x, double *s, double *c) {
 #if defined(__CUDA_ARCH__)
     ::sincos(x, s, c);
@@ -304,7 +280,6 @@ struct MathFast64 {
   static TFK_FN double asin_(double x) { return ::asin(x); }
   static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
   static TFK_FN double atan2_rare_(double y, double x) { return ::atan2(y, x); }
-#endif
   static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
   struct Den {
     double b, y;

@@ -114,7 +114,11 @@ std::string spec_source(const std::string &plan_source, const SpecOptions &o) {
       i = j + 1;
     }
   } else {
-    s += "#define TFK_SPEC_INLINE 1\n#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
+    s += "#define TFK_SPEC_INLINE 1\n";
+    // sin/cos out of line and two joints per call: pays wherever the libm is libdevice's (FP32 cfg4 0.340 against 0.357 ms
+    // without, FP64-fast cfg3 0.212 against 0.219 ms).  The strict single-link kernels inline the portable sin/cos (26 FP64
+    // operations, fkmath.h) one joint at a time: cfg2 0.1987 -> 0.1961 ms, cfg3 0.267 -> 0.256 ms
+    if (!(o.kind == 0 && o.precision == PREC_F64_STRICT)) s += "#define TFK_SPEC_SINCOS_CALL 1\n#define TFK_SPEC_SINCOS_PAIR 1\n";
   }
   // several links, FP64 (strict and fast): one rolled copy of the walk, fk_core.h TFK_WALK_LOOP (FP64-fast cfg4: 0.873 ->
   // 0.811 ms with the walk rolled, cfg5 0.880 -> 0.872 ms; FP32 code is half the size and keeps the unrolled walk)
