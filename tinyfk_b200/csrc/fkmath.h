@@ -64,7 +64,7 @@ typedef unsigned long long uint64_t;
 #include "fkmath_consts.inc"
 
 /* changes whenever a result of this header may change in any bit (keys the caches of values derived from it) */
-#define TFK_FKMATH_VERSION "fkmath 3 (fma, one-division atan2, tail-free sincos)"
+#define TFK_FKMATH_VERSION "fkmath 4 (fma, one-division atan2, tail-free sincos, division-free asin)"
 
 /* a*b + c with ONE rounding, identical on host and device */
 #if defined(__CUDA_ARCH__)
@@ -212,9 +212,49 @@ TFK_HD double tfk_cos(double x) {
   return c;
 }
 
-TFK_HD double tfk_asin_pq(double z, double *q) {
-  *q = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_AQ4, TFK_AQ3), TFK_AQ2), TFK_AQ1), 1.0);
-  return z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_AP5, TFK_AP4), TFK_AP3), TFK_AP2), TFK_AP1), TFK_AP0);
+/* ---- asin -----------------------------------------------------------------------------------------------------
+ * No division.  |x| < 1/2: x + x * (z R(z)), z = x^2, R a 14-term polynomial.  Otherwise asin|x| = pi/2 - 2 asin(s),
+ * s = sqrt(t), t = (1 - |x|)/2 <= 1/4, with the SAME polynomial: pi/2 - 2 (s + c + s t R(t)), where c = e / (2 s) restores
+ * what the rounding of the square root lost (e = t - s^2 comes exactly out of one fused operation; c is below an ulp of
+ * s, so the reciprocal of s in single precision -- an IEEE operation on both sides -- is more than enough), and
+ * pi/2 - 2 s is taken as a rounded value v plus its exact error dv.  Accuracy: below 1 ulp (tests/test_fkmath.py). */
+TFK_HD double tfk_asin_poly(double z) { /* z * R(z) */
+  double r = TFK_AR13;
+  r = TFK_FMA(z, r, TFK_AR12);
+  r = TFK_FMA(z, r, TFK_AR11);
+  r = TFK_FMA(z, r, TFK_AR10);
+  r = TFK_FMA(z, r, TFK_AR9);
+  r = TFK_FMA(z, r, TFK_AR8);
+  r = TFK_FMA(z, r, TFK_AR7);
+  r = TFK_FMA(z, r, TFK_AR6);
+  r = TFK_FMA(z, r, TFK_AR5);
+  r = TFK_FMA(z, r, TFK_AR4);
+  r = TFK_FMA(z, r, TFK_AR3);
+  r = TFK_FMA(z, r, TFK_AR2);
+  r = TFK_FMA(z, r, TFK_AR1);
+  r = TFK_FMA(z, r, TFK_AR0);
+  return z * r;
+}
+
+/* 1 / (2 s) to single precision, identically on host and device (correctly rounded conversions and reciprocal) */
+TFK_HD double tfk_half_rcp_f32(double s) {
+#if defined(__CUDA_ARCH__)
+  return 0.5 * (double)__frcp_rn(__double2float_rn(s));
+#else
+  const float sf = (float)s;
+  const float rf = 1.0f / sf;
+  return 0.5 * (double)rf;
+#endif
+}
+
+/* asin of 1/2 <= ax < 1 (ax = |x|) */
+TFK_HD double tfk_asin_upper(double ax, double zr, double s, double t) { /* zr = t R(t), s = sqrt(t) */
+  const double e = TFK_FMA(-s, s, t);
+  const double c = e * tfk_half_rcp_f32(s);
+  const double u = TFK_FMA(s, zr, c);
+  const double v = TFK_FMA(-2.0, s, TFK_PIO2_HI);
+  const double dv = TFK_FMA(-2.0, s, TFK_PIO2_HI - v); /* exact */
+  return v + (TFK_FMA(-2.0, u, TFK_PIO2_LO) + dv);
 }
 
 TFK_HD_CALL double tfk_asin(double x) {
@@ -223,29 +263,13 @@ TFK_HD_CALL double tfk_asin(double x) {
     if (ax == 1.0) return x * TFK_PIO2_HI + x * TFK_PIO2_LO;
     return (x - x) / (x - x); /* |x| > 1 or nan */
   }
-  double p, q;
   if (ax < 0.5) {
-    if (ax < 7.450580596923828125e-9) return x;
-    p = tfk_asin_pq(x * x, &q);
-    return TFK_FMA(x, p / q, x);
+    if (ax < 7.450580596923828125e-9) return x; /* 2^-27 */
+    return TFK_FMA(x, tfk_asin_poly(x * x), x);
   }
-  double w = 1.0 - ax;
-  double t = w * 0.5;
-  p = tfk_asin_pq(t, &q);
-  double s = sqrt(t);
-  if (ax >= 0.975) {
-    w = p / q;
-    t = TFK_PIO2_HI - TFK_FMA(2.0, TFK_FMA(s, w, s), -TFK_PIO2_LO);
-  } else {
-    /* s = w + c with w the top half of s: keeps pi/4 - 2w exact */
-    w = tfk_from_hi32(tfk_hi32(s));
-    double c = TFK_FMA(-w, w, t) / (s + w);
-    double r = p / q;
-    p = TFK_FMA(2.0 * s, r, -TFK_FMA(-2.0, c, TFK_PIO2_LO));
-    q = TFK_FMA(-2.0, w, TFK_PIO4_HI);
-    t = TFK_PIO4_HI - (p - q);
-  }
-  return (x > 0.0) ? t : -t;
+  const double t = TFK_FMA(-0.5, ax, 0.5); /* exact */
+  const double r = tfk_asin_upper(ax, tfk_asin_poly(t), sqrt(t), t);
+  return (x > 0.0) ? r : -r;
 }
 
 TFK_HD double tfk_atan(double x) {
@@ -337,10 +361,6 @@ TFK_HD double tfk_atan_poly(double z) { /* atan(t) = t - t * (z * A(z)), z = t^2
   } while (0)
 #endif
 
-#ifndef TFK_QUOT
-#define TFK_QUOT(a, b) ((a) / (b))
-#endif
-
 TFK_HD double tfk_atan2_core(double y, double x) {
   const double ax = fabs(x), ay = fabs(y);
   const int swap = ay > ax;
@@ -348,7 +368,7 @@ TFK_HD double tfk_atan2_core(double y, double x) {
   const int big = mn >= 0.5 * mx;
   const double num = big ? mn - mx : mn;
   const double den = big ? mn + mx : mx;
-  const double t = TFK_QUOT(num, den);
+  const double t = num / den;
   const double s = tfk_atan_poly(t * t);
   const int xneg = tfk_hi32(x) < 0;
   const int flip = swap ^ xneg; /* sigma = -1 */

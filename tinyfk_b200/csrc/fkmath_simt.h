@@ -1,43 +1,31 @@
 /*
- * fkmath_simt.h -- the SAME functions as fkmath.h (tfk_sincos, tfk_asin, tfk_atan2), restructured for
- * a SIMT machine.  Every result is BIT-IDENTICAL to the fkmath.h function of the same name
+ * fkmath_simt.h -- the SAME functions as fkmath.h (tfk_sincos, tfk_asin, tfk_atan2) as the kernels call them.
+ * Every result is BIT-IDENTICAL to the fkmath.h function of the same name
  * (tests/test_fkmath.py::test_simt_variants_are_bit_identical compares them on millions of arguments;
  * the GPU parity tests compare the kernels, which use these, with the reference linked against
- * fkmath.h).  What changes is only the control flow:
+ * fkmath.h).  fkmath.h's evaluations are straight-line code already (one reduction for every sin/cos argument, one
+ * division per atan2, no division in asin); what differs here:
  *
- *   - data-dependent branches that split a warp (|x| <= pi/4 or not, the quadrant switch, the three
- *     cosine kernels, asin below/above 0.5, the five atan intervals) become selects around ONE copy
- *     of the arithmetic, so a warp executes the polynomial and the division once instead of once per
- *     taken path;
- *   - rare inputs (huge arguments, NaN/Inf, exact zeros, |y/x| beyond 2^60) are detected with integer
- *     tests on the exponent word and handed to the fkmath.h function itself;
- *   - FP64 compares against thresholds whose low word is zero are done on the high word (the FP64
- *     pipe is the bottleneck of the strict kernels; integer compares run on the ALU pipe);
- *   - on the device the polynomial coefficients come from constant memory (operands of the FP64
- *     instructions) instead of being rebuilt from immediates at every use.
+ *   - rare inputs (huge arguments, NaN/Inf, magnitudes outside atan2's working range, |x| >= 1 for asin) are detected
+ *     with integer tests on the exponent word and handed to the fkmath.h function itself;
+ *   - asin evaluates its polynomial once for both ranges (the argument is selected);
+ *   - sign changes are one XOR on the high word;
+ *   - on the device the polynomial coefficients and the k * pi/4 offsets come from constant memory (operands of the
+ *     FP64 instructions) instead of being rebuilt from immediates at every use.
  *
- * Why identical: each value is produced by the same sequence of IEEE operations on the same
- * operands; where two code paths of fkmath.h are merged the merged expression reduces to each of
- * them exactly (x - 0.0 = x, 1.0 - 0.0 = 1.0, x / 1.0 = x, 1.0 * x = x, 0.0 * x + c = c for finite x,
- * -(a - b) = b - a), as noted at each merge.
+ * Why identical: each value is produced by the same sequence of IEEE operations on the same operands.
  */
 #ifndef TFK_FKMATH_SIMT_H
 #define TFK_FKMATH_SIMT_H
 
 #include "fkmath.h"
 
-/* the quotients inside asin / atan / atan2.  Strict mode: the IEEE division (part of the functions' definition).  The FP64
-   fast mode (fk_math.h:MathFast64, 1e-12 contract) may define it as a reciprocal-multiply before including this header. */
-#ifndef TFK_QUOT
-#define TFK_QUOT(a, b) ((a) / (b))
-#endif
-
 #if defined(__CUDACC__)
 /* constant-bank copies of the coefficients (same literals, so same bits) */
 struct TfkKc {
   double s1, s2, s3, s4, s5, s6;
   double c1, c2, c3, c4, c5, c6;
-  double ap0, ap1, ap2, ap3, ap4, ap5, aq1, aq2, aq3, aq4;
+  double ar[14];
   double at[12];
   double invpio2, pio2_1, pio2_1t, pio2_1tt;
   double k_hi[5], k_lo[5]; /* k * pi/4 as hi + lo: the atan2 offsets */
@@ -45,7 +33,7 @@ struct TfkKc {
 static __constant__ TfkKc tfk_kc = {
     TFK_S1, TFK_S2, TFK_S3, TFK_S4, TFK_S5, TFK_S6,
     TFK_C1, TFK_C2, TFK_C3, TFK_C4, TFK_C5, TFK_C6,
-    TFK_AP0, TFK_AP1, TFK_AP2, TFK_AP3, TFK_AP4, TFK_AP5, TFK_AQ1, TFK_AQ2, TFK_AQ3, TFK_AQ4,
+    {TFK_AR0, TFK_AR1, TFK_AR2, TFK_AR3, TFK_AR4, TFK_AR5, TFK_AR6, TFK_AR7, TFK_AR8, TFK_AR9, TFK_AR10, TFK_AR11, TFK_AR12, TFK_AR13},
     {TFK_AT0, TFK_AT1, TFK_AT2, TFK_AT3, TFK_AT4, TFK_AT5, TFK_AT6, TFK_AT7, TFK_AT8, TFK_AT9, TFK_AT10, TFK_AT11},
     TFK_INVPIO2, TFK_PIO2_1, TFK_PIO2_1T, TFK_PIO2_1TT,
     {0.0, TFK_PIO4_HI, TFK_PIO2_HI, TFK_3PIO4_HI, TFK_PI},
@@ -157,36 +145,33 @@ TFK_HD TfkSinCos2 tfk_sincos2_simt(double xa, double xb) {
   return out;
 }
 
-TFK_HD double tfk_asin_pq_simt(double z, double *q) {
-  *q = TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(aq4, TFK_AQ4), TFK_KC(aq3, TFK_AQ3)), TFK_KC(aq2, TFK_AQ2)), TFK_KC(aq1, TFK_AQ1)), 1.0);
-  return z * TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_FMA(z, TFK_KC(ap5, TFK_AP5), TFK_KC(ap4, TFK_AP4)), TFK_KC(ap3, TFK_AP3)), TFK_KC(ap2, TFK_AP2)),
-                                TFK_KC(ap1, TFK_AP1)),
-                     TFK_KC(ap0, TFK_AP0));
-}
-
-/* bit-identical to tfk_asin (fkmath.h): one rational kernel + one division for both ranges */
+/* bit-identical to tfk_asin (fkmath.h): the same operations with the coefficients as constant-bank operands; one
+   evaluation of the polynomial serves both ranges (its argument is selected) */
 TFK_HD double tfk_asin_simt(double x) {
   const int32_t hx = tfk_hi32(x) & 0x7fffffff;
   if (TFK_UNLIKELY(hx >= 0x3ff00000)) return tfk_asin(x); /* |x| >= 1, nan: rare */
   if (TFK_UNLIKELY(hx < 0x3e400000)) return x; /* |x| < 2^-27 */
   const double ax = fabs(x);
   const int big = hx >= 0x3fe00000; /* |x| >= 0.5 */
-  const double t = (1.0 - ax) * 0.5;
-  double q;
-  const double p = tfk_asin_pq_simt(big ? t : x * x, &q);
-  const double rr = TFK_QUOT(p, q);
-  if (!big) return TFK_FMA(x, rr, x);
-  const double s = sqrt(t);
-  double res;
-  if (tfk_abs_bits(x) >= 0x3fef333333333333ull) { /* ax >= 0.975 */
-    res = TFK_PIO2_HI - TFK_FMA(2.0, TFK_FMA(s, rr, s), -TFK_PIO2_LO);
-  } else {
-    const double w = tfk_from_hi32(tfk_hi32(s));
-    const double c = TFK_QUOT(TFK_FMA(-w, w, t), s + w);
-    const double pp = TFK_FMA(2.0 * s, rr, -TFK_FMA(-2.0, c, TFK_PIO2_LO));
-    const double qq = TFK_FMA(-2.0, w, TFK_PIO4_HI);
-    res = TFK_PIO4_HI - (pp - qq);
-  }
+  const double t = TFK_FMA(-0.5, ax, 0.5);
+  const double z = big ? t : x * x;
+  double r = TFK_KC(ar[13], TFK_AR13);
+  r = TFK_FMA(z, r, TFK_KC(ar[12], TFK_AR12));
+  r = TFK_FMA(z, r, TFK_KC(ar[11], TFK_AR11));
+  r = TFK_FMA(z, r, TFK_KC(ar[10], TFK_AR10));
+  r = TFK_FMA(z, r, TFK_KC(ar[9], TFK_AR9));
+  r = TFK_FMA(z, r, TFK_KC(ar[8], TFK_AR8));
+  r = TFK_FMA(z, r, TFK_KC(ar[7], TFK_AR7));
+  r = TFK_FMA(z, r, TFK_KC(ar[6], TFK_AR6));
+  r = TFK_FMA(z, r, TFK_KC(ar[5], TFK_AR5));
+  r = TFK_FMA(z, r, TFK_KC(ar[4], TFK_AR4));
+  r = TFK_FMA(z, r, TFK_KC(ar[3], TFK_AR3));
+  r = TFK_FMA(z, r, TFK_KC(ar[2], TFK_AR2));
+  r = TFK_FMA(z, r, TFK_KC(ar[1], TFK_AR1));
+  r = TFK_FMA(z, r, TFK_KC(ar[0], TFK_AR0));
+  const double zr = z * r;
+  if (!big) return TFK_FMA(x, zr, x);
+  const double res = tfk_asin_upper(ax, zr, sqrt(t), t);
   return tfk_xor_sign(res, tfk_hi32(x)); /* x > 0 ? res : -res (x is neither 0 nor NaN here) */
 }
 
@@ -204,7 +189,7 @@ TFK_HD double tfk_atan2_simt(double y, double x) {
   const int big = mn >= 0.5 * mx;
   const double num = big ? mn - mx : mn;
   const double den = big ? mn + mx : mx;
-  const double t = TFK_QUOT(num, den);
+  const double t = num / den;
   const double z = t * t;
   double s = TFK_KC(at[11], TFK_AT11);
   s = TFK_FMA(z, s, TFK_KC(at[10], TFK_AT10));
