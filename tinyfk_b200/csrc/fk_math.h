@@ -327,15 +327,16 @@ template <class M> struct Ops {
   // Rotation::GetInverse, pose.h:284-299 (returns the default-constructed identity if norm <= 0)
   static TFK_FN Q qget_inverse(const Q &q) {
     T norm = q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z;
-    Q r = qidentity();
-    if (TFK_LIKELY(norm > T(0))) {
-      T a[4] = {q.w, -q.x, -q.y, -q.z};
-      M::divn_(a, M::den_(norm));
-      r.w = a[0];
-      r.x = a[1];
-      r.y = a[2];
-      r.z = a[3];
-    }
+    // the quotients first, the reference's test second: the common path is straight-line code and nothing is preset
+    // (a zero / negative / NaN norm takes divn_'s rare path and is overwritten here)
+    T a[4] = {q.w, -q.x, -q.y, -q.z};
+    M::divn_(a, M::den_(norm));
+    Q r;
+    r.w = a[0];
+    r.x = a[1];
+    r.y = a[2];
+    r.z = a[3];
+    if (TFK_UNLIKELY(!(norm > T(0)))) r = qidentity();
     return r;
   }
 
@@ -619,14 +620,14 @@ template <class M> struct Ops {
   // GetInverse (pose.h:284-299)
   static TFK_FN QZ qz_get_inverse(const QZ &q) {
     const T norm = q.w * q.w + q.z * q.z;
+    T a[2] = {q.w, -q.z}; // quotients first, the reference's test second (see qget_inverse)
+    M::divn_(a, M::den_(norm));
     QZ r;
-    r.z = T(0);
-    r.w = T(1);
-    if (TFK_LIKELY(norm > T(0))) {
-      T a[2] = {q.w, -q.z};
-      M::divn_(a, M::den_(norm));
-      r.w = a[0];
-      r.z = a[1];
+    r.w = a[0];
+    r.z = a[1];
+    if (TFK_UNLIKELY(!(norm > T(0)))) {
+      r.z = T(0);
+      r.w = T(1);
     }
     return r;
   }
