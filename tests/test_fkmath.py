@@ -93,6 +93,35 @@ def test_atan2_below_two_ulp_and_special_values(lib):
     assert np.allclose(so, g, rtol=0, atol=3e-16) and (np.signbit(so) == np.signbit(g)).all()
 
 
+def test_atan2_one_division_core_at_its_edges(lib):
+    """the split at mn / mx = 1/2 (both sides of it, every quadrant and both orders of |x|, |y|), magnitudes that the fkmath.h
+    function rescales before the core (beyond 2^1022, below 2^-900, subnormals), exponents hundreds of binades apart; the
+    device variant (fkmath_simt.h) on the same arguments, bit for bit"""
+    rng = np.random.default_rng(16)
+    n = 4000
+    mx = rng.uniform(0.5, 2.0, n)
+    ratio = np.concatenate([rng.uniform(0.49, 0.51, n // 2), np.full(n // 4, 0.5), rng.uniform(0.0, 1.0, n // 4)])
+    mn = mx * ratio
+    swap = rng.integers(0, 2, n).astype(bool)
+    y = np.where(swap, mx, mn) * rng.choice([-1.0, 1.0], n)
+    x = np.where(swap, mn, mx) * rng.choice([-1.0, 1.0], n)
+    e = rng.integers(-1070, 1020, n)
+    ys, xs = np.ldexp(y, e), np.ldexp(x, e)                       # same ratio at every magnitude, subnormals included
+    yw = np.ldexp(y, rng.integers(-1000, 1000, n))                 # ... and far apart
+    Y, X = np.concatenate([y, ys, yw]), np.concatenate([x, xs, x])
+    keep = (X != 0) | (Y != 0)
+    Y, X = Y[keep], X[keep]
+    o0, o1 = np.empty_like(X), np.empty_like(X)
+    lib.tfkm_atan2_v(Y.ctypes.data_as(_dp), X.ctypes.data_as(_dp), o0.ctypes.data_as(_dp), ctypes.c_long(X.size))
+    lib.tfkm_atan2_simt_v(Y.ctypes.data_as(_dp), X.ctypes.data_as(_dp), o1.ctypes.data_as(_dp), ctypes.c_long(X.size))
+    assert _bits_equal(o0, o1)
+    nz = (X != 0) & (Y != 0)  # mpmath has no signed zeros; those cases are in the special-value table above
+    sub = (np.abs(X) < 2.3e-308) | (np.abs(Y) < 2.3e-308)  # a subnormal operand carries fewer bits: its own rounding dominates
+    ok = nz & ~sub
+    assert _max_ulp(o0[ok], lambda a: mp.atan2(mp.mpf(float(a[0])), mp.mpf(float(a[1]))), list(zip(Y[ok], X[ok]))) < 2.0
+    assert np.allclose(o0[nz & sub], np.arctan2(Y[nz & sub], X[nz & sub]), rtol=1e-15, atol=5e-324)
+
+
 def _special_doubles():
     return np.array([0.0, -0.0, 1.0, -1.0, 0.5, -0.5, 0.3, 0.78125, 0.7853981633974483, 0.7853981633974484, 0.975,
                      0.4375, 0.6875, 1.1875, 2.4375, 1e-300, -1e-300, 5e-324, 1e300, np.inf, -np.inf, np.nan,

@@ -14,16 +14,16 @@
  * operation on both sides -- `__fma_rn` on the device, `fma()` on the host, which glibc evaluates exactly
  * with or without FMA hardware), comparisons and integer bit moves, so the two sides round identically.
  * The explicit fused operations are part of the DEFINITION of these functions (they do not depend on
- * -fmad / -ffp-contract): every Horner step and every "product minus correction" of the kernels is one
- * of them, which halves the FP64 instruction count of the polynomials on the GPU (DESIGN.md section 3,
- * "libm with explicit fused operations") and does not hurt accuracy.
+ * -fmad / -ffp-contract).
  *
- * Algorithms: classic table-free ones (Cody-Waite three-stage pi/2 reduction; odd / even
- * polynomial kernels on [-pi/4, pi/4]; rational kernel for asin with the sqrt identity above 0.5;
- * four-interval reduction for atan).  This structure follows the published fdlibm design
- * (Sun Microsystems, 1993, freely redistributable); the coefficients are our own fit
- * (tools/gen_fkmath_consts.py, mpmath).  Measured accuracy vs mpmath: see tests/test_fkmath.py
- * (sin, cos, asin < 1 ulp; atan2 < 2 ulp).
+ * Algorithms (table-free, straight-line on ordinary arguments; details at each function): sin / cos -- one
+ * three-step fused reduction by pi/2 for every argument below 2^20 * pi/2 and Horner kernels on the reduced
+ * argument, no tail word; asin -- one polynomial for both ranges, no division, the square root's rounding error
+ * restored from its exact residual; atan2 -- one division (numerator and denominator chosen before dividing), one
+ * polynomial on |t| <= 1/2, offsets k * pi/4.  tfk_atan (only behind the `atan` symbol of the pinned reference
+ * build) keeps the classic four-interval reduction.  The coefficients are our own fits
+ * (tools/gen_fkmath_consts.py, mpmath).  Measured accuracy vs mpmath (tests/test_fkmath.py): sin, cos < 1.5 ulp,
+ * asin < 1 ulp (0.60), atan2 < 2 ulp (1.52).  DESIGN.md section 3, "Arithmetic building blocks", has the history.
  *
  * Domain note: sin/cos are accurate for |x| < 2^38; beyond that the reduction is crude (but still
  * deterministic and identical on both sides).
