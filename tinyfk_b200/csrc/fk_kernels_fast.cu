@@ -1,6 +1,9 @@
-// fk_kernels_fast.cu -- opt-in FP32 mode (FMA contraction on, libdevice libm, analytic base-rotation
+// fk_kernels_fast.cu -- the opt-in modes.  FP32 mode (FMA contraction on, libdevice libm, analytic base-rotation
 // columns: the reference's eps = 1e-7 forward difference is below one FP32 ulp).  Tolerance vs the
 // reference: 1e-5 (BASELINE.json north_star).
+// The FP64 fast mode evaluates sin / cos / asin / atan2 with the portable libm's device variant (fkmath_simt.h; atan2's quotient as
+// a reciprocal-multiply) -- measured faster than libdevice's (fk_math.h:MathFast64); no strict code lives in this translation unit.
+#define TFK_FAST_PORTABLE_LIBM 1
 #include "fk_kernels.cuh"
 
 namespace tfk {

@@ -16,6 +16,11 @@
 #define TFK_FK_MATH_H
 
 #include "fkmath.h"
+#if defined(TFK_FAST_PORTABLE_LIBM) && defined(__CUDA_ARCH__)
+// FP64 fast mode only (a translation unit that never holds strict code), device pass: atan2's quotient as one correctly
+// rounded reciprocal times the numerator
+#define TFK_QUOT(a, b) ((a) * __drcp_rn(b))
+#endif
 #include "fkmath_simt.h"
 
 #if defined(__CUDACC__)
@@ -257,7 +262,9 @@ struct MathNative32 {
 };
 
 // Opt-in FP64 "fast" mode (SURVEY.md section 7 hard part 4): double arithmetic with FMA contraction (the translation
-// unit is built with the default -fmad=true), the platform libm (libdevice), quotients through one correctly rounded
+// unit is built with the default -fmad=true), the portable libm's device variant on the GPU (TFK_FAST_PORTABLE_LIBM, set by
+// fk_kernels_fast.cu and jit.cpp: cfg2 0.1389 -> 0.1356 ms, cfg3 0.2086 -> 0.2039 ms against libdevice, which builds every
+// polynomial coefficient from immediates) and the platform libm on the host, quotients through one correctly rounded
 // reciprocal and a multiplication (1 ulp), base-rotation columns analytic.  Not bit-identical to the reference: the
 // contract is 1e-12 on poses and analytic Jacobian entries.
 struct MathFast64 {
@@ -265,6 +272,24 @@ struct MathFast64 {
   enum { SPARE_REGS = 0 }; // see MathPortable (measured: no gain on cfg4 / cfg5)
   static TFK_FN double sin_(double x) { return ::sin(x); }
   static TFK_FN double cos_(double x) { return ::cos(x); }
+#if defined(TFK_FAST_PORTABLE_LIBM) && defined(__CUDA_ARCH__)
+  // fkmath_simt.h (explicit fused operations, coefficients as constant-bank operands, straight-line evaluations; atan2's
+  // quotient as a reciprocal-multiply): libdevice builds every polynomial coefficient from immediates
+  static __device__ __noinline__ TfkSinCos sincos_call_(double x) { return tfk_sincos_simt(x); }
+  static TFK_FN void sincos_(double x, double *s, double *c) {
+    const TfkSinCos r = sincos_call_(x);
+    *s = r.s;
+    *c = r.c;
+  }
+  static __device__ __noinline__ TfkSinCos2 sincos2_call_(double xa, double xb) { return tfk_sincos2_simt(xa, xb); }
+  static TFK_FN void sincos2_(double xa, double xb, double *sa, double *ca, double *sb, double *cb) {
+    const TfkSinCos2 r = sincos2_call_(xa, xb);
+    *sa = r.a.s, *ca = r.a.c, *sb = r.b.s, *cb = r.b.c;
+  }
+  static TFK_FN double asin_(double x) { return tfk_asin_simt(x); }
+  static TFK_FN double atan2_(double y, double x) { return tfk_atan2_simt(y, x); }
+  static TFK_FN double atan2_rare_(double y, double x) { return tfk_atan2(y, x); }
+#else
   static TFK_FN void sincos_(double x, double *s, double *c) {
 #if defined(__CUDA_ARCH__)
     ::sincos(x, s, c);
@@ -280,6 +305,7 @@ struct MathFast64 {
   static TFK_FN double asin_(double x) { return ::asin(x); }
   static TFK_FN double atan2_(double y, double x) { return ::atan2(y, x); }
   static TFK_FN double atan2_rare_(double y, double x) { return ::atan2(y, x); }
+#endif
   static TFK_FN double sqrt_(double x) { return ::sqrt(x); }
   struct Den {
     double b, y;

@@ -20,6 +20,12 @@
 
 #include "fkmath.h"
 
+/* the one quotient of atan2.  Strict mode: the IEEE division (part of the function's definition).  The FP64 fast mode
+   (fk_math.h:MathFast64, 1e-12 contract) defines it as a reciprocal-multiply before including this header. */
+#ifndef TFK_QUOT
+#define TFK_QUOT(a, b) ((a) / (b))
+#endif
+
 #if defined(__CUDACC__)
 /* constant-bank copies of the coefficients (same literals, so same bits) */
 struct TfkKc {
@@ -189,7 +195,7 @@ TFK_HD double tfk_atan2_simt(double y, double x) {
   const int big = mn >= 0.5 * mx;
   const double num = big ? mn - mx : mn;
   const double den = big ? mn + mx : mx;
-  const double t = num / den;
+  const double t = TFK_QUOT(num, den);
   const double z = t * t;
   double s = TFK_KC(at[11], TFK_AT11);
   s = TFK_FMA(z, s, TFK_KC(at[10], TFK_AT10));
