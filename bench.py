@@ -54,7 +54,7 @@ METRIC = "pr2_arm_fk_jacobian_configs_per_sec"
 UNIT = "configs/s"
 PRECISIONS = {"fp64": 0, "fp32": 1, "fp64_fast": 2}
 MODE_NOTE = ["strict FP64: reference operation order, portable libm, no FMA contraction", "FP32 opt-in mode",
-             "FP64 fast opt-in mode: FMA, CUDA libm, analytic base columns (1e-12 contract)"]
+             "FP64 fast opt-in mode: FMA contraction, reciprocal quotients, analytic base columns (1e-12 contract)"]
 
 
 def parse_args():

@@ -24,7 +24,7 @@
  *     with n_dof = n_joint (+3 PLANER: x, y, yaw columns, python/tinyfk/__init__.py:154-158; +6 FLOATING).
  *   - precision: TFK_F64_STRICT computes in double in the reference's operation order (matches the
  *     reference to 1e-12 and the libm-pinned reference bit for bit); TFK_F32 is the opt-in float mode
- *     (arrays are float, tolerance 1e-5); TFK_F64_FAST is the opt-in double mode with FMA contraction, the CUDA libm,
+ *     (arrays are float, tolerance 1e-5); TFK_F64_FAST is the opt-in double mode with FMA contraction,
  *     reciprocal-multiply quotients and ANALYTIC base-rotation Jacobian columns: poses and analytic Jacobian entries
  *     within 1e-12 of the reference; its base-rotation columns are the exact derivative, which the reference's
  *     eps = 1e-7 forward difference (src/kinematics.cpp:201-232) only approximates to ~1e-7 * |f''|.

@@ -190,6 +190,19 @@ bool Engine::spec_eligible(const PlanEntry &e, int precision, int *tile, int *bp
       }
     }
   }
+  // FP64 fast (since it runs the portable libm: 2.2 k instead of 3.3 k warp instructions per 32 cfg2 configurations, long
+  // scoreboard 1.8 and barrier 0.5 cycles per issue at 2 x 256): four blocks of 128 -- cfg2 0.1386 -> 0.1348 ms, cfg3 0.2036 ->
+  // 0.1949 ms (83 % of HBM); 2 x 320: cfg2 0.1319 ms but no room for cfg3's records.  Strict keeps 2 x 256 (cfg2 0.1909 ms against
+  // 0.2107 at 4 x 128, 0.1957 at 2 x 320, 0.2238 at 3 x 192; cfg3 0.2606 against 0.2551 / - / 0.2640)
+  if (precision == PREC_F64_FAST) {
+    const int sm = fused_smem_bytes(128, h->fz_size, rb);
+    if (4 * (sm + 1024) <= limit) {
+      *tile = 128;
+      *bps = 4;
+      *smem = sm;
+      return true;
+    }
+  }
   {
     const int sm = fused_smem_bytes(256, h->fz_size, rb);
     int b = precision == PREC_F32 ? 3 : 2;
