@@ -4,6 +4,7 @@ header naming the kernel-source hash they belong to, the per-launch traffic tabl
 bench lines.  Run in the build container after the cycle."""
 import json
 import os
+import re
 import shutil
 import sys
 
@@ -36,6 +37,19 @@ def main():
                     "tools/gpu_cycle_final.sh; B200, CUDA 12.9)\n"
                     "# %s: kernel sources %s (bench.py:kernel_source_hash); summarised by tools/ncu_lines.py\n" % (c, m, note, here))
             open(os.path.join(P, "r2_full_%s_%s.txt" % (c, m)), "w").write(head + body)
+    # FP64-pipe warp instructions per 32 configurations (bench.py's `roofline.fp64_pipe` bound): `--set full` has no per-pipe
+    # instruction COUNT, so it comes from the opcode histogram of the same capture (tools/ncu_lines.py): the D* opcodes
+    for key, e in rec["entries"].items():
+        c, m = key.split("/")
+        if m == "fp32":
+            continue
+        txt = open(os.path.join(G, "f_lines_%s_%s.txt" % (c, m))).read()
+        hist = re.search(r"executed warp instructions per 32 configs: \d+\n(.*)\n", txt)
+        if hist:
+            ops = dict(kv.split("=") for kv in hist.group(1).split() if "=" in kv)
+            e["fp64_warp_instructions_per_32_configs"] = float(sum(int(v) for k, v in ops.items() if k.startswith("D")))
+            e["fp64_count_source"] = "D* opcodes (DFMA, DMUL, DADD, DSETP ...) of the capture's opcode histogram, top 24 opcodes"
+    json.dump(rec, open(os.path.join(G, "ncu_traffic.json"), "w"), indent=1)
     shutil.copy(os.path.join(G, "ncu_traffic.json"), os.path.join(P, "ncu_traffic.json"))
     shutil.copy(os.path.join(G, "f_launches_cfg2.csv"), os.path.join(P, "r2_launches_cfg2_strict_final.csv"))
     jsonl(os.path.join(G, "f_b.log"), os.path.join(P, "r2_logs", "bench_n1_final.jsonl"))
