@@ -144,3 +144,22 @@ def test_switch_and_untrusted_directory(cache_dir, monkeypatch):
     with pytest.raises(ValueError):
         capi.Model("<robot name='r'><link name='a'/><link name='a'/></robot>")
     assert len(os.listdir(cache_dir)) == n
+
+
+def test_concurrent_processes_share_one_cache(cache_dir):
+    """several processes that meet the same URDF at the same time (one rank per GPU under torchrun): every one gets a correct
+    model, whichever of them writes the file (temporary + rename), and the file they leave behind verifies"""
+    import subprocess
+    import sys
+
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from tinyfk_b200 import capi, workloads as W\n"
+            "m = capi.Model(W.urdf_text('pr2.urdf'))\n"
+            "print(m.n_links, m.n_joints, int(m.tables_from_cache()))\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    procs = [subprocess.Popen([sys.executable, "-c", code], stdout=subprocess.PIPE, text=True, env=dict(os.environ)) for _ in range(6)]
+    outs = [p.communicate()[0].split() for p in procs]
+    assert all(p.returncode == 0 for p in procs)
+    assert all(o[:2] == ["162", "45"] for o in outs)
+    files = os.listdir(cache_dir)
+    assert len(files) == 1 and not files[0].endswith(".tmp")
+    assert capi.Model(W.urdf_text("pr2.urdf")).tables_from_cache()
