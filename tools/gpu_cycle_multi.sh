@@ -1,4 +1,4 @@
-# cycle L (N GPUs): the engine's own device-list split on N real devices, bench.py under torchrun with N ranks (weak + strong
+# multi-GPU cycle (N GPUs, `gpurun --gpus N -- bash tools/gpu_cycle_multi.sh N`): the engine's own device-list split on N real devices, bench.py under torchrun with N ranks (weak + strong
 # readings, per-rank e2e, in-process e2e over devices 0..N-1); D2H=1 also measures the D2H ceiling per process layout
 NG=${1:-8}
 mkdir -p gpurun_out
